@@ -1,0 +1,181 @@
+/*
+ * b200sort.h — C ABI of the B200-native radix sort engine that stands in for
+ * the sort path of the Rust crate nessex/rdst.
+ *
+ * This is the drop-in boundary.  The reference is a pure-Rust library with no
+ * FFI of its own; the functions below are what an `extern "C"` block inside the
+ * reference's `RadixSortBuilder::sort` would bind (see INTEGRATION.md for the
+ * Rust stub).  Each entry point cites the reference interface it replaces
+ * (paths relative to the reference checkout).
+ *
+ * Conventions (mirroring src/radix_sort_builder.rs:149-157):
+ *   - the caller owns the data; the sort is in place; scratch is owned by the
+ *     library (a per-device cached pool) unless the caller passes its own;
+ *   - calls block until the result is in the caller's buffer;
+ *   - the reference API is infallible, so every failure is a non-zero return
+ *     code that the binding turns into a panic; there is NO CPU fallback;
+ *   - thread-safe: concurrent calls serialise on a per-device context.
+ */
+#ifndef B200SORT_H
+#define B200SORT_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define B200_MAX_LEVELS 64
+
+/* Return codes. 0 = success. */
+enum {
+    B200_OK = 0,
+    B200_ERR_LEVELS_ZERO = 1,   /* RadixKey::LEVELS == 0 — the reference panics here
+                                   (src/radix_sort_builder.rs:22) */
+    B200_ERR_BAD_DESC = 2,      /* descriptor inconsistent (offset outside the record, bad width …) */
+    B200_ERR_CUDA = 3,          /* a CUDA runtime call failed; see b200_last_cuda_error() */
+    B200_ERR_NO_DEVICE = 4,     /* no usable sm_100 device */
+    B200_ERR_ALLOC = 5,         /* scratch / staging allocation failed */
+    B200_ERR_BAD_ARG = 6,       /* null pointer, unknown variant id … */
+    B200_ERR_LEVEL_RANGE = 7    /* level >= LEVELS (src/radix_key.rs:18 debug_assert) */
+};
+
+/*
+ * How RadixKey::get_level (src/radix_key.rs:1-5) is lowered for the device.
+ * Level 0 is the LEAST significant byte (README.md:37-38).
+ *
+ *  UINT  — src/radix_key_impl.rs:3-76   (self >> 8*level) as u8
+ *  SINT  — src/radix_key_impl.rs:87-160 ((self ^ MIN) >> 8*level) as u8
+ *  FLOAT — src/radix_key_impl.rs:162-185 IEEE total-order map, then as SINT
+ *  BYTES — src/radix_key_impl.rs:78-85 and user keys (examples/impl_radix_key.rs):
+ *          level l reads record byte level[l].byte_offset, xor level[l].xor_mask
+ */
+typedef enum {
+    B200_KEY_UINT = 0,
+    B200_KEY_SINT = 1,
+    B200_KEY_FLOAT = 2,
+    B200_KEY_BYTES = 3
+} b200_key_kind;
+
+typedef struct {
+    uint16_t byte_offset; /* byte inside the record that holds this level's digit */
+    uint8_t xor_mask;     /* applied after the load */
+    uint8_t _pad;
+} b200_level;
+
+typedef struct {
+    uint32_t elem_size;   /* size_of::<T>() — record stride, payload included */
+    uint32_t elem_align;  /* align_of::<T>() (informational; 1,2,4,8,16) */
+    uint32_t levels;      /* T::LEVELS; may be smaller than key_width (partial keys, src/lib.rs:58-76) */
+    uint32_t kind;        /* b200_key_kind */
+    uint32_t key_offset;  /* byte offset of the little-endian key word in the record (UINT/SINT/FLOAT) */
+    uint32_t key_width;   /* bytes of the key word: 1,2,4,8,16 (FLOAT: 4 or 8) */
+    b200_level level[B200_MAX_LEVELS]; /* BYTES kind only: one entry per level, level 0 first */
+} b200_key_desc;
+
+/*
+ * Options — what RadixSortBuilder carries (src/radix_sort_builder.rs:8-12)
+ * re-expressed for the device engine.
+ */
+typedef struct {
+    uint32_t stable;   /* 1 = rdst's stable order (Lsb/LrLsb/MtLsb, src/sorts/lsb_sort.rs:5-7).
+                          0 = any sorted permutation is legal (default tuner). The engine is a
+                          stable LSD sort either way; the flag is recorded for the tuner. */
+    int32_t variant;   /* -1 = let the tuner pick; else index < b200_variant_count() */
+    int32_t device;    /* CUDA device ordinal; -1 = current device */
+    void* stream;      /* cudaStream_t to order the work on; NULL = the library's own stream */
+} b200_sort_opts;
+
+typedef struct {
+    uint32_t levels_run;       /* passes actually executed */
+    uint32_t levels_skipped;   /* single-bucket levels (src/sorts/lsb_sort.rs:20-23) */
+    uint32_t variant;          /* tile/occupancy variant used by the pass kernel */
+    uint32_t copy_back;        /* 1 if a final device copy into the caller's buffer was needed
+                                  (src/sorts/lsb_sort.rs:117-126) */
+    uint64_t algorithmic_bytes;/* n*elem_size*(1 + 2*levels_run) (+ n*elem_size if copy_back) */
+    float ms_hist;             /* K1 + scan, CUDA events */
+    float ms_passes;           /* all K2 passes (+ copy back), CUDA events */
+    float ms_h2d, ms_d2h;      /* host entry point only */
+    float ms_total;            /* first launch to last completion */
+    uint64_t tiles_per_pass;
+} b200_stats;
+
+/*
+ * Sort `n` records that live in HOST memory, in place.
+ * Replaces: RadixSortBuilder::sort (src/radix_sort_builder.rs:149-157) →
+ *           Sorter::route_top_level (src/sorter.rs:105-119), i.e. everything
+ *           behind RadixSort::radix_sort_unstable (src/radix_sort.rs:21-45).
+ * n <= 1 returns immediately (src/radix_sort_builder.rs:151).
+ */
+int b200_sort_host(void* host_ptr, size_t n, const b200_key_desc* desc,
+                   const b200_sort_opts* opts, b200_stats* stats);
+
+/*
+ * Sort `n` records that already live in DEVICE memory, in place.
+ * `dev_tmp` is an optional caller-owned scratch of n*elem_size bytes
+ * (the `tmp_bucket` of src/sorts/lsb_sort.rs:53); NULL = library pool.
+ * Replaces: Sorter::lsb_sort_adapter / mt_lsb_sort_adapter and the counting
+ *           utilities they call (src/sorts/lsb_sort.rs:38-128,
+ *           src/sorts/mt_lsb_sort.rs:136-195, src/sort_utils.rs:33-249).
+ */
+int b200_sort_device(void* dev_ptr, void* dev_tmp, size_t n, const b200_key_desc* desc,
+                     const b200_sort_opts* opts, b200_stats* stats);
+
+/*
+ * K1 on its own: all LEVELS 256-bin histograms of device data in one read.
+ * `hist_out` is HOST memory, levels*256 uint64 counts, level 0 first.
+ * Replaces: get_counts / get_counts_with_ends / get_tile_counts +
+ *           aggregate_tile_counts (src/sort_utils.rs:108-249).
+ */
+int b200_histogram_device(const void* dev_ptr, size_t n, const b200_key_desc* desc,
+                          const b200_sort_opts* opts, uint64_t* hist_out);
+
+/*
+ * One stable counting-sort pass over one level, device to device
+ * (dev_src and dev_dst must not overlap).  `counts` is the HOST 256-bin
+ * histogram of that level (as returned by b200_histogram_device).
+ * Replaces: out_of_place_sort / lr_out_of_place_sort and the per-level body of
+ *           mt_lsb_sort (src/sorts/out_of_place_sort.rs:51-108,201-275,
+ *           src/sorts/mt_lsb_sort.rs:40-133).
+ */
+int b200_pass_device(const void* dev_src, void* dev_dst, size_t n, const b200_key_desc* desc,
+                     uint32_t level, const uint64_t* counts, const b200_sort_opts* opts);
+
+/*
+ * Multi-GPU helpers for the range-partitioned sort (one process per GPU; the
+ * exchange itself is the caller's collective).  Given this rank's device data
+ * and P-1 splitter digits on `level`, partition the records stably into P
+ * contiguous destination ranges (dest g = digits in [split[g-1], split[g]))
+ * and return the per-destination record counts in host memory.
+ * This is b200_pass_device with a 256 -> P bucket remap.
+ */
+int b200_partition_device(const void* dev_src, void* dev_dst, size_t n, const b200_key_desc* desc,
+                          uint32_t level, const uint64_t* counts, const uint32_t* split, uint32_t parts,
+                          uint64_t* part_counts_out, const b200_sort_opts* opts);
+
+/*
+ * RadixKey::get_level evaluated on the host through the descriptor — lets the
+ * binding validate a user key against its lowering before launching.
+ * Returns the digit (0..255) or a negative error code.
+ */
+int b200_get_level(const void* record, const b200_key_desc* desc, uint32_t level);
+
+/* Pinned host memory for the host entry point's fast path (plain DMA, no staging). */
+int b200_host_alloc(void** out, size_t bytes);
+int b200_host_free(void* p);
+/* Release the cached per-device scratch pool. */
+int b200_release_scratch(int device);
+
+/* Tuner introspection: the Tuner now only picks a tile/occupancy variant. */
+int b200_variant_count(void);
+const char* b200_variant_name(int variant);
+
+const char* b200_strerror(int code);
+const char* b200_last_cuda_error(void);
+const char* b200_version(void);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* B200SORT_H */

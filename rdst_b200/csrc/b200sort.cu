@@ -1,0 +1,760 @@
+// b200sort.cu — the C ABI of the B200 radix sort engine (include/b200sort.h)
+// and the host pass planner behind it.
+//
+// The planner is what is left of rdst's router and LSB driver on a GPU
+//   Sorter::handle_chunk / route*       (reference src/sorter.rs:24-171)
+//   Sorter::lsb_sort_adapter            (reference src/sorts/lsb_sort.rs:38-128)
+//   mt_lsb_sort_adapter                 (reference src/sorts/mt_lsb_sort.rs:136-195)
+// : count every level once (K1), skip levels whose histogram is one bucket
+// (lsb_sort.rs:20-23, mt_lsb_sort.rs:170-174, ska_sort.rs:52-54), run one stable
+// pass (K2) per remaining level from level 0 upwards while ping-ponging between
+// the caller's buffer and a scratch buffer (lsb_sort.rs:86-98), and copy back if
+// the result ended in scratch (lsb_sort.rs:117-126).  No recursion, no CPU path.
+#include "../../include/b200sort.h"
+
+#include <cuda_runtime.h>
+
+#include <algorithm>
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <mutex>
+#include <string>
+#include <vector>
+
+#include "hist.cuh"
+#include "launch.h"
+#include "onesweep.cuh"
+#include "variants.h"
+
+using namespace b200;
+
+namespace {
+
+thread_local std::string g_last_cuda_error;
+
+#define CUDA_TRY(expr)                                                                          \
+    do {                                                                                        \
+        cudaError_t _e = (expr);                                                                \
+        if (_e != cudaSuccess) {                                                                \
+            g_last_cuda_error = std::string(#expr) + ": " + cudaGetErrorString(_e);             \
+            cudaGetLastError();                                                                 \
+            return B200_ERR_CUDA;                                                               \
+        }                                                                                       \
+    } while (0)
+
+// ---------------------------------------------------------------------------
+// Descriptor lowering: RadixKey::get_level -> (byte offset, xor mask) per level.
+// ---------------------------------------------------------------------------
+struct Lowered {
+    uint32_t elem_size = 0, levels = 0;
+    bool is_float = false;
+    uint32_t sign_byte = 0;
+    LevelLowering lv[MAX_LEVELS];
+    bool contiguous = false;  // level l is byte key_offset + l (word kinds)
+    uint32_t key_offset = 0, key_width = 0;
+};
+
+int lower_desc(const b200_key_desc* d, Lowered* out) {
+    if (!d) return B200_ERR_BAD_ARG;
+    if (d->levels == 0) return B200_ERR_LEVELS_ZERO;
+    if (d->levels > B200_MAX_LEVELS) return B200_ERR_BAD_DESC;
+    if (d->elem_size == 0 || d->elem_size > 65535) return B200_ERR_BAD_DESC;
+    Lowered lo;
+    lo.elem_size = d->elem_size;
+    lo.levels = d->levels;
+    switch (d->kind) {
+        case B200_KEY_UINT:
+        case B200_KEY_SINT:
+        case B200_KEY_FLOAT: {
+            const uint32_t w = d->key_width;
+            if (!(w == 1 || w == 2 || w == 4 || w == 8 || w == 16)) return B200_ERR_BAD_DESC;
+            if (d->kind == B200_KEY_FLOAT && !(w == 4 || w == 8)) return B200_ERR_BAD_DESC;
+            if (uint64_t(d->key_offset) + w > d->elem_size) return B200_ERR_BAD_DESC;
+            if (d->levels > w) return B200_ERR_BAD_DESC;
+            lo.contiguous = true;
+            lo.key_offset = d->key_offset;
+            lo.key_width = w;
+            lo.is_float = d->kind == B200_KEY_FLOAT;
+            lo.sign_byte = d->key_offset + w - 1;
+            for (uint32_t l = 0; l < d->levels; ++l) {
+                lo.lv[l].byte_offset = d->key_offset + l;
+                lo.lv[l].xor_mask = (d->kind != B200_KEY_UINT && l == w - 1) ? 0x80u : 0u;
+            }
+            break;
+        }
+        case B200_KEY_BYTES: {
+            for (uint32_t l = 0; l < d->levels; ++l) {
+                if (d->level[l].byte_offset >= d->elem_size) return B200_ERR_BAD_DESC;
+                lo.lv[l].byte_offset = d->level[l].byte_offset;
+                lo.lv[l].xor_mask = d->level[l].xor_mask;
+            }
+            break;
+        }
+        default:
+            return B200_ERR_BAD_DESC;
+    }
+    *out = lo;
+    return B200_OK;
+}
+
+uint32_t host_digit(const uint8_t* rec, const Lowered& lo, uint32_t level) {
+    uint32_t b = rec[lo.lv[level].byte_offset];
+    if (lo.is_float && (rec[lo.sign_byte] & 0x80u)) return b ^ 0xffu;
+    return b ^ lo.lv[level].xor_mask;
+}
+
+DigitParams digit_params(const Lowered& lo, uint32_t level) {
+    DigitParams dp;
+    dp.word = lo.lv[level].byte_offset / 4;
+    dp.shift = (lo.lv[level].byte_offset % 4) * 8;
+    dp.xor_mask = lo.lv[level].xor_mask;
+    dp.sign_word = lo.sign_byte / 4;
+    dp.sign_shift = (lo.sign_byte % 4) * 8 + 7;
+    return dp;
+}
+
+// ---------------------------------------------------------------------------
+// Per-device context: stream, events, cached scratch.
+// ---------------------------------------------------------------------------
+struct DeviceCtx {
+    int dev = -1;
+    bool ready = false;
+    std::mutex mu;
+    cudaStream_t stream = nullptr;
+    cudaEvent_t ev[8] = {};
+    int sm_count = 0;
+    // small device block: hist [64][256] u64 | base [64][256] u64 | tickets [64] u32 | remap [256] u8 | part base
+    uint8_t* d_small = nullptr;
+    uint64_t* h_hist = nullptr;  // pinned [64][256]
+    void* d_tmp = nullptr;
+    size_t tmp_bytes = 0;
+    uint64_t* d_lookback = nullptr;
+    size_t lookback_bytes = 0;
+    void* d_stage = nullptr;  // device copy of host data for b200_sort_host
+    size_t stage_bytes = 0;
+    void* h_bounce[2] = {nullptr, nullptr};  // pinned bounce buffers for pageable host memory
+    size_t bounce_bytes = 0;
+    cudaEvent_t bounce_ev[2] = {};
+};
+
+constexpr size_t SMALL_HIST_OFF = 0;
+constexpr size_t SMALL_BASE_OFF = size_t(MAX_LEVELS) * RADIX * 8;
+constexpr size_t SMALL_TICKET_OFF = SMALL_BASE_OFF + size_t(MAX_LEVELS) * RADIX * 8;
+constexpr size_t SMALL_REMAP_OFF = SMALL_TICKET_OFF + 1024;
+constexpr size_t SMALL_PBASE_OFF = SMALL_REMAP_OFF + 256;
+constexpr size_t SMALL_BYTES = SMALL_PBASE_OFF + RADIX * 8;
+
+constexpr int MAX_DEVICES = 64;
+DeviceCtx g_ctx[MAX_DEVICES];
+
+int get_ctx(int device, DeviceCtx** out) {
+    int dev = device;
+    if (dev < 0) {
+        CUDA_TRY(cudaGetDevice(&dev));
+    }
+    int count = 0;
+    cudaError_t e = cudaGetDeviceCount(&count);
+    if (e != cudaSuccess || count == 0) {
+        g_last_cuda_error = std::string("cudaGetDeviceCount: ") + cudaGetErrorString(e);
+        cudaGetLastError();
+        return B200_ERR_NO_DEVICE;
+    }
+    if (dev >= count || dev >= MAX_DEVICES) return B200_ERR_BAD_ARG;
+    DeviceCtx& c = g_ctx[dev];
+    std::lock_guard<std::mutex> lk(c.mu);
+    if (!c.ready) {
+        CUDA_TRY(cudaSetDevice(dev));
+        cudaDeviceProp prop;
+        CUDA_TRY(cudaGetDeviceProperties(&prop, dev));
+        if (prop.major < 10) {
+            g_last_cuda_error = "device is not sm_100 class";
+            return B200_ERR_NO_DEVICE;
+        }
+        c.dev = dev;
+        c.sm_count = prop.multiProcessorCount;
+        CUDA_TRY(cudaStreamCreateWithFlags(&c.stream, cudaStreamNonBlocking));
+        for (auto& ev : c.ev) CUDA_TRY(cudaEventCreate(&ev));
+        for (auto& ev : c.bounce_ev) CUDA_TRY(cudaEventCreateWithFlags(&ev, cudaEventDisableTiming));
+        CUDA_TRY(cudaMalloc(&c.d_small, SMALL_BYTES));
+        CUDA_TRY(cudaMallocHost(&c.h_hist, size_t(MAX_LEVELS) * RADIX * 8));
+        c.ready = true;
+    }
+    *out = &c;
+    return B200_OK;
+}
+
+int ensure_bytes(void** p, size_t* have, size_t need) {
+    if (*have >= need && *p) return B200_OK;
+    if (*p) {
+        cudaFree(*p);
+        *p = nullptr;
+        *have = 0;
+    }
+    // grow with a little slack so that repeated slightly larger sorts do not thrash
+    size_t want = need + need / 16 + 256;
+    cudaError_t e = cudaMalloc(p, want);
+    if (e != cudaSuccess) {
+        cudaGetLastError();
+        want = need;
+        e = cudaMalloc(p, want);
+    }
+    if (e != cudaSuccess) {
+        g_last_cuda_error = std::string("cudaMalloc scratch: ") + cudaGetErrorString(e);
+        cudaGetLastError();
+        *p = nullptr;
+        return B200_ERR_ALLOC;
+    }
+    *have = want;
+    return B200_OK;
+}
+
+// ---------------------------------------------------------------------------
+// Kernel selection.
+// ---------------------------------------------------------------------------
+bool word_path_ok(const Lowered& lo, const void* a, const void* b) {
+    if (lo.elem_size % 4 != 0) return false;
+    const uint32_t words = lo.elem_size / 4;
+    if (words < 1 || words > 4) return false;
+    const uintptr_t pa = reinterpret_cast<uintptr_t>(a), pb = reinterpret_cast<uintptr_t>(b);
+    return pa % 16 == 0 && pb % 16 == 0;
+}
+
+PassLaunch get_pass_launch(uint32_t words, bool floatk, bool remap, int variant) {
+    switch (words) {
+        case 1: return get_pass_launch_w1(floatk, remap, variant);
+        case 2: return get_pass_launch_w2(floatk, remap, variant);
+        case 3: return get_pass_launch_w3(floatk, remap, variant);
+        case 4: return get_pass_launch_w4(floatk, remap, variant);
+    }
+    return PassLaunch{};
+}
+
+int default_variant(uint32_t words, uint64_t n) {
+    (void)words;
+    (void)n;
+    const char* env = getenv("B200SORT_VARIANT");
+    if (env) {
+        int v = atoi(env);
+        if (v >= 0 && v < NUM_VARIANTS) return v;
+    }
+    return 1;
+}
+
+constexpr int BYTE_THREADS = 256, BYTE_ITEMS = 4;
+
+struct PassPlan {
+    bool word_path;
+    uint32_t words;
+    PassLaunch pl;
+    uint32_t tile;
+    uint32_t num_tiles;
+    int grid;
+    int variant;
+};
+
+int plan_pass(DeviceCtx& c, const Lowered& lo, uint64_t n, const void* a, const void* b, bool remap, int variant,
+              PassPlan* out) {
+    PassPlan pp{};
+    pp.word_path = word_path_ok(lo, a, b);
+    if (pp.word_path) {
+        pp.words = lo.elem_size / 4;
+        if (variant < 0) variant = default_variant(pp.words, n);
+        if (variant >= NUM_VARIANTS) return B200_ERR_BAD_ARG;
+        if (remap) variant = 0;
+        pp.variant = variant;
+        pp.pl = get_pass_launch(pp.words, lo.is_float, remap, variant);
+        if (!pp.pl.kernel) return B200_ERR_BAD_ARG;
+        pp.tile = pp.pl.tile;
+        CUDA_TRY(cudaFuncSetAttribute(pp.pl.kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, int(pp.pl.smem)));
+        int occ = 0;
+        CUDA_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, pp.pl.kernel, pp.pl.threads, pp.pl.smem));
+        if (occ < 1) {
+            g_last_cuda_error = "pass kernel does not fit on an SM";
+            return B200_ERR_CUDA;
+        }
+        const uint64_t tiles = (n + pp.tile - 1) / pp.tile;
+        if (tiles > 0xffffffffull) return B200_ERR_BAD_ARG;
+        pp.num_tiles = uint32_t(tiles);
+        pp.grid = int(std::min<uint64_t>(tiles, uint64_t(c.sm_count) * occ));
+    } else {
+        pp.variant = 0;
+        pp.tile = BYTE_THREADS * BYTE_ITEMS;
+        const uint64_t tiles = (n + pp.tile - 1) / pp.tile;
+        if (tiles > 0xffffffffull) return B200_ERR_BAD_ARG;
+        pp.num_tiles = uint32_t(tiles);
+        pp.grid = int(std::min<uint64_t>(tiles, uint64_t(c.sm_count) * 8));
+    }
+    *out = pp;
+    return B200_OK;
+}
+
+int launch_pass(DeviceCtx& c, cudaStream_t st, const PassPlan& pp, const Lowered& lo, const void* src, void* dst,
+                uint64_t n, uint32_t level, const uint64_t* d_base, uint32_t* d_ticket, uint32_t tag,
+                const uint8_t* d_remap) {
+    if (pp.word_path) {
+        PassParams p;
+        p.src = static_cast<const uint32_t*>(src);
+        p.dst = static_cast<uint32_t*>(dst);
+        p.n = n;
+        p.dp = digit_params(lo, level);
+        p.bucket_base = d_base;
+        p.lookback = c.d_lookback;
+        p.ticket = d_ticket;
+        p.tag = tag;
+        p.num_tiles = pp.num_tiles;
+        p.remap = d_remap;
+        pp.pl.kernel<<<pp.grid, pp.pl.threads, pp.pl.smem, st>>>(p);
+    } else {
+        BytePassParams p;
+        p.src = static_cast<const uint8_t*>(src);
+        p.dst = static_cast<uint8_t*>(dst);
+        p.n = n;
+        p.elem_size = lo.elem_size;
+        p.byte_offset = lo.lv[level].byte_offset;
+        p.xor_mask = lo.lv[level].xor_mask;
+        p.is_float = lo.is_float ? 1u : 0u;
+        p.sign_byte = lo.sign_byte;
+        p.bucket_base = d_base;
+        p.lookback = c.d_lookback;
+        p.ticket = d_ticket;
+        p.tag = tag;
+        p.num_tiles = pp.num_tiles;
+        p.remap = d_remap;
+        onesweep_pass_bytes_kernel<BYTE_THREADS, BYTE_ITEMS><<<pp.grid, BYTE_THREADS, 0, st>>>(p);
+    }
+    CUDA_TRY(cudaGetLastError());
+    return B200_OK;
+}
+
+// ---- K1 dispatch (instantiations live in hist_w*.cu) ----
+bool hist_agg_enabled() {
+    const char* env = getenv("B200SORT_HIST_AGG");
+    return env ? atoi(env) != 0 : true;
+}
+
+// Fills d_hist [levels][256] (u64) on the stream.
+int launch_histogram(DeviceCtx& c, cudaStream_t st, const Lowered& lo, const void* src, uint64_t n,
+                     unsigned long long* d_hist) {
+    CUDA_TRY(cudaMemsetAsync(d_hist, 0, size_t(lo.levels) * RADIX * 8, st));
+    const bool aligned = reinterpret_cast<uintptr_t>(src) % 16 == 0;
+    const uint32_t words = lo.elem_size / 4;
+    bool fast = aligned && lo.elem_size % 4 == 0 && words >= 1 && words <= 4 && lo.contiguous &&
+                lo.key_offset % 4 == 0 && (!lo.is_float || lo.levels == lo.key_width);
+    const uint32_t nkw = (lo.levels + 3) / 4;
+    if (fast && lo.key_offset / 4 + nkw > words) fast = false;
+    // packed loads assume the key starts the record
+    if (fast && words == nkw && lo.key_offset != 0) fast = false;
+    const int grid_full = c.sm_count * 4;
+    if (fast) {
+        HistParams hp;
+        hp.src = static_cast<const uint32_t*>(src);
+        hp.n = n;
+        hp.kw0 = lo.key_offset / 4;
+        hp.sign_shift = ((lo.levels - 1) % 4) * 8 + 7;
+        for (uint32_t l = 0; l < 16; ++l) hp.xor_mask[l] = l < lo.levels ? lo.lv[l].xor_mask : 0u;
+        hp.ghist = d_hist;
+        const uint64_t per_thread = 8;
+        const int grid =
+            int(std::max<uint64_t>(1, std::min<uint64_t>(grid_full, (n + HIST_THREADS * per_thread - 1) /
+                                                                         (HIST_THREADS * per_thread))));
+        bool ok = false;
+        const bool agg = hist_agg_enabled();
+        switch (words) {
+            case 1: ok = launch_hist_fast_w1(lo.levels, lo.is_float, agg, grid, st, hp); break;
+            case 2: ok = launch_hist_fast_w2(lo.levels, lo.is_float, agg, grid, st, hp); break;
+            case 3: ok = launch_hist_fast_w3(lo.levels, lo.is_float, agg, grid, st, hp); break;
+            case 4: ok = launch_hist_fast_w4(lo.levels, lo.is_float, agg, grid, st, hp); break;
+        }
+        if (ok) {
+            CUDA_TRY(cudaGetLastError());
+            return B200_OK;
+        }
+    }
+    HistGenericParams gp;
+    gp.src = static_cast<const uint8_t*>(src);
+    gp.n = n;
+    gp.elem_size = lo.elem_size;
+    gp.levels = lo.levels;
+    gp.is_float = lo.is_float ? 1u : 0u;
+    gp.sign_byte = lo.sign_byte;
+    gp.ghist = d_hist;
+    for (uint32_t l = 0; l < MAX_LEVELS; ++l) gp.lv[l] = l < lo.levels ? lo.lv[l] : LevelLowering{0, 0};
+    const size_t smem = size_t(lo.levels) * RADIX * 4;
+    static bool attr_set = false;
+    if (!attr_set) {
+        CUDA_TRY(cudaFuncSetAttribute(hist_generic_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                      MAX_LEVELS * RADIX * 4));
+        attr_set = true;
+    }
+    const int grid = int(std::max<uint64_t>(1, std::min<uint64_t>(grid_full, (n + HIST_THREADS - 1) / HIST_THREADS)));
+    hist_generic_kernel<<<grid, HIST_THREADS, smem, st>>>(gp);
+    CUDA_TRY(cudaGetLastError());
+    return B200_OK;
+}
+
+// ---------------------------------------------------------------------------
+// The sort proper, device resident.
+// ---------------------------------------------------------------------------
+int sort_device_impl(DeviceCtx& c, cudaStream_t st, void* data, void* tmp, uint64_t n, const Lowered& lo,
+                     int variant, bool result_anywhere, void** result_ptr, b200_stats* stats) {
+    unsigned long long* d_hist = reinterpret_cast<unsigned long long*>(c.d_small + SMALL_HIST_OFF);
+    unsigned long long* d_base = reinterpret_cast<unsigned long long*>(c.d_small + SMALL_BASE_OFF);
+    uint32_t* d_ticket = reinterpret_cast<uint32_t*>(c.d_small + SMALL_TICKET_OFF);
+
+    CUDA_TRY(cudaEventRecord(c.ev[0], st));
+    int rc = launch_histogram(c, st, lo, data, n, d_hist);
+    if (rc) return rc;
+    scan_hist_kernel<<<lo.levels, RADIX, 0, st>>>(d_hist, d_base);
+    CUDA_TRY(cudaGetLastError());
+    CUDA_TRY(cudaMemcpyAsync(c.h_hist, d_hist, size_t(lo.levels) * RADIX * 8, cudaMemcpyDeviceToHost, st));
+    CUDA_TRY(cudaEventRecord(c.ev[1], st));
+    CUDA_TRY(cudaStreamSynchronize(st));
+
+    // levels with a single non-empty bucket are exact no-ops for a stable LSD sort
+    std::vector<uint32_t> active;
+    for (uint32_t l = 0; l < lo.levels; ++l) {
+        bool single = false;
+        for (int b = 0; b < RADIX; ++b)
+            if (c.h_hist[l * RADIX + b] == n) single = true;
+        if (!single) active.push_back(l);
+    }
+
+    PassPlan pp{};
+    rc = plan_pass(c, lo, n, data, tmp, false, variant, &pp);
+    if (rc) return rc;
+    void* src = data;
+    void* dst = tmp;
+    if (!active.empty()) {
+        const size_t lb_bytes = size_t(pp.num_tiles) * RADIX * 8;
+        rc = ensure_bytes(reinterpret_cast<void**>(&c.d_lookback), &c.lookback_bytes, lb_bytes);
+        if (rc) return rc;
+        CUDA_TRY(cudaMemsetAsync(c.d_lookback, 0, lb_bytes, st));
+        CUDA_TRY(cudaMemsetAsync(d_ticket, 0, 1024, st));
+    }
+    uint32_t pass = 0;
+    for (uint32_t l : active) {
+        rc = launch_pass(c, st, pp, lo, src, dst, n, l, reinterpret_cast<const uint64_t*>(d_base + size_t(l) * RADIX),
+                         d_ticket + pass, pass + 1, nullptr);
+        if (rc) return rc;
+        std::swap(src, dst);
+        ++pass;
+    }
+    uint32_t copy_back = 0;
+    if (src != data && !result_anywhere) {
+        CUDA_TRY(cudaMemcpyAsync(data, src, n * lo.elem_size, cudaMemcpyDeviceToDevice, st));
+        copy_back = 1;
+        src = data;
+    }
+    if (result_ptr) *result_ptr = src;
+    CUDA_TRY(cudaEventRecord(c.ev[2], st));
+    CUDA_TRY(cudaStreamSynchronize(st));
+    if (stats) {
+        stats->levels_run = pass;
+        stats->levels_skipped = lo.levels - pass;
+        stats->variant = uint32_t(pp.variant);
+        stats->copy_back = copy_back;
+        stats->algorithmic_bytes = n * lo.elem_size * (1ull + 2ull * pass) + (copy_back ? 2ull * n * lo.elem_size : 0);
+        CUDA_TRY(cudaEventElapsedTime(&stats->ms_hist, c.ev[0], c.ev[1]));
+        CUDA_TRY(cudaEventElapsedTime(&stats->ms_passes, c.ev[1], c.ev[2]));
+        CUDA_TRY(cudaEventElapsedTime(&stats->ms_total, c.ev[0], c.ev[2]));
+        stats->tiles_per_pass = pp.num_tiles;
+    }
+    return B200_OK;
+}
+
+struct DeviceGuard {
+    int prev = -1;
+    explicit DeviceGuard(int dev) {
+        cudaGetDevice(&prev);
+        if (prev != dev) cudaSetDevice(dev);
+    }
+    ~DeviceGuard() {
+        if (prev >= 0) cudaSetDevice(prev);
+    }
+};
+
+}  // namespace
+
+// ===========================================================================
+// C ABI
+// ===========================================================================
+extern "C" {
+
+int b200_sort_device(void* dev_ptr, void* dev_tmp, size_t n, const b200_key_desc* desc, const b200_sort_opts* opts,
+                     b200_stats* stats) {
+    Lowered lo;
+    int rc = lower_desc(desc, &lo);
+    if (rc) return rc;
+    if (stats) memset(stats, 0, sizeof(*stats));
+    if (n <= 1) return B200_OK;  // reference src/radix_sort_builder.rs:151
+    if (!dev_ptr) return B200_ERR_BAD_ARG;
+    DeviceCtx* c = nullptr;
+    rc = get_ctx(opts ? opts->device : -1, &c);
+    if (rc) return rc;
+    std::lock_guard<std::mutex> lk(c->mu);
+    DeviceGuard guard(c->dev);
+    cudaStream_t st = (opts && opts->stream) ? static_cast<cudaStream_t>(opts->stream) : c->stream;
+    void* tmp = dev_tmp;
+    if (!tmp) {
+        rc = ensure_bytes(&c->d_tmp, &c->tmp_bytes, n * lo.elem_size);
+        if (rc) return rc;
+        tmp = c->d_tmp;
+    }
+    return sort_device_impl(*c, st, dev_ptr, tmp, n, lo, opts ? opts->variant : -1, false, nullptr, stats);
+}
+
+int b200_sort_host(void* host_ptr, size_t n, const b200_key_desc* desc, const b200_sort_opts* opts,
+                   b200_stats* stats) {
+    Lowered lo;
+    int rc = lower_desc(desc, &lo);
+    if (rc) return rc;
+    if (stats) memset(stats, 0, sizeof(*stats));
+    if (n <= 1) return B200_OK;
+    if (!host_ptr) return B200_ERR_BAD_ARG;
+    DeviceCtx* c = nullptr;
+    rc = get_ctx(opts ? opts->device : -1, &c);
+    if (rc) return rc;
+    std::lock_guard<std::mutex> lk(c->mu);
+    DeviceGuard guard(c->dev);
+    cudaStream_t st = (opts && opts->stream) ? static_cast<cudaStream_t>(opts->stream) : c->stream;
+    const size_t bytes = n * lo.elem_size;
+    rc = ensure_bytes(&c->d_stage, &c->stage_bytes, bytes);
+    if (rc) return rc;
+    rc = ensure_bytes(&c->d_tmp, &c->tmp_bytes, bytes);
+    if (rc) return rc;
+
+    cudaPointerAttributes attr;
+    bool pinned = false;
+    if (cudaPointerGetAttributes(&attr, host_ptr) == cudaSuccess) {
+        pinned = attr.type == cudaMemoryTypeHost || attr.type == cudaMemoryTypeManaged;
+    } else {
+        cudaGetLastError();
+    }
+    constexpr size_t CHUNK = size_t(64) << 20;
+    if (!pinned && !c->h_bounce[0]) {
+        for (int i = 0; i < 2; ++i) CUDA_TRY(cudaMallocHost(&c->h_bounce[i], CHUNK));
+        c->bounce_bytes = CHUNK;
+    }
+
+    CUDA_TRY(cudaEventRecord(c->ev[3], st));
+    if (pinned) {
+        CUDA_TRY(cudaMemcpyAsync(c->d_stage, host_ptr, bytes, cudaMemcpyHostToDevice, st));
+    } else {
+        // pageable memory: stage through two pinned bounce buffers so the DMA of
+        // chunk i overlaps the host memcpy of chunk i+1
+        size_t off = 0;
+        int k = 0;
+        while (off < bytes) {
+            const size_t len = std::min(CHUNK, bytes - off);
+            CUDA_TRY(cudaEventSynchronize(c->bounce_ev[k]));
+            memcpy(c->h_bounce[k], static_cast<const uint8_t*>(host_ptr) + off, len);
+            CUDA_TRY(cudaMemcpyAsync(static_cast<uint8_t*>(c->d_stage) + off, c->h_bounce[k], len,
+                                     cudaMemcpyHostToDevice, st));
+            CUDA_TRY(cudaEventRecord(c->bounce_ev[k], st));
+            off += len;
+            k ^= 1;
+        }
+    }
+    CUDA_TRY(cudaEventRecord(c->ev[4], st));
+    void* result = nullptr;
+    b200_stats local{};
+    rc = sort_device_impl(*c, st, c->d_stage, c->d_tmp, n, lo, opts ? opts->variant : -1, true, &result, &local);
+    if (rc) return rc;
+    CUDA_TRY(cudaEventRecord(c->ev[5], st));
+    if (pinned) {
+        CUDA_TRY(cudaMemcpyAsync(host_ptr, result, bytes, cudaMemcpyDeviceToHost, st));
+    } else {
+        size_t off = 0;
+        int k = 0;
+        size_t pend_off[2] = {0, 0}, pend_len[2] = {0, 0};
+        while (off < bytes || pend_len[0] || pend_len[1]) {
+            if (pend_len[k]) {
+                CUDA_TRY(cudaEventSynchronize(c->bounce_ev[k]));
+                memcpy(static_cast<uint8_t*>(host_ptr) + pend_off[k], c->h_bounce[k], pend_len[k]);
+                pend_len[k] = 0;
+            }
+            if (off < bytes) {
+                const size_t len = std::min(CHUNK, bytes - off);
+                CUDA_TRY(cudaMemcpyAsync(c->h_bounce[k], static_cast<const uint8_t*>(result) + off, len,
+                                         cudaMemcpyDeviceToHost, st));
+                CUDA_TRY(cudaEventRecord(c->bounce_ev[k], st));
+                pend_off[k] = off;
+                pend_len[k] = len;
+                off += len;
+            }
+            k ^= 1;
+        }
+    }
+    CUDA_TRY(cudaEventRecord(c->ev[6], st));
+    CUDA_TRY(cudaStreamSynchronize(st));
+    if (stats) {
+        *stats = local;
+        CUDA_TRY(cudaEventElapsedTime(&stats->ms_h2d, c->ev[3], c->ev[4]));
+        CUDA_TRY(cudaEventElapsedTime(&stats->ms_d2h, c->ev[5], c->ev[6]));
+        CUDA_TRY(cudaEventElapsedTime(&stats->ms_total, c->ev[3], c->ev[6]));
+    }
+    return B200_OK;
+}
+
+int b200_histogram_device(const void* dev_ptr, size_t n, const b200_key_desc* desc, const b200_sort_opts* opts,
+                          uint64_t* hist_out) {
+    Lowered lo;
+    int rc = lower_desc(desc, &lo);
+    if (rc) return rc;
+    if (!hist_out) return B200_ERR_BAD_ARG;
+    memset(hist_out, 0, size_t(lo.levels) * RADIX * 8);
+    if (n == 0) return B200_OK;
+    if (!dev_ptr) return B200_ERR_BAD_ARG;
+    DeviceCtx* c = nullptr;
+    rc = get_ctx(opts ? opts->device : -1, &c);
+    if (rc) return rc;
+    std::lock_guard<std::mutex> lk(c->mu);
+    DeviceGuard guard(c->dev);
+    cudaStream_t st = (opts && opts->stream) ? static_cast<cudaStream_t>(opts->stream) : c->stream;
+    unsigned long long* d_hist = reinterpret_cast<unsigned long long*>(c->d_small + SMALL_HIST_OFF);
+    rc = launch_histogram(*c, st, lo, dev_ptr, n, d_hist);
+    if (rc) return rc;
+    CUDA_TRY(cudaMemcpyAsync(c->h_hist, d_hist, size_t(lo.levels) * RADIX * 8, cudaMemcpyDeviceToHost, st));
+    CUDA_TRY(cudaStreamSynchronize(st));
+    memcpy(hist_out, c->h_hist, size_t(lo.levels) * RADIX * 8);
+    return B200_OK;
+}
+
+static int pass_common(const void* dev_src, void* dev_dst, size_t n, const b200_key_desc* desc, uint32_t level,
+                       const uint64_t* counts, const uint32_t* split, uint32_t parts, uint64_t* part_counts_out,
+                       const b200_sort_opts* opts) {
+    Lowered lo;
+    int rc = lower_desc(desc, &lo);
+    if (rc) return rc;
+    if (level >= lo.levels) return B200_ERR_LEVEL_RANGE;
+    if (!counts) return B200_ERR_BAD_ARG;
+    const bool remap = split != nullptr;
+    if (remap && (parts == 0 || parts > RADIX)) return B200_ERR_BAD_ARG;
+    uint64_t total = 0;
+    for (int b = 0; b < RADIX; ++b) total += counts[b];
+    if (total != n) return B200_ERR_BAD_ARG;
+    // bucket bases; with a split table digits are first mapped to their part
+    uint8_t h_remap[RADIX];
+    uint64_t h_base[RADIX];
+    if (remap) {
+        uint64_t pc[RADIX] = {0};
+        for (int b = 0; b < RADIX; ++b) {
+            uint32_t part = 0;
+            while (part + 1 < parts && uint32_t(b) >= split[part]) ++part;
+            h_remap[b] = uint8_t(part);
+            pc[part] += counts[b];
+        }
+        uint64_t run = 0;
+        for (int q = 0; q < RADIX; ++q) {
+            h_base[q] = run;
+            run += pc[q];
+        }
+        if (part_counts_out)
+            for (uint32_t q = 0; q < parts; ++q) part_counts_out[q] = pc[q];
+    } else {
+        uint64_t run = 0;
+        for (int b = 0; b < RADIX; ++b) {
+            h_base[b] = run;
+            run += counts[b];
+        }
+    }
+    if (n == 0) return B200_OK;
+    if (!dev_src || !dev_dst) return B200_ERR_BAD_ARG;
+    DeviceCtx* c = nullptr;
+    rc = get_ctx(opts ? opts->device : -1, &c);
+    if (rc) return rc;
+    std::lock_guard<std::mutex> lk(c->mu);
+    DeviceGuard guard(c->dev);
+    cudaStream_t st = (opts && opts->stream) ? static_cast<cudaStream_t>(opts->stream) : c->stream;
+    PassPlan pp{};
+    rc = plan_pass(*c, lo, n, dev_src, dev_dst, remap, opts ? opts->variant : -1, &pp);
+    if (rc) return rc;
+    const size_t lb_bytes = size_t(pp.num_tiles) * RADIX * 8;
+    rc = ensure_bytes(reinterpret_cast<void**>(&c->d_lookback), &c->lookback_bytes, lb_bytes);
+    if (rc) return rc;
+    uint64_t* d_pbase = reinterpret_cast<uint64_t*>(c->d_small + SMALL_PBASE_OFF);
+    uint8_t* d_remap = c->d_small + SMALL_REMAP_OFF;
+    uint32_t* d_ticket = reinterpret_cast<uint32_t*>(c->d_small + SMALL_TICKET_OFF);
+    CUDA_TRY(cudaMemsetAsync(c->d_lookback, 0, lb_bytes, st));
+    CUDA_TRY(cudaMemsetAsync(d_ticket, 0, 1024, st));
+    CUDA_TRY(cudaMemcpyAsync(d_pbase, h_base, sizeof(h_base), cudaMemcpyHostToDevice, st));
+    if (remap) CUDA_TRY(cudaMemcpyAsync(d_remap, h_remap, sizeof(h_remap), cudaMemcpyHostToDevice, st));
+    rc = launch_pass(*c, st, pp, lo, dev_src, dev_dst, n, level, d_pbase, d_ticket, 1, remap ? d_remap : nullptr);
+    if (rc) return rc;
+    CUDA_TRY(cudaStreamSynchronize(st));
+    return B200_OK;
+}
+
+int b200_pass_device(const void* dev_src, void* dev_dst, size_t n, const b200_key_desc* desc, uint32_t level,
+                     const uint64_t* counts, const b200_sort_opts* opts) {
+    return pass_common(dev_src, dev_dst, n, desc, level, counts, nullptr, 0, nullptr, opts);
+}
+
+int b200_partition_device(const void* dev_src, void* dev_dst, size_t n, const b200_key_desc* desc, uint32_t level,
+                          const uint64_t* counts, const uint32_t* split, uint32_t parts, uint64_t* part_counts_out,
+                          const b200_sort_opts* opts) {
+    if (!split && parts > 1) return B200_ERR_BAD_ARG;
+    static const uint32_t none[1] = {256};
+    return pass_common(dev_src, dev_dst, n, desc, level, counts, split ? split : none, parts ? parts : 1,
+                       part_counts_out, opts);
+}
+
+int b200_get_level(const void* record, const b200_key_desc* desc, uint32_t level) {
+    Lowered lo;
+    int rc = lower_desc(desc, &lo);
+    if (rc) return -rc;
+    if (!record) return -B200_ERR_BAD_ARG;
+    if (level >= lo.levels) return -B200_ERR_LEVEL_RANGE;  // reference src/radix_key.rs:18
+    return int(host_digit(static_cast<const uint8_t*>(record), lo, level));
+}
+
+int b200_host_alloc(void** out, size_t bytes) {
+    if (!out) return B200_ERR_BAD_ARG;
+    CUDA_TRY(cudaMallocHost(out, bytes ? bytes : 1));
+    return B200_OK;
+}
+int b200_host_free(void* p) {
+    if (p) CUDA_TRY(cudaFreeHost(p));
+    return B200_OK;
+}
+
+int b200_release_scratch(int device) {
+    DeviceCtx* c = nullptr;
+    int rc = get_ctx(device, &c);
+    if (rc) return rc;
+    std::lock_guard<std::mutex> lk(c->mu);
+    DeviceGuard guard(c->dev);
+    void** ptrs[] = {&c->d_tmp, reinterpret_cast<void**>(&c->d_lookback), &c->d_stage};
+    size_t* sizes[] = {&c->tmp_bytes, &c->lookback_bytes, &c->stage_bytes};
+    for (int i = 0; i < 3; ++i) {
+        if (*ptrs[i]) cudaFree(*ptrs[i]);
+        *ptrs[i] = nullptr;
+        *sizes[i] = 0;
+    }
+    return B200_OK;
+}
+
+int b200_variant_count(void) { return NUM_VARIANTS; }
+const char* b200_variant_name(int variant) {
+    if (variant < 0 || variant >= NUM_VARIANTS) return nullptr;
+    return kVariants[variant].name;
+}
+
+const char* b200_strerror(int code) {
+    switch (code) {
+        case B200_OK: return "ok";
+        case B200_ERR_LEVELS_ZERO: return "RadixKey::LEVELS is zero";
+        case B200_ERR_BAD_DESC: return "inconsistent key descriptor";
+        case B200_ERR_CUDA: return "CUDA runtime error";
+        case B200_ERR_NO_DEVICE: return "no usable sm_100 device";
+        case B200_ERR_ALLOC: return "device scratch allocation failed";
+        case B200_ERR_BAD_ARG: return "bad argument";
+        case B200_ERR_LEVEL_RANGE: return "level >= LEVELS";
+    }
+    return "unknown error";
+}
+const char* b200_last_cuda_error(void) { return g_last_cuda_error.c_str(); }
+const char* b200_version(void) { return "b200sort 0.1.0 (sm_100a)"; }
+
+}  // extern "C"

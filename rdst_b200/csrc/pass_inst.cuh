@@ -1,0 +1,48 @@
+// pass_inst.cuh — instantiates the K2 pass kernel for one record width (WORDS)
+// over every variant; included by pass_w{1,2,3,4}.cu so the widths compile in
+// parallel.
+#pragma once
+#include "onesweep.cuh"
+#include "variants.h"
+#include "launch.h"
+
+namespace b200 {
+
+template <int WORDS, bool FLOATK, bool REMAP, int V>
+static PassLaunch make_launch() {
+    constexpr VariantInfo vi = kVariants[V];
+    constexpr int ITEMS = vi.items[WORDS - 1];
+    using SM = PassSmem<WORDS, vi.threads, ITEMS, vi.tma>;
+    PassLaunch pl;
+    pl.kernel = &onesweep_pass_kernel<WORDS, vi.threads, ITEMS, FLOATK, vi.tma, vi.match_hw, REMAP, vi.min_blocks>;
+    pl.smem = SM::TOTAL;
+    pl.tile = SM::TILE;
+    pl.threads = vi.threads;
+    return pl;
+}
+
+template <int WORDS, bool FLOATK, bool REMAP>
+static PassLaunch pick_launch(int v) {
+    switch (v) {
+        case 0: return make_launch<WORDS, FLOATK, REMAP, 0>();
+        case 1: return make_launch<WORDS, FLOATK, REMAP, 1>();
+        case 2: return make_launch<WORDS, FLOATK, REMAP, 2>();
+        case 3: return make_launch<WORDS, FLOATK, REMAP, 3>();
+        case 4: return make_launch<WORDS, FLOATK, REMAP, 4>();
+        case 5: return make_launch<WORDS, FLOATK, REMAP, 5>();
+        default: break;
+    }
+    PassLaunch none{};
+    return none;
+}
+
+template <int WORDS>
+static PassLaunch pick_launch_w(bool floatk, bool remap, int v) {
+    if (remap) {
+        // the range-partition pass exists in variant 0 only
+        return floatk ? make_launch<WORDS, true, true, 0>() : make_launch<WORDS, false, true, 0>();
+    }
+    return floatk ? pick_launch<WORDS, true, false>(v) : pick_launch<WORDS, false, false>(v);
+}
+
+}  // namespace b200

@@ -1,0 +1,4 @@
+#include "pass_inst.cuh"
+namespace b200 {
+PassLaunch get_pass_launch_w2(bool floatk, bool remap, int variant) { return pick_launch_w<2>(floatk, remap, variant); }
+}  // namespace b200

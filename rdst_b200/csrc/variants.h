@@ -1,0 +1,29 @@
+// variants.h — the tile / occupancy variants of the K2 pass kernel.  In the
+// reference the Tuner picks one of nine CPU algorithms per chunk
+// (reference src/tuner.rs:10-35, src/tuners/standard_tuner.rs:10-64); here the
+// only remaining choice is which tile shape of the one GPU pass kernel to run.
+#pragma once
+
+namespace b200 {
+
+struct VariantInfo {
+    const char* name;
+    int threads;
+    int items[4];  // records per thread for WORDS = 1, 2, 3, 4
+    bool tma;      // stage tiles with bulk asynchronous copies (persistent, prefetching)
+    bool match_hw; // MATCH.ANY instead of eight ballots
+    int min_blocks;
+};
+
+constexpr int NUM_VARIANTS = 6;
+
+constexpr VariantInfo kVariants[NUM_VARIANTS] = {
+    {"t512_ldg", 512, {16, 16, 12, 8}, false, false, 1},
+    {"t512_tma", 512, {24, 16, 12, 8}, true, false, 1},
+    {"t256_tma_occ", 256, {16, 16, 12, 8}, true, false, 2},
+    {"t256_ldg_occ", 256, {16, 16, 12, 8}, false, false, 2},
+    {"t512_tma_matchhw", 512, {24, 16, 12, 8}, true, true, 1},
+    {"t1024_tma", 1024, {12, 8, 6, 4}, true, false, 1},
+};
+
+}  // namespace b200
