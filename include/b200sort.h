@@ -82,7 +82,8 @@ typedef struct {
     uint32_t stable;   /* 1 = rdst's stable order (Lsb/LrLsb/MtLsb, src/sorts/lsb_sort.rs:5-7).
                           0 = any sorted permutation is legal (default tuner). The engine is a
                           stable LSD sort either way; the flag is recorded for the tuner. */
-    int32_t variant;   /* -1 = let the tuner pick; else index < b200_variant_count() */
+    int32_t variant;   /* < 0 = let the tuner pick (-2: prefer the low-scratch variant);
+                          else index < b200_variant_count() */
     int32_t device;    /* CUDA device ordinal; -1 = current device */
     void* stream;      /* cudaStream_t to order the work on; NULL = the library's own stream */
 } b200_sort_opts;
@@ -99,6 +100,8 @@ typedef struct {
     float ms_h2d, ms_d2h;      /* host entry point only */
     float ms_total;            /* first launch to last completion */
     uint64_t tiles_per_pass;
+    uint32_t already_sorted;   /* reserved (rdst's already_sorted shortcut, src/sorter.rs:59-65) */
+    uint32_t kernel_launches;  /* kernels of this library launched by the call */
 } b200_stats;
 
 /*

@@ -459,6 +459,7 @@ int sort_device_impl(DeviceCtx& c, cudaStream_t st, void* data, void* tmp, uint6
         CUDA_TRY(cudaEventElapsedTime(&stats->ms_passes, c.ev[1], c.ev[2]));
         CUDA_TRY(cudaEventElapsedTime(&stats->ms_total, c.ev[0], c.ev[2]));
         stats->tiles_per_pass = pp.num_tiles;
+        stats->kernel_launches = 2 + pass;  // K1 + scan + one K2 per executed level
     }
     return B200_OK;
 }
