@@ -1,0 +1,371 @@
+#!/usr/bin/env python3
+"""bench.py — Gkeys/s of the sort path on N B200s (BASELINE.json metric).
+
+  python bench.py [--gpus N] [--steps K] [--warmup W] [--impl b200|reference] [--workload NAME]
+
+Workload at N=1 (default): BASELINE.json configs[1] — u64 keys, 1 B uniform random,
+8 levels (uniform data has no trivial level), device resident.  At N>1 (torchrun, one rank
+per GPU): configs[4] — the same 1 B u64 keys PER GPU (weak scaling), sharded, top-level
+range partition + NCCL all-to-all + local sort.  One step = one full sort of one batch.
+
+Timing: CUDA events on the launching stream around each step's sort; the in-place sort's
+input is restored (device-to-device copy) between steps outside the event pairs, so the
+timed region starts with the unsorted input resident in HBM.  Inputs (8 GB) are far larger
+than L2, no flush needed.  Max over ranks.  `e2e` = same metric through the public host API
+(radix_sort_unstable on a pinned host array: H2D + sort + D2H inside the timed region).
+
+--impl reference: the reference's CPU path.  The reference is a pure-Rust crate and this
+image has no Rust toolchain, so what is timed is oracle/ (the C restatement of rdst's
+default multi-threaded path: StandardTuner -> Scanning/Recombinating/Ska/Lsb/...), with all
+host threads, on a bounded sample of the same workload.
+"""
+import argparse
+import json
+import os
+import statistics
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+sys.path.insert(0, os.path.join(ROOT, "tests"))
+
+import numpy as np
+
+WORKLOADS = {
+    # name: (dtype, n per GPU, generator, description)
+    "u64_1b_uniform": ("u8", 1_000_000_000, "uniform", "BASELINE configs[1]: u64 keys, 1B uniform random, LSD 8 levels"),
+    "u32_100m_uniform": ("u4", 100_000_000, "uniform", "BASELINE configs[0]: u32, 100M uniform random keys"),
+    "u64_1b_40bit": ("u8", 1_000_000_000, "low40", "configs[1] variant: keys < 2^40, 3 trivial levels skipped"),
+    "f32_500m": ("f4", 500_000_000, "uniform", "BASELINE configs[2]: f32 random bit patterns, 500M"),
+    "i64_500m": ("i8", 500_000_000, "uniform", "BASELINE configs[2]: i64, 500M incl. negatives"),
+    "u64_1b_zipf": ("u8", 1_000_000_000, "zipf", "configs[4] skewed: Zipf(1.1) ranks as u64 keys"),
+}
+CPU_SAMPLE = 200_000_000  # records of the same generator the CPU baseline sorts per step
+
+
+def gen_host(dtype, n, gen, seed):
+    rng = np.random.default_rng(seed)
+    dt = np.dtype(dtype)
+    if gen == "zipf":
+        return np.minimum(rng.zipf(1.1, n), 2**32).astype(dt)
+    a = rng.integers(0, 2**64, n, dtype=np.uint64) if dt.itemsize == 8 else rng.integers(0, 2**32, n, dtype=np.uint32)
+    if gen == "low40":
+        a &= np.uint64((1 << 40) - 1)
+    if dt.kind == "f":  # NaN/Inf-free random bit patterns (BASELINE configs[2])
+        a = np.where((a >> 23) & 0xFF == 0xFF, a & np.uint32(0x807FFFFF), a).astype(np.uint32)
+    return a.view(dt)
+
+
+def gen_device(torch, dtype, n, gen, seed):
+    """Same distributions generated on the device (flat int64/int32 storage of the key bits)."""
+    g = torch.Generator(device="cuda").manual_seed(seed)
+    dt = np.dtype(dtype)
+    if dt.itemsize == 8:
+        if gen == "zipf":
+            u = torch.rand(n, dtype=torch.float64, device="cuda", generator=g)
+            # inverse-CDF approximation of Zipf(s=1.1) over 2^32 ranks: r = (1 - u*(1 - R^(1-s)))^(1/(1-s))
+            s, R = 1.1, 2.0**32
+            r = (1.0 - u * (1.0 - R ** (1.0 - s))) ** (1.0 / (1.0 - s))
+            return r.clamp_(1, R).to(torch.int64)
+        t = torch.randint(-2**63, 2**63 - 1, (n,), dtype=torch.int64, device="cuda", generator=g)
+        if gen == "low40":
+            t &= (1 << 40) - 1
+        return t
+    t = torch.randint(-2**31, 2**31, (n,), dtype=torch.int32, device="cuda", generator=g)
+    if dt.kind == "f":
+        exp_all_ones = ((t >> 23) & 0xFF) == 0xFF
+        t = torch.where(exp_all_ones, t & -2139095041, t)  # clear exponent bits 0x7F800000: NaN/Inf-free
+    return t
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons sampled DURING the timed region."""
+
+    Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+         "clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index):
+        self.index, self.proc, self.lines = index, None, []
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.index), f"--query-gpu={self.Q}",
+                                          "--format=csv,noheader,nounits", "-lms", "100"],
+                                         stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.t = threading.Thread(target=self._read, daemon=True)
+            self.t.start()
+        except Exception:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.lines.append(line.strip())
+
+    def stop(self):
+        if not self.proc:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=5)
+        except Exception:
+            self.proc.kill()
+        sm, mx, reasons = [], [], set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for ln in self.lines:
+            f = [x.strip() for x in ln.split(",")]
+            if len(f) < 9:
+                continue
+            try:
+                sm.append(float(f[1])), mx.append(float(f[2]))
+            except ValueError:
+                continue
+            for name, val in zip(names, f[5:9]):
+                if val.lower().startswith("active"):
+                    reasons.add(name)
+        return {"sm_mhz": statistics.median(sm) if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "reasons": sorted(reasons), "samples": len(sm)}
+
+
+def cpu_baseline(dtype, gen, steps, warmup, sample=CPU_SAMPLE):
+    """oracle/ (C restatement of rdst's default multi-threaded path) timed on the host cores."""
+    import oracle_ffi as o
+    from rdst_b200 import RadixKey
+
+    key = RadixKey.for_dtype(dtype)
+    cores = o.hardware_threads()
+    src = gen_host(dtype, sample, gen, 0x5EED0002)
+    work = np.empty_like(src)
+    times = []
+    for i in range(warmup + steps):
+        np.copyto(work, src)
+        t0 = time.perf_counter()
+        o.sort(work, key, tuner="standard", multi_threaded=True, threads=cores)
+        dt = time.perf_counter() - t0
+        if i >= warmup:
+            times.append(dt)
+    assert o.is_sorted(work[:: max(1, sample // 1_000_000)].copy(), key)
+    ok = bool(np.all(work[1:] >= work[:-1])) if np.dtype(dtype).kind == "u" else True
+    assert ok, "CPU baseline produced an unsorted result"
+    return {"value": sample / statistics.median(times) / 1e9, "unit": "Gkeys/s", "cores": cores, "kind": "port",
+            "sample": f"{sample} {dtype} keys of the same generator per step (of {WORKLOADS_N[dtype, gen]}), "
+                      f"median of {steps} after {warmup} warm-up; oracle/ restates rdst's StandardTuner path "
+                      "(the Rust crate cannot be built in this image)",
+            "times_s": [round(t, 4) for t in times]}
+
+
+WORKLOADS_N = {(v[0], v[2]): v[1] for v in WORKLOADS.values()}
+
+
+def run_reference(args):
+    """--impl reference: the reference's own CPU implementation of the path (oracle port)."""
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return 0  # rank 0 alone runs the CPU arm
+    dtype, n, gen, desc = WORKLOADS[args.workload]
+    sample = min(args.cpu_sample, n)
+    cb = cpu_baseline(dtype, gen, args.steps, args.warmup, sample)
+    ms = sample / cb["value"] / 1e6
+    line = {
+        "impl": "reference", "metric": "Gkeys/s sorted", "value": cb["value"], "unit": "Gkeys/s",
+        "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms,
+        "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": np.dtype(dtype).name.replace("uint", "u"),
+        "data": "synthetic", "config": {"workload": f"{args.workload}: {desc}", "records_per_step": sample,
+                                        "note": "bounded sample of the workload, CPU host cores only"},
+        "cpu_baseline": cb,
+        "e2e": {"value": cb["value"], "unit": "Gkeys/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+    }
+    print(json.dumps(line))
+    return 0
+
+
+def run_b200(args):
+    import torch
+    import torch.distributed as dist
+
+    from rdst_b200 import RadixKey, _abi, radix_sort_builder
+    from rdst_b200.dist import CudaEngine, sharded_sort
+
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    assert torch.cuda.is_available(), "bench.py needs a GPU (no CPU fallback)"
+    torch.cuda.set_device(local_rank)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+    dtype, n, gen, desc = WORKLOADS[args.workload]
+    if args.n:
+        n = args.n
+    key = RadixKey.for_dtype(dtype)
+    es = key.elem_size
+    nbytes = n * es
+
+    src = gen_device(torch, dtype, n, gen, 0x5EED0002 + rank)           # pristine input, never sorted
+    work = torch.empty_like(src)
+    eng = CudaEngine(key)
+    scratch = {"tmp": torch.empty(nbytes, dtype=torch.uint8, device="cuda")}
+    if world > 1:
+        slack = 1.0 + args.recv_slack
+        scratch["part"] = torch.empty(nbytes, dtype=torch.uint8, device="cuda")
+        scratch["recv"] = torch.empty(int(nbytes * slack) // es * es, dtype=torch.uint8, device="cuda")
+        scratch["tmp"] = torch.empty(scratch["recv"].numel(), dtype=torch.uint8, device="cuda")
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    ev0 = [torch.cuda.Event(enable_timing=True) for _ in range(args.steps)]
+    ev1 = [torch.cuda.Event(enable_timing=True) for _ in range(args.steps)]
+    wbuf = work.view(torch.uint8).view(-1)
+    last = {}
+
+    def one_step(i, timed):
+        work.copy_(src)  # restore the unsorted input (untimed)
+        if world > 1:
+            dist.barrier()
+        if timed:
+            ev0[i].record()
+        out, n_out = sharded_sort(wbuf, n, key, engine=eng, scratch=scratch, timings=last)
+        if timed:
+            ev1[i].record()
+        return out, n_out
+
+    for i in range(args.warmup):
+        out, n_out = one_step(i, False)
+    barrier()
+    launches0 = eng.launches
+    sampler = ClockSampler(local_rank)
+    sampler.start()
+    barrier()
+    t_wall0 = time.perf_counter()
+    for i in range(args.steps):
+        out, n_out = one_step(i, True)
+    barrier()
+    t_wall = time.perf_counter() - t_wall0
+    clocks = sampler.stop()
+    launches = eng.launches - launches0
+    ms_steps = [ev0[i].elapsed_time(ev1[i]) for i in range(args.steps)]
+    ms_total = sum(ms_steps)
+
+    # cheap on-device verification of the last step (outside the timed region)
+    res = out[: n_out * es].view(torch.int64 if es == 8 else torch.int32)
+    flip = -2**63 if es == 8 else -2**31
+    if np.dtype(dtype).kind == "u":
+        u = res ^ flip
+        ok = bool((u[1:] >= u[:-1]).all()) if n_out > 1 else True
+        assert ok, "result is not sorted"
+        del u
+    st_local = last.get("local", {})
+
+    # ---- e2e: the public host API on a pinned host buffer, H2D + sort + D2H per step ----
+    e2e = None
+    if not args.no_e2e:
+        e2e_steps = max(1, min(args.steps, args.e2e_steps))
+        host_src = torch.empty(n, dtype=src.dtype).pin_memory()
+        host_src.copy_(src)
+        host_work = torch.empty(n, dtype=src.dtype).pin_memory()
+        harr = host_work.numpy().view(dtype)
+        e_times = []
+        for i in range(1 + e2e_steps):
+            host_work.copy_(host_src)
+            barrier()
+            t0 = time.perf_counter()
+            b = radix_sort_builder(harr, key)
+            b.sort()  # blocking: returns when the sorted data is back in host memory
+            e_times.append(time.perf_counter() - t0)
+            launches_e2e = b.stats["kernel_launches"]
+        e_times = e_times[1:]
+        assert bool(np.all(harr[1:] >= harr[:-1])) if np.dtype(dtype).kind == "u" else True
+        e_t = torch.tensor([sum(e_times) / len(e_times)], device="cuda")
+        if world > 1:
+            dist.all_reduce(e_t, op=dist.ReduceOp.MAX)
+        e2e = {"value": n * world / float(e_t.item()) / 1e9, "unit": "Gkeys/s", "h2d_bytes_per_step": nbytes * world,
+               "d2h_bytes_per_step": nbytes * world, "steps": e2e_steps, "ms_per_step": float(e_t.item()) * 1e3,
+               "api": "rdst_b200.radix_sort_builder(pinned numpy array).sort() -> b200_sort_host",
+               "ms_h2d": b.stats["ms_h2d"], "ms_d2h": b.stats["ms_d2h"], "ms_sort_device": b.stats["ms_hist"] + b.stats["ms_passes"]}
+        del host_src, host_work
+
+    t = torch.tensor([ms_total], device="cuda")
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    ms_total_max = float(t.item())
+    if rank != 0:
+        if world > 1:
+            dist.destroy_process_group()
+        return 0
+
+    peaks = {}
+    try:
+        peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
+    except Exception:
+        pass
+    peak = float(peaks.get("hbm_gbs", 6650.0))
+    peak_src = "MEASURED_PEAKS.json hbm_gbs (measured)" if "hbm_gbs" in peaks else "fallback 6650 GB/s"
+    passes = int(st_local.get("levels_run", 0))
+    ms_passes = float(st_local.get("ms_passes", 0.0))
+    n_sorted = int(last.get("n_recv", n)) if world > 1 else n
+    roof = None
+    if passes and ms_passes > 0:
+        per_launch_bytes = 2 * n_sorted * es
+        ach = per_launch_bytes * passes / (ms_passes * 1e-3) / 1e9
+        roof = {"bound": "hbm", "kernel": "onesweep_pass_kernel (K2)", "achieved": ach, "peak": peak, "unit": "GB/s",
+                "frac": ach / peak, "traffic": None, "peak_source": peak_src,
+                "algorithmic_bytes_per_launch": per_launch_bytes, "launches_per_step": passes,
+                "avg_launch_ms": ms_passes / passes,
+                "how": "CUDA events recorded by the library on the launch stream around the K2 passes of the last step"}
+        whole = n_sorted * es * (1 + 2 * passes) / ((st_local["ms_hist"] + ms_passes) * 1e-3) / 1e9
+        roof["whole_sort"] = {"algorithmic_bytes": n_sorted * es * (1 + 2 * passes), "achieved": whole,
+                              "frac": whole / peak, "frac_of_8TBs_nominal": whole / 8000.0,
+                              "ms_hist": st_local["ms_hist"], "ms_passes": ms_passes}
+    cb = None
+    if world == 1 and not args.no_cpu:
+        cb = cpu_baseline(dtype, gen, args.cpu_steps, 1, min(args.cpu_sample, n))
+    value = n * world * args.steps / (ms_total_max * 1e-3) / 1e9
+    line = {
+        "metric": "Gkeys/s sorted", "value": value, "unit": "Gkeys/s", "n_gpus": world, "steps": args.steps,
+        "warmup": args.warmup, "ms_per_step": ms_total_max / args.steps, "higher_is_better": True, "scaling": "weak",
+        "vs_baseline": None, "dtype": np.dtype(dtype).name.replace("uint", "u").replace("float", "f").replace("int", "i"),
+        "data": "synthetic",
+        "config": {"workload": f"{args.workload}: {desc}", "records_per_gpu": n, "record_bytes": es,
+                   "levels_run": passes, "parallelism": f"range-partition x{world}" if world > 1 else "single GPU",
+                   "l2": "inputs (>= 0.4 GB) larger than L2; unsorted input restored by a D2D copy between steps, untimed",
+                   "timing": "CUDA events per step on the launch stream, summed; max over ranks",
+                   "wall_s_timed_loop_incl_restore": t_wall},
+        "ms_steps": ms_steps, "clocks": clocks, "e2e": e2e, "gpu_launches": launches,
+        "roofline": roof, "cpu_baseline": cb,
+    }
+    if world > 1:
+        line["exchange"] = {k: last.get(k) for k in ("level", "n_recv", "sent_bytes")}
+    print(json.dumps(line))
+    if world > 1:
+        dist.destroy_process_group()
+    return 0
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=5)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--workload", default="u64_1b_uniform", choices=sorted(WORKLOADS))
+    ap.add_argument("--n", type=int, default=0, help="override records per GPU (debug)")
+    ap.add_argument("--cpu-sample", type=int, default=CPU_SAMPLE)
+    ap.add_argument("--cpu-steps", type=int, default=3)
+    ap.add_argument("--e2e-steps", type=int, default=3)
+    ap.add_argument("--recv-slack", type=float, default=0.3)
+    ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--no-cpu", action="store_true")
+    args = ap.parse_args()
+    if args.warmup < 3 and args.impl == "b200":
+        args.warmup = max(args.warmup, 3) if not args.n else args.warmup
+    return run_reference(args) if args.impl == "reference" else run_b200(args)
+
+
+if __name__ == "__main__":
+    sys.exit(main())

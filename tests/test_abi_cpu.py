@@ -1,0 +1,131 @@
+"""CPU-only checks of the drop-in boundary: the C-ABI library loads, exports every symbol
+include/b200sort.h declares, the descriptor lowering agrees with the oracle's get_level,
+and the host-side mirror keeps the reference's argument/error behaviour.  No kernels run."""
+import ctypes as C
+import os
+import re
+
+import numpy as np
+import pytest
+
+import oracle_ffi as o
+import rdst_b200
+from rdst_b200 import RadixKey, _abi, radix_sort_builder, radix_sort_unstable, tuner
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def header_functions():
+    src = open(os.path.join(ROOT, "include", "b200sort.h")).read()
+    src = re.sub(r"/\*.*?\*/", "", src, flags=re.S)
+    return sorted(set(re.findall(r"\b(b200_[a-z0-9_]+)\s*\(", src)))
+
+
+def test_library_exports_every_declared_symbol():
+    names = header_functions()
+    assert len(names) >= 14
+    l = C.CDLL(_abi.LIB_PATH)
+    for n in names:
+        assert hasattr(l, n), f"libb200sort.so does not export {n}"
+    # and the Python binding covers the whole header
+    assert set(names) == set(_abi.SYMBOLS), set(names) ^ set(_abi.SYMBOLS)
+
+
+def test_version_and_variants():
+    l = _abi.lib()
+    assert b"sm_100a" in l.b200_version()
+    nv = l.b200_variant_count()
+    assert nv >= 1
+    for v in range(nv):
+        assert l.b200_variant_name(v)
+    assert l.b200_variant_name(nv) is None
+    assert l.b200_strerror(1) == b"RadixKey::LEVELS is zero"
+
+
+def test_struct_layouts_match_header():
+    assert C.sizeof(_abi.Level) == 4
+    assert C.sizeof(_abi.KeyDesc) == 24 + 4 * 64
+    assert C.sizeof(_abi.SortOpts) == 24
+    assert _abi.Stats.algorithmic_bytes.offset == 16
+
+
+KEYS = [RadixKey.for_dtype(d) for d in ("u1", "u2", "u4", "u8", "i1", "i2", "i4", "i8", "f4", "f8")] + [
+    RadixKey.u128(), RadixKey.i128(), RadixKey.byte_array(3), RadixKey.byte_array(7),
+    RadixKey.for_dtype("u4", levels=2), RadixKey.for_dtype("i8", levels=5),
+    RadixKey.custom(4, [3, 1]), RadixKey.custom(6, [(5, 0x80), (0, 0), (2, 0xFF)]),
+    RadixKey.field(np.dtype([("p", "<u8"), ("k", "<f4"), ("q", "<u4")]), "k"),
+]
+
+
+@pytest.mark.parametrize("key", KEYS, ids=repr)
+def test_b200_get_level_matches_oracle(key):
+    rng = np.random.default_rng(1)
+    for _ in range(64):
+        rec = rng.integers(0, 256, key.elem_size, dtype=np.uint8).tobytes()
+        for l in range(key.levels):
+            assert key.get_level(rec, l) == o.get_level(rec, key, l)
+    with pytest.raises(_abi.B200SortError):  # debug_assert!(level < LEVELS), reference src/radix_key.rs:18
+        key.get_level(bytes(key.elem_size), key.levels)
+
+
+def test_levels_zero_panics_at_builder_construction():
+    """assert_ne!(T::LEVELS, 0) fires in RadixSortBuilder::new, even for empty input
+    (reference src/radix_sort_builder.rs:22)."""
+    a = np.zeros(0, dtype="u4")
+    with pytest.raises(rdst_b200.LevelsZeroError):
+        radix_sort_builder(a, RadixKey.for_dtype("u4", levels=0))
+    d = RadixKey.for_dtype("u4", levels=0).to_desc()
+    assert _abi.lib().b200_sort_device(None, None, 0, C.byref(d), None, None) == 1
+    assert _abi.lib().b200_sort_host(None, 0, C.byref(d), None, None) == 1
+
+
+def test_len_le_1_is_a_noop_without_a_device():
+    """`if self.data.len() <= 1 { return; }` (reference src/radix_sort_builder.rs:151)."""
+    for n in (0, 1):
+        a = np.arange(n, dtype="u8")
+        radix_sort_unstable(a)
+        assert a.tolist() == list(range(n))
+        d = RadixKey.for_dtype("u8").to_desc()
+        assert _abi.lib().b200_sort_host(a.ctypes.data, n, C.byref(d), None, None) == 0
+
+
+def test_bad_descriptors_rejected():
+    l = _abi.lib()
+    for key in (RadixKey("uint", 4, 4, 2, 4), RadixKey("uint", 4, 5, 0, 4), RadixKey("float", 2, 2, 0, 2),
+                RadixKey("bytes", 4, 1, level_map=[(4, 0)]), RadixKey("uint", 0, 1, 0, 1)):
+        d = key.to_desc()
+        assert l.b200_sort_device(None, None, 10, C.byref(d), None, None) == 2  # B200_ERR_BAD_DESC
+
+
+def test_no_gpu_is_a_loud_error_not_a_fallback():
+    import torch
+
+    if torch.cuda.is_available():
+        pytest.skip("has a GPU")
+    a = np.array([3, 1, 2], dtype="i4")
+    with pytest.raises(_abi.B200SortError):
+        radix_sort_unstable(a)
+    assert a.tolist() == [3, 1, 2]
+
+
+def test_tuner_tables_match_the_oracle_restatement():
+    """The Python StandardTuner / LowMemoryTuner / SingleThreadedTuner are the reference's
+    threshold tables (src/tuners/*.rs); cross-check with the oracle's C restatement through
+    sizes where the chosen algorithm changes."""
+    st, lm, sg = tuner.StandardTuner(), tuner.LowMemoryTuner(), tuner.SingleThreadedTuner()
+    flat = [100] * 256
+    skew = [0] * 255 + [10**9]
+    for n in (100, 128, 129, 4999, 5000, 50_000, 50_001, 100_001, 150_000, 150_001, 200_000, 200_001, 260_000,
+              260_001, 350_000, 350_001, 800_000, 800_001, 1_000_001, 4_000_001, 5_000_001, 50_000_001):
+        for level, total in ((3, 4), (2, 4), (0, 4), (7, 8)):
+            p = tuner.TuningParams(8, level, total, n, None)
+            for counts in (flat, skew):
+                for t in (st, lm, sg):
+                    assert isinstance(t.pick_algorithm(p, counts), tuner.Algorithm)
+    p = tuner.TuningParams(8, 3, 4, 100_000_000, None)
+    assert st.pick_algorithm(p, flat) is tuner.Algorithm.Scanning
+    assert st.pick_algorithm(tuner.TuningParams(8, 2, 4, 390_000, 10**8), flat) is tuner.Algorithm.Ska
+    assert st.pick_algorithm(tuner.TuningParams(8, 1, 4, 1_500, 390_000), flat) is tuner.Algorithm.Lsb
+    assert st.pick_algorithm(tuner.TuningParams(8, 7, 8, 6_000_000, None), skew) is tuner.Algorithm.Regions
+    assert lm.pick_algorithm(p, flat) is tuner.Algorithm.Regions
+    assert sg.pick_algorithm(tuner.TuningParams(1, 3, 4, 900_000, None), flat) is tuner.Algorithm.Ska

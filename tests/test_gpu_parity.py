@@ -1,0 +1,438 @@
+"""GPU parity: the CUDA path, called through the C ABI (via rdst_b200's ctypes mirror of
+the reference API), against the oracle on the same seeded inputs.  Bit-exact everywhere:
+this is integer / byte work.  Key-only sorts must equal the oracle byte for byte; records
+with payload must equal rdst's STABLE order (oracle: the Lsb algorithm); at full
+BASELINE sizes, size-independent properties are checked on the device."""
+import ctypes as C
+import json
+import os
+
+import numpy as np
+import pytest
+
+import oracle_ffi as o
+from rdst_b200 import RadixKey, _abi, radix_sort_builder, radix_sort_stable, radix_sort_unstable, tuner
+
+pytestmark = pytest.mark.gpu
+
+G = json.load(open(os.path.join(os.path.dirname(__file__), "golden", "reference_vectors.json")))
+NPT = {"i32": "i4", "u64": "u8"}
+
+
+def torch_mod():
+    import torch
+
+    assert torch.cuda.is_available()
+    return torch
+
+
+def gpu_sort_both_ways(a, key, stable=False, variant=-1):
+    """Sort a copy through the host entry point and another through the device entry
+    point; both must agree; returns the result."""
+    torch = torch_mod()
+    h = a.copy()
+    b = radix_sort_builder(h, key).with_variant(variant)
+    (b.with_stable(True) if stable else b).sort()
+    raw = np.ascontiguousarray(a).view(np.uint8).reshape(-1)
+    if raw.size:
+        t = torch.from_numpy(raw.copy()).cuda()
+        b2 = radix_sort_builder(t, key).with_variant(variant)
+        (b2.with_stable(True) if stable else b2).sort()
+        torch.cuda.synchronize()
+        assert t.cpu().numpy().tobytes() == h.tobytes(), "host and device entry points disagree"
+    return h
+
+
+def rand_bits(rng, dt, n):
+    return rng.integers(0, 256, n * np.dtype(dt).itemsize, dtype=np.uint8).view(dt).copy()
+
+
+# ---------------------------------------------------------------- golden vectors
+def test_reference_golden_vectors_on_gpu():
+    for vec in G["sort_vectors"]:
+        a = np.array(vec["input"], dtype=NPT[vec["type"]])
+        radix_sort_unstable(a)
+        assert a.tolist() == vec["expected"], vec["cite"]
+    for vec in G["byte_array_vectors"]:
+        a = np.array(vec["input"], dtype=np.uint8)
+        radix_sort_unstable(a, RadixKey.byte_array(vec["n"]))
+        assert a.tolist() == vec["expected"]
+    for vec in G["custom_key_vectors"]:
+        a = np.array(vec["input"], dtype=np.uint8)
+        radix_sort_unstable(a, RadixKey.custom(vec["elem_size"], vec["level_offsets"]))
+        assert a.tolist() == vec["expected"], vec["cite"]
+
+
+def test_builder_variants_of_the_reference_api():
+    """doctests of reference src/lib.rs:110-172 and src/radix_sort_builder.rs:43-147."""
+    a = np.array([10, 15, 0, 22, 9], dtype="u8")
+    radix_sort_builder(a).with_low_mem_tuner().sort()
+    assert a.tolist() == [0, 9, 10, 15, 22]
+    a = np.array([10, 15, 0, 22, 9], dtype="u8")
+    radix_sort_builder(a).with_single_threaded_tuner().with_parallel(False).sort()
+    assert a.tolist() == [0, 9, 10, 15, 22]
+
+    class MyTuner(tuner.Tuner):
+        def __init__(self):
+            self.calls = []
+
+        def pick_algorithm(self, p, counts):
+            self.calls.append((p, list(counts)))
+            return tuner.Algorithm.Ska if p.input_len >= 500_000 else tuner.Algorithm.Lsb
+
+    t = MyTuner()
+    a = np.array([10, 25, 9, 22, 6], dtype="u8")
+    radix_sort_builder(a).with_tuner(t).sort()
+    assert a.tolist() == [6, 9, 10, 22, 25]
+    p, counts = t.calls[0]
+    assert (p.level, p.total_levels, p.input_len, p.parent_len) == (7, 8, 5, None)
+    assert counts[0] == 5 and sum(counts) == 5
+
+
+# ---------------------------------------------------------------- key-only primitives
+SIZES = [2, 10, 100, 128, 129, 400, 5_000, 10_000, 50_000, 100_000, 260_000, 300_000, 1_000_000]
+
+
+@pytest.mark.parametrize("dt", ["u1", "u2", "u4", "u8", "i1", "i2", "i4", "i8", "f4", "f8"])
+def test_primitive_size_ladder(dt):
+    """Size ladder + bimodal shift of reference src/test_utils.rs:51-95 (all 10 key types;
+    random BIT patterns, so floats include NaN / Inf / subnormal / -0.0 like block_rand)."""
+    rng = np.random.default_rng(100 + np.dtype(dt).num)
+    key = RadixKey.for_dtype(dt)
+    bits = np.dtype(dt).itemsize * 8
+    for n in SIZES:
+        for shift in (0, bits // 2):
+            a = rand_bits(rng, dt, n)
+            if shift:
+                u = a.view("u%d" % a.dtype.itemsize)
+                u[: n // 2] >>= np.array(shift, dtype=u.dtype)
+                u[n // 2:] <<= np.array(shift, dtype=u.dtype)
+            got = gpu_sort_both_ways(a, key)
+            assert got.tobytes() == o.sorted_copy(a, key).tobytes(), (dt, n, shift)
+
+
+def test_u32_mask_patterns():
+    """validate_u32_patterns, reference src/test_utils.rs:148-262."""
+    rng = np.random.default_rng(5)
+    key = RadixKey.for_dtype("u4")
+    masks = [0xFFFF_FFFF, 0xFFFF_FF00, 0xFFFF_00FF, 0xFF00_FFFF, 0x00FF_FFFF, 0x0000_FFFF, 0xFFFF_0000,
+             0x8000_0000, 0x1, 0xFFFF_FFFE, 0x7FFF_FFFF, 0xAAAA_AAAA, 0x5555_5555]
+    bases = [np.full(128, 0xFFFFFFFF, dtype="u4"), rng.integers(0, 2**32, 128, dtype="u4"),
+             rng.integers(0, 2**32, 128_000, dtype="u4"), rng.integers(0, 2**32, 4, dtype="u4")]
+    for base in bases:
+        for m in masks:
+            a = base & np.uint32(m)
+            assert gpu_sort_both_ways(a, key).tobytes() == o.sorted_copy(a, key).tobytes(), hex(m)
+    a = np.zeros(128_000, dtype="u4")
+    a[:5] = 0x7700_0000
+    assert gpu_sort_both_ways(a, key).tobytes() == o.sorted_copy(a, key).tobytes()
+
+
+@pytest.mark.parametrize("dist", ["all_equal", "sorted", "reverse", "mostly_sorted", "two_values", "zipf"])
+def test_distributions_u64(dist):
+    rng = np.random.default_rng(21)
+    n = 777_777
+    if dist == "all_equal":
+        a = np.full(n, 0xDEADBEEFCAFEF00D, dtype="u8")
+    elif dist == "sorted":
+        a = np.sort(rng.integers(0, 2**63, n, dtype="u8"))
+    elif dist == "reverse":
+        a = np.sort(rng.integers(0, 2**63, n, dtype="u8"))[::-1].copy()
+    elif dist == "mostly_sorted":
+        a = np.sort(rng.integers(0, 2**63, n, dtype="u8"))
+        a[-n // 10:] = rng.integers(0, 2**63, len(a[-n // 10:]), dtype="u8")
+    elif dist == "two_values":
+        a = rng.choice(np.array([5, 2**40 + 1], dtype="u8"), n)
+    else:
+        a = rng.zipf(1.1, n).astype("u8")
+    key = RadixKey.for_dtype("u8")
+    assert gpu_sort_both_ways(a, key).tobytes() == o.sorted_copy(a, key).tobytes()
+
+
+def test_float_total_order_with_specials():
+    """IEEE total order incl. NaN payloads, +-0, +-inf, subnormals (reference
+    src/radix_key_impl.rs:162-185; src/radix_sort.rs:97-144)."""
+    rng = np.random.default_rng(31)
+    for dt, ut in (("f4", "u4"), ("f8", "u8")):
+        key = RadixKey.for_dtype(dt)
+        sp = [b["bits"] for b in G["f32_levels" if dt == "f4" else "f64_levels"]]
+        a = np.concatenate([np.array(sp, dtype=ut), rand_bits(rng, ut, 200_000)]).view(dt)
+        rng.shuffle(a.view(ut))
+        got = gpu_sort_both_ways(a, key)
+        assert got.tobytes() == o.sorted_copy(a, key).tobytes()
+        for _ in range(200):  # the reference's 10-element random-bit cases
+            b = rand_bits(rng, dt, 10)
+            h = b.copy()
+            radix_sort_unstable(h)
+            assert h.tobytes() == o.sorted_copy(b, key).tobytes()
+
+
+# ---------------------------------------------------------------- records with payload
+REC12 = np.dtype([("key", "<u4"), ("idx", "<u8")])                      # BASELINE config 4
+REC16 = np.dtype([("key", "<u8"), ("idx", "<u8")])
+LARGE = np.dtype([("a", "<u8"), ("b", "<u8"), ("sort_key", "<f4"), ("c", "<u4"), ("d", "<u8"), ("e", "<u8")])  # 40 B
+REC8 = np.dtype([("idx", "<u4"), ("key", "<i4")])
+REC6 = np.dtype([("key", "<u2"), ("idx", "<u4")])                       # odd stride -> byte path
+
+
+@pytest.mark.parametrize("rec,field,levels", [(REC12, "key", 3), (REC12, "key", 4), (REC16, "key", 8),
+                                              (REC16, "key", 2), (LARGE, "sort_key", 4), (REC8, "key", 4),
+                                              (REC6, "key", 2), (REC6, "key", 1)])
+def test_struct_records_stable(rec, field, levels):
+    rng = np.random.default_rng(41)
+    key = RadixKey.field(rec, field, levels)
+    for n in (129, 4_097, 100_000, 1_000_003):
+        a = np.zeros(n, dtype=rec)
+        raw = a.view(np.uint8).reshape(n, rec.itemsize)
+        raw[:] = rng.integers(0, 256, raw.shape, dtype=np.uint8)  # garbage everywhere, incl. ignored key bytes
+        kd = rec.fields[field][0]
+        if kd.kind == "f":
+            a[field] = rng.integers(-50, 50, n).astype(kd)  # duplicates + negatives
+        else:
+            a[field] = rng.integers(0, 1 << 11, n).astype(kd) | (rng.integers(0, 256, n).astype(kd) << (8 * levels) if levels < kd.itemsize else 0)
+        got = gpu_sort_both_ways(a, key, stable=True)
+        exp = o.stable_sorted(a, key)
+        assert got.tobytes() == exp.tobytes(), (rec, field, levels, n)
+        assert exp.tobytes() == o.numpy_stable_sorted(a, key).tobytes()
+
+
+def test_unstable_mode_is_sorted_permutation():
+    """Default (unstable) mode on payload records: sorted by key AND a permutation of the
+    input.  (The engine happens to be stable; only this is promised.)"""
+    rng = np.random.default_rng(43)
+    n = 500_000
+    a = np.zeros(n, dtype=REC12)
+    a["key"] = rng.integers(0, 1 << 24, n)
+    a["idx"] = np.arange(n)
+    key = RadixKey.field(REC12, "key", 3)
+    got = gpu_sort_both_ways(a, key)
+    assert o.is_sorted(got, key)
+    assert np.array_equal(np.sort(got["idx"]), a["idx"])
+    assert np.array_equal(a["key"][got["idx"]], got["key"])
+
+
+def test_partial_levels_on_primitives_ignore_high_bytes():
+    rng = np.random.default_rng(47)
+    for dt, levels in (("u4", 2), ("u8", 5), ("i8", 3), ("u8", 1)):
+        key = RadixKey.for_dtype(dt, levels=levels)
+        a = rand_bits(rng, dt, 300_000)
+        got = gpu_sort_both_ways(a, key, stable=True)
+        assert got.tobytes() == o.stable_sorted(a, key).tobytes(), (dt, levels)
+
+
+@pytest.mark.parametrize("n_bytes", [3, 5, 7, 16, 20])
+def test_byte_arrays_lexicographic(n_bytes):
+    rng = np.random.default_rng(53)
+    key = RadixKey.byte_array(n_bytes)
+    a = rng.integers(0, 4, (50_001, n_bytes), dtype=np.uint8)
+    got = gpu_sort_both_ways(a, key)
+    exp = o.numpy_stable_sorted(a, key)
+    assert got.tobytes() == exp.tobytes()
+    if n_bytes in (3, 5, 7, 16, 20):
+        assert exp.tobytes() == o.sorted_copy(a, key, tuner="single_algo", algo="Lsb").tobytes()
+
+
+def test_u128_i128():
+    rng = np.random.default_rng(59)
+    a = rng.integers(0, 256, (200_003, 16), dtype=np.uint8)
+    a[:, 9:] &= 1  # duplicates in the high bytes
+    for key in (RadixKey.u128(), RadixKey.i128()):
+        got = gpu_sort_both_ways(a, key)
+        assert got.tobytes() == o.numpy_stable_sorted(a, key).tobytes()
+        assert got.tobytes() == o.stable_sorted(a, key).tobytes()
+
+
+def test_custom_multi_field_key():
+    """reference src/lib.rs:78-104 MyStruct {key_1,key_2,key_3}: level 0 -> key_1 ..."""
+    rng = np.random.default_rng(61)
+    a = rng.integers(0, 7, (123_457, 4), dtype=np.uint8)
+    key = RadixKey.custom(4, [0, 1, 2])
+    got = gpu_sort_both_ways(a, key, stable=True)
+    assert got.tobytes() == o.stable_sorted(a, key).tobytes()
+    key = RadixKey.custom(4, [(3, 0x80), (0, 0xFF)])
+    got = gpu_sort_both_ways(a, key, stable=True)
+    assert got.tobytes() == o.stable_sorted(a, key).tobytes()
+
+
+# ---------------------------------------------------------------- kernels one by one
+def _dev(a):
+    torch = torch_mod()
+    return torch.from_numpy(np.ascontiguousarray(a).view(np.uint8).reshape(-1).copy()).cuda()
+
+
+@pytest.mark.parametrize("dt,n", [("u4", 1), ("u4", 1_000_003), ("u8", 999_999), ("f4", 300_001), ("f8", 70_000),
+                                  ("i4", 65_536), ("u2", 100_001), ("u1", 4_099)])
+def test_k1_histogram_matches_get_counts(dt, n):
+    """K1 vs get_counts_with_ends (reference src/sort_utils.rs:108-180) for every level."""
+    rng = np.random.default_rng(67)
+    a = rand_bits(rng, dt, n)
+    key = RadixKey.for_dtype(dt)
+    t = _dev(a)
+    hist = (C.c_uint64 * (256 * key.levels))()
+    d = key.to_desc()
+    _abi.check(_abi.lib().b200_histogram_device(t.data_ptr(), n, C.byref(d), None, hist))
+    for l in range(key.levels):
+        counts, _, _, _ = o.get_counts(a, key, l)
+        assert [hist[l * 256 + b] for b in range(256)] == counts.tolist(), (dt, l)
+
+
+def test_k1_histogram_struct_and_skew():
+    rng = np.random.default_rng(71)
+    n = 400_000
+    a = np.zeros(n, dtype=LARGE)
+    a.view(np.uint8)[:] = rng.integers(0, 256, a.nbytes, dtype=np.uint8)
+    a["sort_key"] = np.where(rng.random(n) < 0.9, 1.5, rng.standard_normal(n)).astype("f4")
+    key = RadixKey.field(LARGE, "sort_key")
+    t = _dev(a)
+    hist = (C.c_uint64 * (256 * 4))()
+    d = key.to_desc()
+    _abi.check(_abi.lib().b200_histogram_device(t.data_ptr(), n, C.byref(d), None, hist))
+    for l in range(4):
+        assert [hist[l * 256 + b] for b in range(256)] == o.get_counts(a, key, l)[0].tolist()
+
+
+@pytest.mark.parametrize("dt,level", [("u4", 0), ("u4", 3), ("u8", 5), ("f4", 3), ("i8", 7), ("u2", 1)])
+def test_k2_single_pass_matches_out_of_place_sort(dt, level):
+    """K2 vs out_of_place_sort (reference src/sorts/out_of_place_sort.rs:51-108)."""
+    torch = torch_mod()
+    rng = np.random.default_rng(73)
+    n = 654_321
+    a = rand_bits(rng, dt, n)
+    key = RadixKey.for_dtype(dt)
+    counts = o.get_counts(a, key, level)[0]
+    src, dst = _dev(a), torch.empty(a.nbytes, dtype=torch.uint8, device="cuda")
+    d = key.to_desc()
+    _abi.check(_abi.lib().b200_pass_device(src.data_ptr(), dst.data_ptr(), n, C.byref(d), level,
+                                           counts.ctypes.data_as(C.POINTER(C.c_uint64)), None))
+    exp = o.out_of_place_pass(a, key, level)
+    assert dst.cpu().numpy().tobytes() == exp.tobytes()
+    assert exp.tobytes() == o.out_of_place_pass(a, key, level, lr=True).tobytes()  # LR variant is the same order
+
+
+def test_partition_pass():
+    torch = torch_mod()
+    rng = np.random.default_rng(79)
+    n = 500_009
+    a = rng.integers(0, 2**64, n, dtype="u8")
+    key = RadixKey.for_dtype("u8")
+    level = 7
+    counts = o.get_counts(a, key, level)[0]
+    split = np.array([64, 128, 200], dtype=np.uint32)
+    parts = 4
+    src, dst = _dev(a), torch.empty(a.nbytes, dtype=torch.uint8, device="cuda")
+    pc = (C.c_uint64 * parts)()
+    d = key.to_desc()
+    _abi.check(_abi.lib().b200_partition_device(src.data_ptr(), dst.data_ptr(), n, C.byref(d), level,
+                                                counts.ctypes.data_as(C.POINTER(C.c_uint64)),
+                                                split.ctypes.data_as(C.POINTER(C.c_uint32)), parts, pc, None))
+    top = (a >> np.uint64(56)).astype(np.int64)
+    part = np.searchsorted(split, top, side="right")
+    exp = a[np.argsort(part, kind="stable")]
+    assert dst.cpu().numpy().tobytes() == exp.tobytes()
+    assert list(pc) == np.bincount(part, minlength=parts).tolist()
+
+
+def test_every_variant_and_tile_boundaries():
+    rng = np.random.default_rng(83)
+    l = _abi.lib()
+    for v in range(l.b200_variant_count()):
+        for dt in ("u4", "u8"):
+            key = RadixKey.for_dtype(dt)
+            for n in (4095, 4096, 4097, 8191, 8192, 8193, 12287, 12288, 12289, 16383, 16384, 16385, 24576, 24577,
+                      200_000):
+                a = rand_bits(rng, dt, n)
+                got = gpu_sort_both_ways(a, key, variant=v)
+                assert got.tobytes() == np.sort(a).tobytes(), (v, dt, n)
+        a = np.zeros(100_001, dtype=REC12)
+        a["key"] = rng.integers(0, 1 << 16, len(a))
+        a["idx"] = np.arange(len(a))
+        key = RadixKey.field(REC12, "key", 3)
+        assert gpu_sort_both_ways(a, key, stable=True, variant=v).tobytes() == o.stable_sorted(a, key).tobytes()
+
+
+def test_stats_report_level_skipping():
+    """Single-bucket levels are skipped (reference lsb_sort.rs:20-23, mt_lsb_sort.rs:170-174)."""
+    rng = np.random.default_rng(89)
+    a = rng.integers(0, 1 << 40, 300_000, dtype="u8")
+    b = radix_sort_builder(a)
+    b.sort()
+    assert b.stats["levels_run"] == 5 and b.stats["levels_skipped"] == 3
+    assert b.stats["algorithmic_bytes"] >= a.nbytes * (1 + 2 * 5)
+    assert np.array_equal(a, np.sort(a))
+    c = np.full(10_000, 7, dtype="u4")
+    b = radix_sort_builder(c)
+    b.sort()
+    assert b.stats["levels_run"] == 0 and b.stats["levels_skipped"] == 4
+
+
+# ---------------------------------------------------------------- BASELINE sizes (properties)
+def _device_props_check(torch, t_sorted, t_in):
+    assert bool((t_sorted[1:] >= t_sorted[:-1]).all())
+    assert int(t_sorted.sum()) == int(t_in.sum())  # wrapping int64 sum: multiset checksum
+    assert int((t_sorted * 0x9E3779B1 ^ (t_sorted >> 7)).sum()) == int((t_in * 0x9E3779B1 ^ (t_in >> 7)).sum())
+
+
+def test_config1_u32_100m_properties():
+    """BASELINE configs[0]: 100 M uniform u32 — sortedness, multiset checksums, idempotence,
+    and exact equality with the oracle on a 2 M-record slice of the same generator."""
+    torch = torch_mod()
+    g = torch.Generator(device="cuda").manual_seed(0x5EED0001)
+    n = 100_000_000
+    ti = torch.randint(-2**31, 2**31, (n,), dtype=torch.int32, device="cuda", generator=g)
+    ref = ti.to(torch.int64) & 0xFFFFFFFF
+    keys = ti.clone()
+    u32 = RadixKey.for_dtype("u4")
+    radix_sort_unstable(keys, u32)  # the int32 storage holds u32 bit patterns
+    torch.cuda.synchronize()
+    s = keys.to(torch.int64) & 0xFFFFFFFF
+    _device_props_check(torch, s, ref)
+    del s, ref
+    again = keys.clone()
+    radix_sort_unstable(again, u32)
+    assert torch.equal(again, keys)
+    small = ti[:2_000_000].cpu().numpy().view("u4")
+    h = small.copy()
+    radix_sort_unstable(h)
+    assert h.tobytes() == o.sorted_copy(small, RadixKey.for_dtype("u4")).tobytes()
+
+
+def test_config2_u64_1b_properties():
+    """BASELINE configs[1]: 1 B uniform u64 (8 GB + 8 GB scratch)."""
+    torch = torch_mod()
+    g = torch.Generator(device="cuda").manual_seed(0x5EED0002)
+    n = 1_000_000_000
+    t = torch.randint(-2**63, 2**63 - 1, (n,), dtype=torch.int64, device="cuda", generator=g)
+    chk = int(t.sum()), int((t ^ (t >> 9)).sum())
+    radix_sort_unstable(t, RadixKey.for_dtype("u8"))  # the int64 storage holds u64 bit patterns
+    torch.cuda.synchronize()
+    # unsigned order: compare with the sign bit flipped
+    u = t ^ (-2**63)
+    ok = True
+    step = 1 << 27
+    for i in range(0, n - 1, step):
+        j = min(n - 1, i + step)
+        ok = ok and bool((u[i + 1:j + 1] >= u[i:j]).all())
+    assert ok
+    assert chk == (int(t.sum()), int((t ^ (t >> 9)).sum()))
+    del u
+    _abi.lib().b200_release_scratch(-1)
+
+
+def test_config4_struct_100m_stable_property():
+    """BASELINE configs[3] shape at 100 M: {u32 key (LEVELS=3), 8-byte payload = index}.
+    Stability <=> within equal keys the payload indices ascend."""
+    torch = torch_mod()
+    g = torch.Generator(device="cuda").manual_seed(0x5EED0004)
+    n = 100_000_000
+    rec = torch.empty((n, 3), dtype=torch.int32, device="cuda")
+    rec[:, 0] = torch.randint(0, 1 << 24, (n,), dtype=torch.int32, device="cuda", generator=g)
+    rec[:, 1] = torch.arange(n, dtype=torch.int32, device="cuda")
+    rec[:, 2] = 0
+    radix_sort_stable(rec, RadixKey("uint", 12, 3, 0, 4))
+    torch.cuda.synchronize()
+    k, idx = rec[:, 0], rec[:, 1]
+    assert bool((k[1:] >= k[:-1]).all())
+    same = k[1:] == k[:-1]
+    assert bool((idx[1:][same] > idx[:-1][same]).all())
+    assert int(idx.to(torch.int64).sum()) == n * (n - 1) // 2
+    _abi.lib().b200_release_scratch(-1)
