@@ -1,0 +1,145 @@
+"""World-size-2 (and 4) gloo tests of the sharded sort's HOST logic on CPU: splitter
+choice, send matrix, exchange plumbing and result assembly.  The data-path operations
+(K1 / partition / local sort) are CUDA-only in the product; here a TEST DOUBLE engine,
+built on the oracle, stands in for them so the collective logic can run without a GPU."""
+import os
+import socket
+import sys
+
+import numpy as np
+import pytest
+import torch
+import torch.distributed as dist
+import torch.multiprocessing as mp
+
+import oracle_ffi as o
+from rdst_b200 import RadixKey
+from rdst_b200.dist import choose_splitters, part_of_digit, pick_partition_level, send_matrix, sharded_sort
+
+
+class OracleEngine:
+    """CPU test double with CudaEngine's interface (buffers are flat uint8 torch CPU tensors)."""
+
+    def __init__(self, key):
+        self.key, self.launches = key, 0
+
+    def empty(self, n):
+        return torch.empty(max(1, n) * self.key.elem_size, dtype=torch.uint8)
+
+    def _np(self, buf, n):
+        return buf.numpy()[: n * self.key.elem_size]
+
+    def histogram(self, buf, n):
+        a = self._np(buf, n)
+        return np.stack([o.get_counts(a, self.key, l)[0] for l in range(self.key.levels)])
+
+    def partition(self, src, dst, n, level, row, split, parts):
+        a = self._np(src, n).reshape(n, self.key.elem_size)
+        digits = o.key_matrix(a.reshape(-1), self.key)[:, level]
+        part = part_of_digit(np.asarray(split), parts)[digits]
+        order = np.argsort(part, kind="stable")
+        dst.numpy()[: n * self.key.elem_size] = a[order].reshape(-1)
+        return np.bincount(part, minlength=parts).astype(np.int64)
+
+    def sort(self, buf, n, tmp=None):
+        a = self._np(buf, n)
+        a[:] = o.stable_sorted(a.copy(), self.key)
+        return {"levels_run": self.key.levels, "kernel_launches": 0}
+
+    def to_comm(self, arr):
+        return torch.from_numpy(arr)
+
+    def exchange(self, send, recv, send_counts, recv_counts, group):
+        es = self.key.elem_size
+        outs = [recv[int(recv_counts[:r].sum()) * es: int(recv_counts[: r + 1].sum()) * es] for r in range(len(recv_counts))]
+        ins = [send[int(send_counts[:r].sum()) * es: int(send_counts[: r + 1].sum()) * es] for r in range(len(send_counts))]
+        # gloo has no all_to_all_single on CPU for uneven splits in every build: use isend/irecv pairs
+        rank, world = dist.get_rank(), dist.get_world_size()
+        outs[rank].copy_(ins[rank])
+        reqs = []
+        for r in range(world):
+            if r == rank:
+                continue
+            if ins[r].numel():
+                reqs.append(dist.isend(ins[r].contiguous(), r))
+            if outs[r].numel():
+                reqs.append(dist.irecv(outs[r], r))
+        for q in reqs:
+            q.wait()
+
+
+def _worker(rank, world, port, case, ret):
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port), RANK=str(rank), WORLD_SIZE=str(world))
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        key, full = make_case(case)
+        n = len(full) // key.elem_size
+        lo, hi = rank * n // world, (rank + 1) * n // world
+        shard = torch.from_numpy(full[lo * key.elem_size: hi * key.elem_size].copy())
+        t = {}
+        out, n_out = sharded_sort(shard, hi - lo, key, engine=OracleEngine(key), timings=t)
+        ret[rank] = out.numpy()[: n_out * key.elem_size].tobytes()
+    finally:
+        dist.destroy_process_group()
+
+
+def make_case(case):
+    rng = np.random.default_rng(1234)
+    if case == "u64_uniform":
+        return RadixKey.for_dtype("u8"), rng.integers(0, 2**64, 200_001, dtype="u8").view(np.uint8)
+    if case == "u64_small_values":  # top bytes trivial -> partition level moves down
+        return RadixKey.for_dtype("u8"), rng.integers(0, 50_000, 150_000, dtype="u8").view(np.uint8)
+    if case == "all_equal":
+        return RadixKey.for_dtype("u4"), np.full(10_000, 77, dtype="u4").view(np.uint8)
+    if case == "zipf":
+        return RadixKey.for_dtype("u8"), np.minimum(rng.zipf(1.1, 120_000), 2**32).astype("u8").view(np.uint8)
+    if case == "struct_stable":
+        rec = np.dtype([("key", "<u4"), ("idx", "<u8")])
+        a = np.zeros(90_000, dtype=rec)
+        a["key"] = rng.integers(0, 1 << 20, len(a))
+        a["idx"] = np.arange(len(a))
+        return RadixKey.field(rec, "key", 3), a.view(np.uint8)
+    if case == "f32":
+        return RadixKey.for_dtype("f4"), rng.standard_normal(100_003).astype("f4").view(np.uint8)
+    raise KeyError(case)
+
+
+def _free_port():
+    s = socket.socket()
+    s.bind(("127.0.0.1", 0))
+    p = s.getsockname()[1]
+    s.close()
+    return p
+
+
+@pytest.mark.parametrize("world", [2, 4])
+@pytest.mark.parametrize("case", ["u64_uniform", "u64_small_values", "all_equal", "zipf", "struct_stable", "f32"])
+def test_sharded_sort_gloo(world, case):
+    if world == 4 and case not in ("u64_uniform", "struct_stable"):
+        pytest.skip("world 4 covered by two cases")
+    mgr = mp.Manager()
+    ret = mgr.dict()
+    mp.spawn(_worker, args=(world, _free_port(), case, ret), nprocs=world, join=True)
+    key, full = make_case(case)
+    got = b"".join(ret[r] for r in range(world))
+    assert got == o.stable_sorted(full, key).tobytes()
+
+
+def test_splitter_logic():
+    row = np.full(256, 1000)
+    for p in (2, 4, 8):
+        sp = choose_splitters(row, p)
+        assert sp.tolist() == [256 * g // p for g in range(1, p)]
+        m = send_matrix(np.stack([row, row]), sp, p)
+        assert m.shape == (2, p) and (m == 256_000 // p).all()
+    row = np.zeros(256, dtype=np.int64)
+    row[9] = 5
+    sp = choose_splitters(row, 4)
+    assert send_matrix(row[None], sp, 4).sum() == 5
+    pod = part_of_digit(np.array([10, 10, 200]), 4)
+    assert pod[9] == 0 and pod[10] == 2 and pod[199] == 2 and pod[200] == 3
+    h = np.zeros((8, 256), dtype=np.int64)
+    h[:, 0] = 100
+    assert pick_partition_level(h) == -1
+    h[2, 0], h[2, 5] = 60, 40
+    assert pick_partition_level(h) == 2
