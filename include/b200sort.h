@@ -85,7 +85,8 @@ typedef struct {
     int32_t variant;   /* < 0 = let the tuner pick (-2: prefer the low-scratch variant);
                           else index < b200_variant_count() */
     int32_t device;    /* CUDA device ordinal; -1 = current device */
-    void* stream;      /* cudaStream_t to order the work on; NULL = the library's own stream */
+    void* stream;      /* cudaStream_t to order the work on; NULL = the library's own (blocking) stream,
+                          which is ordered against the legacy default stream */
 } b200_sort_opts;
 
 typedef struct {

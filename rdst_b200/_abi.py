@@ -158,3 +158,14 @@ def check(code):
     if code == 1:
         raise LevelsZeroError(code, "RadixKey must have at least 1 level")
     raise B200SortError(code, detail)
+
+
+CUDA_STREAM_LEGACY = 0x1  # cudaStreamLegacy
+
+
+def torch_stream_handle(torch):
+    """cudaStream_t of torch's current stream.  torch reports its default stream as 0, which
+    in b200_sort_opts means "the library's own stream"; the legacy default stream has the
+    explicit handle cudaStreamLegacy, so the sort is ordered after work torch already queued."""
+    h = torch.cuda.current_stream().cuda_stream
+    return h if h else CUDA_STREAM_LEGACY

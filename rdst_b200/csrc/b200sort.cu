@@ -122,7 +122,7 @@ struct DeviceCtx {
     bool ready = false;
     std::mutex mu;
     cudaStream_t stream = nullptr;
-    cudaEvent_t ev[8] = {};
+    cudaEvent_t ev[12] = {};
     int sm_count = 0;
     // small device block: hist [64][256] u64 | base [64][256] u64 | tickets [64] u32 | remap [256] u8 | part base
     uint8_t* d_small = nullptr;
@@ -173,7 +173,9 @@ int get_ctx(int device, DeviceCtx** out) {
         }
         c.dev = dev;
         c.sm_count = prop.multiProcessorCount;
-        CUDA_TRY(cudaStreamCreateWithFlags(&c.stream, cudaStreamNonBlocking));
+        // a blocking stream: ordered against the legacy default stream, so callers that enqueue work
+        // on stream 0 (e.g. a copy into the buffer) and pass stream = NULL are still ordered correctly
+        CUDA_TRY(cudaStreamCreateWithFlags(&c.stream, cudaStreamDefault));
         for (auto& ev : c.ev) CUDA_TRY(cudaEventCreate(&ev));
         for (auto& ev : c.bounce_ev) CUDA_TRY(cudaEventCreateWithFlags(&ev, cudaEventDisableTiming));
         CUDA_TRY(cudaMalloc(&c.d_small, SMALL_BYTES));
@@ -330,7 +332,7 @@ int launch_pass(DeviceCtx& c, cudaStream_t st, const PassPlan& pp, const Lowered
 // ---- K1 dispatch (instantiations live in hist_w*.cu) ----
 bool hist_agg_enabled() {
     const char* env = getenv("B200SORT_HIST_AGG");
-    return env ? atoi(env) != 0 : true;
+    return env ? atoi(env) != 0 : false;
 }
 
 // Fills d_hist [levels][256] (u64) on the stream.
@@ -405,11 +407,21 @@ int sort_device_impl(DeviceCtx& c, cudaStream_t st, void* data, void* tmp, uint6
     CUDA_TRY(cudaEventRecord(c.ev[0], st));
     int rc = launch_histogram(c, st, lo, data, n, d_hist);
     if (rc) return rc;
+    static const bool dbg = getenv("B200SORT_DEBUG_TIMING") != nullptr;
+    if (dbg) cudaEventRecord(c.ev[8], st);
     scan_hist_kernel<<<lo.levels, RADIX, 0, st>>>(d_hist, d_base);
     CUDA_TRY(cudaGetLastError());
+    if (dbg) cudaEventRecord(c.ev[9], st);
     CUDA_TRY(cudaMemcpyAsync(c.h_hist, d_hist, size_t(lo.levels) * RADIX * 8, cudaMemcpyDeviceToHost, st));
     CUDA_TRY(cudaEventRecord(c.ev[1], st));
     CUDA_TRY(cudaStreamSynchronize(st));
+    if (dbg) {
+        float a = 0, b = 0, d = 0;
+        cudaEventElapsedTime(&a, c.ev[0], c.ev[8]);
+        cudaEventElapsedTime(&b, c.ev[8], c.ev[9]);
+        cudaEventElapsedTime(&d, c.ev[9], c.ev[1]);
+        fprintf(stderr, "[b200sort] memset+K1 %.3f ms, scan %.3f ms, D2H hist %.3f ms\n", a, b, d);
+    }
 
     // levels with a single non-empty bucket are exact no-ops for a stable LSD sort
     std::vector<uint32_t> active;

@@ -3,6 +3,7 @@
 // parallel.
 #pragma once
 #include "onesweep.cuh"
+#include "pass_or.cuh"
 #include "variants.h"
 #include "launch.h"
 
@@ -12,11 +13,18 @@ template <int WORDS, bool FLOATK, bool REMAP, int V>
 static PassLaunch make_launch() {
     constexpr VariantInfo vi = kVariants[V];
     constexpr int ITEMS = vi.items[WORDS - 1];
-    using SM = PassSmem<WORDS, vi.threads, ITEMS, vi.tma>;
     PassLaunch pl;
-    pl.kernel = &onesweep_pass_kernel<WORDS, vi.threads, ITEMS, FLOATK, vi.tma, vi.match_hw, REMAP, vi.min_blocks>;
-    pl.smem = SM::TOTAL;
-    pl.tile = SM::TILE;
+    if constexpr (vi.algo == 1) {
+        using SM = OrSmem<WORDS, vi.threads, ITEMS>;
+        pl.kernel = &lsd_pass_or_kernel<WORDS, vi.threads, ITEMS, FLOATK, REMAP, vi.min_blocks>;
+        pl.smem = SM::TOTAL;
+        pl.tile = SM::TILE;
+    } else {
+        using SM = PassSmem<WORDS, vi.threads, ITEMS, vi.tma>;
+        pl.kernel = &onesweep_pass_kernel<WORDS, vi.threads, ITEMS, FLOATK, vi.tma, vi.match_hw, REMAP, vi.min_blocks>;
+        pl.smem = SM::TOTAL;
+        pl.tile = SM::TILE;
+    }
     pl.threads = vi.threads;
     return pl;
 }
@@ -30,6 +38,12 @@ static PassLaunch pick_launch(int v) {
         case 3: return make_launch<WORDS, FLOATK, REMAP, 3>();
         case 4: return make_launch<WORDS, FLOATK, REMAP, 4>();
         case 5: return make_launch<WORDS, FLOATK, REMAP, 5>();
+        case 6: return make_launch<WORDS, FLOATK, REMAP, 6>();
+        case 7: return make_launch<WORDS, FLOATK, REMAP, 7>();
+        case 8: return make_launch<WORDS, FLOATK, REMAP, 8>();
+        case 9: return make_launch<WORDS, FLOATK, REMAP, 9>();
+        case 10: return make_launch<WORDS, FLOATK, REMAP, 10>();
+        case 11: return make_launch<WORDS, FLOATK, REMAP, 11>();
         default: break;
     }
     PassLaunch none{};

@@ -13,17 +13,24 @@ struct VariantInfo {
     bool tma;      // stage tiles with bulk asynchronous copies (persistent, prefetching)
     bool match_hw; // MATCH.ANY instead of eight ballots
     int min_blocks;
+    int algo;      // 0 = ballot-matching kernel (onesweep.cuh), 1 = OR-matching kernel (pass_or.cuh)
 };
 
-constexpr int NUM_VARIANTS = 6;
+constexpr int NUM_VARIANTS = 12;
 
 constexpr VariantInfo kVariants[NUM_VARIANTS] = {
-    {"t512_ldg", 512, {16, 16, 12, 8}, false, false, 1},
-    {"t512_tma", 512, {24, 16, 12, 8}, true, false, 1},
-    {"t256_tma_occ", 256, {16, 16, 12, 8}, true, false, 2},
-    {"t256_ldg_occ", 256, {16, 16, 12, 8}, false, false, 2},
-    {"t512_tma_matchhw", 512, {24, 16, 12, 8}, true, true, 1},
-    {"t1024_tma", 1024, {12, 8, 6, 4}, true, false, 1},
+    {"t512_ldg", 512, {16, 16, 12, 8}, false, false, 1, 0},
+    {"t512_tma", 512, {24, 16, 12, 8}, true, false, 1, 0},
+    {"t256_tma_occ", 256, {16, 16, 12, 8}, true, false, 2, 0},
+    {"t256_ldg_occ", 256, {16, 16, 12, 8}, false, false, 2, 0},
+    {"t512_tma_matchhw", 512, {24, 16, 12, 8}, true, true, 1, 0},
+    {"t1024_tma", 1024, {12, 8, 6, 4}, true, false, 1, 0},
+    {"or256_i16", 256, {16, 16, 10, 8}, false, false, 3, 1},
+    {"or256_i8", 256, {8, 8, 6, 4}, false, false, 4, 1},
+    {"or512_i8", 512, {8, 8, 6, 4}, false, false, 2, 1},
+    {"or384_i18", 384, {18, 12, 8, 6}, false, false, 2, 1},
+    {"or256_i12", 256, {12, 12, 8, 6}, false, false, 4, 1},
+    {"or256_i24", 256, {24, 20, 12, 10}, false, false, 2, 1},
 };
 
 }  // namespace b200

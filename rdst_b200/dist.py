@@ -85,7 +85,7 @@ class CudaEngine:
         o.stable = 1
         o.variant = -1
         o.device = self.torch.cuda.current_device()
-        o.stream = self.torch.cuda.current_stream().cuda_stream
+        o.stream = _abi.torch_stream_handle(self.torch)
         return o
 
     def empty(self, n_records):

@@ -24,6 +24,10 @@ _LOW_MEM = LowMemoryTuner()
 _SINGLE = SingleThreadedTuner()
 
 
+def _stream_handle(torch):
+    return _abi.torch_stream_handle(torch)
+
+
 def _is_torch(x):
     return type(x).__module__.startswith("torch")
 
@@ -119,7 +123,7 @@ class RadixSortBuilder:
             import torch
 
             with torch.cuda.device(dev):
-                opts.stream = torch.cuda.current_stream().cuda_stream
+                opts.stream = _stream_handle(torch)
                 _abi.check(lib.b200_sort_device(ptr, None, n, C.byref(desc), C.byref(opts), C.byref(stats)))
         else:
             _abi.check(lib.b200_sort_host(ptr, n, C.byref(desc), C.byref(opts), C.byref(stats)))
@@ -140,7 +144,7 @@ class RadixSortBuilder:
         dev = t.device.index
         opts.device = dev
         with torch.cuda.device(dev):
-            opts.stream = torch.cuda.current_stream().cuda_stream
+            opts.stream = _stream_handle(torch)
             L = self._key.levels
             hist = (C.c_uint64 * (256 * L))()
             _abi.check(lib.b200_histogram_device(t.data_ptr(), n, C.byref(desc), C.byref(opts), hist))
