@@ -233,14 +233,13 @@ PassLaunch get_pass_launch(uint32_t words, bool floatk, bool remap, int variant)
 }
 
 int default_variant(uint32_t words, uint64_t n) {
-    (void)words;
     (void)n;
     const char* env = getenv("B200SORT_VARIANT");
     if (env) {
         int v = atoi(env);
         if (v >= 0 && v < NUM_VARIANTS) return v;
     }
-    return 1;
+    return kDefaultVariant[words - 1];
 }
 
 constexpr int BYTE_THREADS = 256, BYTE_ITEMS = 4;
@@ -263,7 +262,7 @@ int plan_pass(DeviceCtx& c, const Lowered& lo, uint64_t n, const void* a, const 
         pp.words = lo.elem_size / 4;
         if (variant < 0) variant = default_variant(pp.words, n);
         if (variant >= NUM_VARIANTS) return B200_ERR_BAD_ARG;
-        if (remap) variant = 0;
+        if (remap) variant = kRemapVariant;
         pp.variant = variant;
         pp.pl = get_pass_launch(pp.words, lo.is_float, remap, variant);
         if (!pp.pl.kernel) return B200_ERR_BAD_ARG;

@@ -4,6 +4,7 @@
 #pragma once
 #include "onesweep.cuh"
 #include "pass_or.cuh"
+#include "pass_or16.cuh"
 #include "variants.h"
 #include "launch.h"
 
@@ -14,7 +15,12 @@ static PassLaunch make_launch() {
     constexpr VariantInfo vi = kVariants[V];
     constexpr int ITEMS = vi.items[WORDS - 1];
     PassLaunch pl;
-    if constexpr (vi.algo == 1) {
+    if constexpr (vi.algo == 2) {
+        using SM = Or16Smem<WORDS, vi.threads, ITEMS>;
+        pl.kernel = &lsd_pass_or16_kernel<WORDS, vi.threads, ITEMS, FLOATK, REMAP, vi.min_blocks>;
+        pl.smem = SM::TOTAL;
+        pl.tile = SM::TILE;
+    } else if constexpr (vi.algo == 1) {
         using SM = OrSmem<WORDS, vi.threads, ITEMS>;
         pl.kernel = &lsd_pass_or_kernel<WORDS, vi.threads, ITEMS, FLOATK, REMAP, vi.min_blocks>;
         pl.smem = SM::TOTAL;
@@ -44,6 +50,10 @@ static PassLaunch pick_launch(int v) {
         case 9: return make_launch<WORDS, FLOATK, REMAP, 9>();
         case 10: return make_launch<WORDS, FLOATK, REMAP, 10>();
         case 11: return make_launch<WORDS, FLOATK, REMAP, 11>();
+        case 12: return make_launch<WORDS, FLOATK, REMAP, 12>();
+        case 13: return make_launch<WORDS, FLOATK, REMAP, 13>();
+        case 14: return make_launch<WORDS, FLOATK, REMAP, 14>();
+        case 15: return make_launch<WORDS, FLOATK, REMAP, 15>();
         default: break;
     }
     PassLaunch none{};
@@ -53,8 +63,8 @@ static PassLaunch pick_launch(int v) {
 template <int WORDS>
 static PassLaunch pick_launch_w(bool floatk, bool remap, int v) {
     if (remap) {
-        // the range-partition pass exists in variant 0 only
-        return floatk ? make_launch<WORDS, true, true, 0>() : make_launch<WORDS, false, true, 0>();
+        // the range-partition pass exists in one variant only (kRemapVariant)
+        return floatk ? make_launch<WORDS, true, true, kRemapVariant>() : make_launch<WORDS, false, true, kRemapVariant>();
     }
     return floatk ? pick_launch<WORDS, true, false>(v) : pick_launch<WORDS, false, false>(v);
 }

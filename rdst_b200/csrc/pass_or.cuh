@@ -65,7 +65,7 @@ __global__ void __launch_bounds__(THREADS, MINB) lsd_pass_or_kernel(const PassPa
     uint8_t* s_slot_raw = smem_raw + SM::OUT_BYTES;
     uint64_t* s_gofs = reinterpret_cast<uint64_t*>(smem_raw + SM::OUT_BYTES + SM::SLOT_BYTES);
     uint8_t* misc = smem_raw + SM::OUT_BYTES + SM::SLOT_BYTES + SM::GOFS_BYTES;
-    volatile uint32_t* s_tile = reinterpret_cast<volatile uint32_t*>(misc);
+    volatile uint32_t* s_tile = reinterpret_cast<volatile uint32_t*>(misc);  // [0] first, [1] next tile id
     uint32_t* s_wtot = reinterpret_cast<uint32_t*>(misc + 32);  // 8 digit-warp totals
 
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
@@ -81,30 +81,42 @@ __global__ void __launch_bounds__(THREADS, MINB) lsd_pass_or_kernel(const PassPa
         for (int i = tid; i < int(SM::SLOT_BYTES / 16); i += THREADS) z[i] = make_uint4(0, 0, 0, 0);
     }
 
-    while (true) {
-        if (tid == 0) *s_tile = atomicAdd(p.ticket, 1u);
-        __syncthreads();  // (A) tile id visible; previous write-out done; slots are clean
-        const uint32_t tile = *s_tile;
-        if (tile >= p.num_tiles) break;
-        const uint64_t tile_base = uint64_t(tile) * TILE;
-        const uint64_t rem = p.n - tile_base;
-        const uint32_t valid = rem < uint64_t(TILE) ? uint32_t(rem) : uint32_t(TILE);
-        const bool full = valid == uint32_t(TILE);
-
-        // ---- load: element (warp, j, lane) = warp*32*ITEMS + j*32 + lane, i.e. memory order ----
-        Rec<WORDS> r[ITEMS];
-        const uint32_t e0 = uint32_t(warp) * 32u * ITEMS + lane;
-        const uint32_t* g = p.src + tile_base * WORDS;
+    auto tile_valid = [&](uint32_t t) -> uint32_t {
+        const uint64_t rem = p.n - uint64_t(t) * TILE;
+        return rem < uint64_t(TILE) ? uint32_t(rem) : uint32_t(TILE);
+    };
+    // element (warp, j, lane) = warp*32*ITEMS + j*32 + lane, i.e. memory order
+    const uint32_t e0 = uint32_t(warp) * 32u * ITEMS + lane;
+    Rec<WORDS> r[ITEMS];
+    auto load_tile = [&](uint32_t t) {
+        if (t >= p.num_tiles) return;
+        const uint32_t v = tile_valid(t);
+        const bool f = v == uint32_t(TILE);
+        const uint32_t* g = p.src + uint64_t(t) * TILE * WORDS;
 #pragma unroll
         for (int j = 0; j < ITEMS; ++j) {
             const uint32_t e = e0 + j * 32;
-            if (full || e < valid) {
+            if (f || e < v) {
                 r[j] = load_rec<WORDS>(g, e);
             } else {
 #pragma unroll
                 for (int k = 0; k < WORDS; ++k) r[j].w[k] = 0;
             }
         }
+    };
+
+    // Tiles are claimed in ticket order, one ahead: while a tile is processed the next one
+    // is already claimed, and its records are fetched as soon as the registers are free
+    // (right after the scatter), so the loads fly during the look-back and the write-out.
+    if (tid == 0) s_tile[0] = atomicAdd(p.ticket, 1u);
+    __syncthreads();  // first tile id visible; slots are clean
+    uint32_t tile = s_tile[0];
+    load_tile(tile);
+
+    while (tile < p.num_tiles) {
+        if (tid == 0) s_tile[1] = atomicAdd(p.ticket, 1u);  // read by everyone after barrier (B)
+        const uint32_t valid = tile_valid(tile);
+        const bool full = valid == uint32_t(TILE);
 
         // ---- rank inside the warp by OR-matching; stable: lanes in order, rounds in order ----
         uint32_t rank[ITEMS];
@@ -177,6 +189,8 @@ __global__ void __launch_bounds__(THREADS, MINB) lsd_pass_or_kernel(const PassPa
             const uint32_t pos = lds_u32(my_slots + d * 8 + 4) + rank[j];
             store_rec<WORDS>(s_out, pos, r[j]);
         }
+        const uint32_t next_tile = s_tile[1];
+        load_tile(next_tile);  // registers are free again: fetch the next tile now
         __syncwarp();
         // this warp's slots are only read by this warp: reset them for the next tile now
         {
@@ -217,7 +231,7 @@ __global__ void __launch_bounds__(THREADS, MINB) lsd_pass_or_kernel(const PassPa
         // ---- write-out: runs of equal digits are contiguous in s_out and in dst ----
         if constexpr (WORDS == 1 || WORDS == 2 || WORDS == 4) {
             if (full) {
-#pragma unroll
+#pragma unroll 4
                 for (int k = 0; k < ITEMS; ++k) {
                     const uint32_t i = tid + k * THREADS;
                     const Rec<WORDS> x = load_rec<WORDS>(s_out, i);
@@ -244,7 +258,8 @@ __global__ void __launch_bounds__(THREADS, MINB) lsd_pass_or_kernel(const PassPa
                 p.dst[(s_gofs[d] + pos) * WORDS + k] = s_out[wi];
             }
         }
-        // barrier (A) of the next iteration orders this write-out before the next scatter
+        // barriers (B)..(C) of the next iteration order this write-out before the next scatter
+        tile = next_tile;
     }
 }
 

@@ -1,0 +1,239 @@
+// pass_or16.cuh — K2 variant "or16": as pass_or.cuh, but the matching group is a HALF-warp.
+// A half-warp's slot is one 32-bit word {count:16 | mask:16}, so the three shared-memory
+// operations per record (RED.OR, LDS, leader STS) are 32-bit accesses spread over all 32
+// banks instead of 64-bit accesses on 16 bank pairs: ncu showed the warp-wide variant
+// bound by the L1 data pipe (93 %), 58 % of its shared wavefronts being bank conflicts
+// (profiles/r1c_*).  Each half-warp owns a contiguous run of the tile so that
+// (half-warp, round, lane) order is memory order and the pass stays stable.
+#pragma once
+#include "pass_or.cuh"
+
+namespace b200 {
+
+template <int WORDS, int THREADS, int ITEMS>
+struct Or16Smem {
+    static constexpr int WARPS = THREADS / 32;
+    static constexpr int TILE = THREADS * ITEMS;
+    static constexpr size_t OUT_BYTES = size_t(TILE) * WORDS * 4;
+    static constexpr int GROUPS = THREADS / 16;
+    static constexpr size_t SLOT_BYTES = size_t(GROUPS) * RADIX * 4;
+    static constexpr size_t GOFS_BYTES = RADIX * 8;
+    static constexpr size_t MISC_BYTES = 128;
+    static constexpr size_t TOTAL = OUT_BYTES + SLOT_BYTES + GOFS_BYTES + MISC_BYTES;
+};
+
+template <int WORDS, int THREADS, int ITEMS, bool FLOATK, bool REMAP, int MINB>
+__global__ void __launch_bounds__(THREADS, MINB) lsd_pass_or16_kernel(const PassParams p) {
+    static_assert(THREADS >= RADIX && THREADS % 32 == 0, "one thread per digit is needed for the look-back");
+    using SM = Or16Smem<WORDS, THREADS, ITEMS>;
+    constexpr int GROUPS = SM::GROUPS;
+    static_assert(SM::TILE <= 65536, "16-bit positions");
+    constexpr int TILE = SM::TILE;
+    constexpr int LB_BATCH = 4;
+
+    extern __shared__ __align__(128) uint8_t smem_raw[];
+    uint32_t* s_out = reinterpret_cast<uint32_t*>(smem_raw);
+    uint8_t* s_slot_raw = smem_raw + SM::OUT_BYTES;
+    uint64_t* s_gofs = reinterpret_cast<uint64_t*>(smem_raw + SM::OUT_BYTES + SM::SLOT_BYTES);
+    uint8_t* misc = smem_raw + SM::OUT_BYTES + SM::SLOT_BYTES + SM::GOFS_BYTES;
+    volatile uint32_t* s_tile = reinterpret_cast<volatile uint32_t*>(misc);  // [0] first, [1] next tile id
+    uint32_t* s_wtot = reinterpret_cast<uint32_t*>(misc + 32);  // 8 digit-warp totals
+
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const uint32_t lane_bit = 1u << (lane & 15);
+    const uint32_t lt_mask = lane_bit - 1u;                                  // lanes below me in my half-warp
+    const uint32_t slot_base = smem_u32(s_slot_raw);                         // [GROUPS][256] x 4 B
+    const uint32_t my_slots = slot_base + uint32_t(tid >> 4) * RADIX * 4;    // this half-warp's 256 slots
+    const DigitParams dp = p.dp;
+
+    // all slots start as {mask 0, count 0}
+    {
+        uint4* z = reinterpret_cast<uint4*>(s_slot_raw);
+        for (int i = tid; i < int(SM::SLOT_BYTES / 16); i += THREADS) z[i] = make_uint4(0, 0, 0, 0);
+    }
+
+    auto tile_valid = [&](uint32_t t) -> uint32_t {
+        const uint64_t rem = p.n - uint64_t(t) * TILE;
+        return rem < uint64_t(TILE) ? uint32_t(rem) : uint32_t(TILE);
+    };
+    // element (half-warp h, j, lane16) = h*16*ITEMS + j*16 + lane16: every half-warp owns a
+    // contiguous run of the tile, so (h, j, lane16) order is memory order
+    const uint32_t e0 = uint32_t(tid >> 4) * 16u * ITEMS + (lane & 15);
+    Rec<WORDS> r[ITEMS];
+    auto load_tile = [&](uint32_t t) {
+        if (t >= p.num_tiles) return;
+        const uint32_t v = tile_valid(t);
+        const bool f = v == uint32_t(TILE);
+        const uint32_t* g = p.src + uint64_t(t) * TILE * WORDS;
+#pragma unroll
+        for (int j = 0; j < ITEMS; ++j) {
+            const uint32_t e = e0 + j * 16;
+            if (f || e < v) {
+                r[j] = load_rec<WORDS>(g, e);
+            } else {
+#pragma unroll
+                for (int k = 0; k < WORDS; ++k) r[j].w[k] = 0;
+            }
+        }
+    };
+
+    // Tiles are claimed in ticket order, one ahead: while a tile is processed the next one
+    // is already claimed, and its records are fetched as soon as the registers are free
+    // (right after the scatter), so the loads fly during the look-back and the write-out.
+    if (tid == 0) s_tile[0] = atomicAdd(p.ticket, 1u);
+    __syncthreads();  // first tile id visible; slots are clean
+    uint32_t tile = s_tile[0];
+    load_tile(tile);
+
+    while (tile < p.num_tiles) {
+        if (tid == 0) s_tile[1] = atomicAdd(p.ticket, 1u);  // read by everyone after barrier (B)
+        const uint32_t valid = tile_valid(tile);
+        const bool full = valid == uint32_t(TILE);
+
+        // ---- rank inside the warp by OR-matching; stable: lanes in order, rounds in order ----
+        uint32_t rank[ITEMS];
+#pragma unroll
+        for (int j = 0; j < ITEMS; ++j) {
+            const uint32_t e = e0 + j * 16;
+            uint32_t d = 255u;  // padding sorts to the very end of the tile
+            if (full || e < valid) {
+                d = rec_digit<WORDS, FLOATK>(dp, r[j]);
+                if (REMAP) d = p.remap[d];
+            }
+            const uint32_t sa = my_slots + d * 4;
+            slot_or(sa, lane_bit);
+            __syncwarp();
+            const uint32_t v = lds_u32(sa);  // [15:0] lanes with my digit, [31:16] records of my digit in earlier rounds
+            __syncwarp();
+            const uint32_t m = v & 0xffffu, c = v >> 16;
+            const uint32_t lt = m & lt_mask;
+            if (lt == 0) sts_u32(sa, (c + __popc(m)) << 16);
+            __syncwarp();
+            rank[j] = c + __popc(lt);
+        }
+        __syncthreads();  // (B) every warp's counts final, masks back to zero
+
+        // ---- one thread per digit: tile count, publish, local bases ----
+        uint32_t sum = 0, incl = 0, cnt = 0;
+        if (tid < RADIX) {
+            const uint32_t ca = slot_base + uint32_t(tid) * 4;
+#pragma unroll
+            for (int w = 0; w < GROUPS; ++w) sum += lds_u32(ca + w * RADIX * 4) >> 16;
+            cnt = sum;
+            if (tid == RADIX - 1) cnt -= uint32_t(TILE) - valid;
+            lb_store(&p.lookback[uint64_t(tile) * RADIX + tid], lb_pack(tile == 0 ? LB_PREFIX : LB_AGG, p.tag, cnt));
+            incl = sum;
+#pragma unroll
+            for (int o = 1; o < 32; o <<= 1) {
+                const uint32_t y = __shfl_up_sync(0xffffffffu, incl, o);
+                if (lane >= o) incl += y;
+            }
+            if (lane == 31) s_wtot[warp] = incl;
+        }
+        __syncthreads();  // (B2)
+        uint32_t local_off = 0;
+        if (tid < RADIX) {
+            uint32_t wbase = 0;
+#pragma unroll
+            for (int w = 0; w < RADIX / 32; ++w)
+                if (w < warp) wbase += s_wtot[w];
+            local_off = wbase + incl - sum;
+            // slot count := position of the (warp, digit) group inside the locally sorted tile
+            const uint32_t ca = slot_base + uint32_t(tid) * 4;
+            uint32_t run = local_off;
+#pragma unroll
+            for (int w = 0; w < GROUPS; ++w) {
+                const uint32_t c = lds_u32(ca + w * RADIX * 4) >> 16;
+                sts_u32(ca + w * RADIX * 4, run << 16);
+                run += c;
+            }
+        }
+        __syncthreads();  // (C)
+
+        // ---- scatter into the staging buffer in locally sorted order ----
+#pragma unroll
+        for (int j = 0; j < ITEMS; ++j) {
+            const uint32_t e = e0 + j * 16;
+            uint32_t d = 255u;
+            if (full || e < valid) {
+                d = rec_digit<WORDS, FLOATK>(dp, r[j]);
+                if (REMAP) d = p.remap[d];
+            }
+            const uint32_t pos = (lds_u32(my_slots + d * 4) >> 16) + rank[j];
+            store_rec<WORDS>(s_out, pos, r[j]);
+        }
+        const uint32_t next_tile = s_tile[1];
+        load_tile(next_tile);  // registers are free again: fetch the next tile now
+        __syncwarp();
+        // this warp's slots are only read by this warp: reset them for the next tile now
+        {
+            uint4* z = reinterpret_cast<uint4*>(s_slot_raw + size_t(warp) * 2 * RADIX * 4);
+#pragma unroll
+            for (int i = lane; i < 2 * RADIX * 4 / 16; i += 32) z[i] = make_uint4(0, 0, 0, 0);
+        }
+
+        // ---- decoupled look-back, one thread per digit, LB_BATCH predecessors per round trip ----
+        if (tid < RADIX) {
+            uint64_t excl = 0;
+            if (tile > 0) {
+                int64_t t = int64_t(tile) - 1;
+                bool done = false;
+                while (!done) {
+                    uint64_t v[LB_BATCH];
+#pragma unroll
+                    for (int b = 0; b < LB_BATCH; ++b) {
+                        const int64_t tb = t - b;
+                        v[b] = tb >= 0 ? lb_load(&p.lookback[uint64_t(tb) * RADIX + tid]) : 0ull;
+                    }
+#pragma unroll
+                    for (int b = 0; b < LB_BATCH; ++b) {
+                        if (done) break;
+                        const uint64_t st = v[b] >> 62;
+                        if (st == 0 || uint32_t((v[b] >> 54) & 0xffu) != (p.tag & 0xffu)) break;  // not published yet
+                        excl += v[b] & LB_VALUE_MASK;
+                        --t;
+                        if (st == LB_PREFIX) done = true;
+                    }
+                }
+                lb_store(&p.lookback[uint64_t(tile) * RADIX + tid], lb_pack(LB_PREFIX, p.tag, excl + cnt));
+            }
+            s_gofs[tid] = p.bucket_base[tid] + excl - local_off;
+        }
+        __syncthreads();  // (D)
+
+        // ---- write-out: runs of equal digits are contiguous in s_out and in dst ----
+        if constexpr (WORDS == 1 || WORDS == 2 || WORDS == 4) {
+            if (full) {
+#pragma unroll 4
+                for (int k = 0; k < ITEMS; ++k) {
+                    const uint32_t i = tid + k * THREADS;
+                    const Rec<WORDS> x = load_rec<WORDS>(s_out, i);
+                    uint32_t d = rec_digit<WORDS, FLOATK>(dp, x);
+                    if (REMAP) d = p.remap[d];
+                    store_rec<WORDS>(p.dst, s_gofs[d] + i, x);
+                }
+            } else {
+                for (uint32_t i = tid; i < valid; i += THREADS) {
+                    const Rec<WORDS> x = load_rec<WORDS>(s_out, i);
+                    uint32_t d = rec_digit<WORDS, FLOATK>(dp, x);
+                    if (REMAP) d = p.remap[d];
+                    store_rec<WORDS>(p.dst, s_gofs[d] + i, x);
+                }
+            }
+        } else {
+            for (uint32_t wi = tid; wi < valid * WORDS; wi += THREADS) {
+                const uint32_t pos = wi / WORDS;
+                const uint32_t k = wi - pos * WORDS;
+                const uint32_t kw = s_out[pos * WORDS + dp.word];
+                const uint32_t sw = FLOATK ? s_out[pos * WORDS + dp.sign_word] : 0u;
+                uint32_t d = digit_from_words<FLOATK>(dp, kw, sw);
+                if (REMAP) d = p.remap[d];
+                p.dst[(s_gofs[d] + pos) * WORDS + k] = s_out[wi];
+            }
+        }
+        // barriers (B)..(C) of the next iteration order this write-out before the next scatter
+        tile = next_tile;
+    }
+}
+
+}  // namespace b200

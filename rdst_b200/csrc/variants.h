@@ -13,10 +13,11 @@ struct VariantInfo {
     bool tma;      // stage tiles with bulk asynchronous copies (persistent, prefetching)
     bool match_hw; // MATCH.ANY instead of eight ballots
     int min_blocks;
-    int algo;      // 0 = ballot-matching kernel (onesweep.cuh), 1 = OR-matching kernel (pass_or.cuh)
+    int algo;      // 0 = ballot-matching kernel (onesweep.cuh), 1 = OR-matching kernel (pass_or.cuh),
+                   // 2 = half-warp OR-matching kernel (pass_or16.cuh)
 };
 
-constexpr int NUM_VARIANTS = 12;
+constexpr int NUM_VARIANTS = 16;
 
 constexpr VariantInfo kVariants[NUM_VARIANTS] = {
     {"t512_ldg", 512, {16, 16, 12, 8}, false, false, 1, 0},
@@ -31,6 +32,14 @@ constexpr VariantInfo kVariants[NUM_VARIANTS] = {
     {"or384_i18", 384, {18, 12, 8, 6}, false, false, 2, 1},
     {"or256_i12", 256, {12, 12, 8, 6}, false, false, 4, 1},
     {"or256_i24", 256, {24, 20, 12, 10}, false, false, 2, 1},
+    {"h256_i16", 256, {16, 16, 10, 8}, false, false, 3, 2},
+    {"h256_i12", 256, {12, 12, 8, 6}, false, false, 4, 2},
+    {"h384_i18", 384, {18, 12, 8, 6}, false, false, 2, 2},
+    {"h256_i24", 256, {24, 20, 12, 10}, false, false, 2, 2},
 };
+
+// Defaults measured on B200 (profiles/r1e_sweep.txt): best variant per record width in words.
+constexpr int kDefaultVariant[4] = {14, 12, 6, 12};
+constexpr int kRemapVariant = 12;
 
 }  // namespace b200
