@@ -1,0 +1,66 @@
+"""Multi-GPU parity worker (run under torchrun by tests/test_gpu_dist.py): every rank sorts its
+shard of a seeded array with rdst_b200.dist.sharded_sort (CUDA engine, NCCL exchange); rank 0
+gathers the outputs and compares their concatenation with the oracle's stable sort."""
+import os
+import sys
+
+import numpy as np
+import torch
+import torch.distributed as dist
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+sys.path.insert(0, os.path.join(ROOT, "tests"))
+import oracle_ffi as o
+from rdst_b200 import RadixKey
+from rdst_b200.dist import sharded_sort
+
+
+def cases():
+    rng = np.random.default_rng(4321)
+    yield "u64_uniform", RadixKey.for_dtype("u8"), rng.integers(0, 2**64, 3_000_001, dtype="u8").view(np.uint8)
+    yield "u64_small", RadixKey.for_dtype("u8"), rng.integers(0, 70_000, 1_000_000, dtype="u8").view(np.uint8)
+    yield "all_equal", RadixKey.for_dtype("u4"), np.full(100_000, 9, dtype="u4").view(np.uint8)
+    yield "zipf", RadixKey.for_dtype("u8"), np.minimum(rng.zipf(1.1, 2_000_000), 2**32).astype("u8").view(np.uint8)
+    yield "f32", RadixKey.for_dtype("f4"), rng.standard_normal(1_500_003).astype("f4").view(np.uint8)
+    rec = np.dtype([("key", "<u4"), ("idx", "<u8")])
+    a = np.zeros(1_200_000, dtype=rec)
+    a["key"] = rng.integers(0, 1 << 22, len(a))
+    a["idx"] = np.arange(len(a))
+    yield "struct12_stable", RadixKey.field(rec, "key", 3), a.view(np.uint8)
+
+
+def main():
+    rank, world = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"])
+    torch.cuda.set_device(int(os.environ["LOCAL_RANK"]))
+    dist.init_process_group("nccl", device_id=torch.device("cuda", int(os.environ["LOCAL_RANK"])))
+    ok = True
+    for name, key, full in cases():
+        es = key.elem_size
+        n = len(full) // es
+        lo, hi = rank * n // world, (rank + 1) * n // world
+        shard = torch.from_numpy(full[lo * es: hi * es].copy()).cuda()
+        out, n_out = sharded_sort(shard, hi - lo, key)
+        torch.cuda.synchronize()
+        mine = out[: n_out * es].cpu()
+        sizes = [torch.zeros(1, dtype=torch.int64, device="cuda") for _ in range(world)]
+        dist.all_gather(sizes, torch.tensor([n_out * es], dtype=torch.int64, device="cuda"))
+        sizes = [int(s.item()) for s in sizes]
+        bufs = [torch.empty(s, dtype=torch.uint8, device="cuda") for s in sizes]
+        for r in range(world):  # broadcast-based gather of uneven pieces
+            if r == rank:
+                bufs[r].copy_(mine)
+            dist.broadcast(bufs[r], src=r)
+        if rank == 0:
+            got = torch.cat(bufs).cpu().numpy().tobytes()
+            exp = o.stable_sorted(full, key).tobytes()
+            good = got == exp
+            print(f"[dist_check] {name}: {'ok' if good else 'MISMATCH'} sizes={[s // es for s in sizes]}", flush=True)
+            ok = ok and good
+    dist.barrier()
+    dist.destroy_process_group()
+    sys.exit(0 if ok else 1)
+
+
+if __name__ == "__main__":
+    main()
