@@ -210,9 +210,15 @@ def run_b200(args):
     scratch = {"tmp": torch.empty(nbytes, dtype=torch.uint8, device="cuda")}
     if world > 1:
         slack = 1.0 + args.recv_slack
-        scratch["part"] = torch.empty(nbytes, dtype=torch.uint8, device="cuda")
-        scratch["recv"] = torch.empty(int(nbytes * slack) // es * es, dtype=torch.uint8, device="cuda")
-        scratch["tmp"] = torch.empty(scratch["recv"].numel(), dtype=torch.uint8, device="cuda")
+        cap = int(nbytes * slack) // es * es
+        if args.exchange == "peer":
+            from rdst_b200.dist import PeerBuffers
+
+            scratch["peers"] = PeerBuffers(cap)
+        else:
+            scratch["part"] = torch.empty(nbytes, dtype=torch.uint8, device="cuda")
+            scratch["recv"] = torch.empty(cap, dtype=torch.uint8, device="cuda")
+        scratch["tmp"] = torch.empty(cap, dtype=torch.uint8, device="cuda")
 
     def barrier():
         if world > 1:
@@ -313,7 +319,7 @@ def run_b200(args):
     if passes and ms_passes > 0:
         per_launch_bytes = 2 * n_sorted * es
         ach = per_launch_bytes * passes / (ms_passes * 1e-3) / 1e9
-        roof = {"bound": "hbm", "kernel": "onesweep_pass_kernel (K2)", "achieved": ach, "peak": peak, "unit": "GB/s",
+        roof = {"bound": "hbm", "kernel": "K2 LSD pass (lsd_pass_or16_kernel, variant " + str(st_local.get("variant")) + ")", "achieved": ach, "peak": peak, "unit": "GB/s",
                 "frac": ach / peak, "traffic": None, "peak_source": peak_src,
                 "algorithmic_bytes_per_launch": per_launch_bytes, "launches_per_step": passes,
                 "avg_launch_ms": ms_passes / passes,
@@ -340,7 +346,14 @@ def run_b200(args):
         "roofline": roof, "cpu_baseline": cb,
     }
     if world > 1:
-        line["exchange"] = {k: last.get(k) for k in ("level", "n_recv", "sent_bytes")}
+        line["exchange"] = {"mode": args.exchange}
+        line["exchange"].update({k: last.get(k) for k in ("level", "n_recv", "sent_bytes", "phase_ms")})
+        pm = last.get("phase_ms") or {}
+        if pm.get("all_to_all"):
+            t_x = pm["all_to_all"] + (pm["partition"] if args.exchange == "peer" else 0.0)
+            line["exchange"]["exchange_ms"] = t_x
+            line["exchange"]["all_to_all_GBps_per_direction"] = last["sent_bytes"] / (t_x * 1e-3) / 1e9
+            line["exchange"]["nvlink_peak_GBps"] = 900.0
     print(json.dumps(line))
     if world > 1:
         dist.destroy_process_group()
@@ -359,6 +372,8 @@ def main():
     ap.add_argument("--cpu-steps", type=int, default=3)
     ap.add_argument("--e2e-steps", type=int, default=3)
     ap.add_argument("--recv-slack", type=float, default=0.3)
+    ap.add_argument("--exchange", default="peer", choices=["peer", "nccl"],
+                    help="N>1: fused partition + peer stores over NVLink (CUDA IPC), or partition + NCCL all-to-all")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-cpu", action="store_true")
     args = ap.parse_args()

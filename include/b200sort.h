@@ -159,6 +159,27 @@ int b200_partition_device(const void* dev_src, void* dev_dst, size_t n, const b2
                           uint64_t* part_counts_out, const b200_sort_opts* opts);
 
 /*
+ * Fused partition + exchange: as b200_partition_device, but part g is written to its own
+ * destination pointer dst_ptrs[g] (HOST array of `parts` device pointers, each already offset to
+ * where this rank's records start in that destination).  The pointers may be peer GPUs' buffers
+ * mapped through CUDA IPC: the partition kernel then stores its staged runs straight over
+ * NVLink, which removes the separate all-to-all and one local read + write.
+ * Records must be a multiple of 4 bytes.  The caller orders the kernels of different ranks
+ * (a stream-ordered collective before and after).
+ */
+int b200_partition_peers_device(const void* dev_src, void* const* dst_ptrs, size_t n, const b200_key_desc* desc,
+                                uint32_t level, const uint64_t* counts, const uint32_t* split, uint32_t parts,
+                                uint64_t* part_counts_out, const b200_sort_opts* opts);
+
+/* CUDA IPC helpers for the one-process-per-GPU exchange: allocate a shareable device buffer and
+ * its 64-byte handle; open / close a peer's handle; free. */
+#define B200_IPC_HANDLE_BYTES 64
+int b200_ipc_alloc(void** dev_ptr, size_t bytes, void* handle_out);
+int b200_ipc_open(const void* handle, void** dev_ptr);
+int b200_ipc_close(void* dev_ptr);
+int b200_ipc_free(void* dev_ptr);
+
+/*
  * RadixKey::get_level evaluated on the host through the descriptor — lets the
  * binding validate a user key against its lowering before launching.
  * Returns the digit (0..255) or a negative error code.

@@ -119,6 +119,25 @@ SYMBOLS = {
             C.POINTER(SortOpts),
         ],
     ),
+    "b200_partition_peers_device": (
+        C.c_int,
+        [
+            C.c_void_p,
+            C.POINTER(C.c_void_p),
+            C.c_size_t,
+            C.POINTER(KeyDesc),
+            C.c_uint32,
+            C.POINTER(C.c_uint64),
+            C.POINTER(C.c_uint32),
+            C.c_uint32,
+            C.POINTER(C.c_uint64),
+            C.POINTER(SortOpts),
+        ],
+    ),
+    "b200_ipc_alloc": (C.c_int, [C.POINTER(C.c_void_p), C.c_size_t, C.c_void_p]),
+    "b200_ipc_open": (C.c_int, [C.c_void_p, C.POINTER(C.c_void_p)]),
+    "b200_ipc_close": (C.c_int, [C.c_void_p]),
+    "b200_ipc_free": (C.c_int, [C.c_void_p]),
     "b200_get_level": (C.c_int, [C.c_void_p, C.POINTER(KeyDesc), C.c_uint32]),
     "b200_host_alloc": (C.c_int, [C.POINTER(C.c_void_p), C.c_size_t]),
     "b200_host_free": (C.c_int, [C.c_void_p]),

@@ -143,7 +143,8 @@ constexpr size_t SMALL_BASE_OFF = size_t(MAX_LEVELS) * RADIX * 8;
 constexpr size_t SMALL_TICKET_OFF = SMALL_BASE_OFF + size_t(MAX_LEVELS) * RADIX * 8;
 constexpr size_t SMALL_REMAP_OFF = SMALL_TICKET_OFF + 1024;
 constexpr size_t SMALL_PBASE_OFF = SMALL_REMAP_OFF + 256;
-constexpr size_t SMALL_BYTES = SMALL_PBASE_OFF + RADIX * 8;
+constexpr size_t SMALL_DTAB_OFF = SMALL_PBASE_OFF + RADIX * 8;
+constexpr size_t SMALL_BYTES = SMALL_DTAB_OFF + RADIX * 8;
 
 constexpr int MAX_DEVICES = 64;
 DeviceCtx g_ctx[MAX_DEVICES];
@@ -292,7 +293,7 @@ int plan_pass(DeviceCtx& c, const Lowered& lo, uint64_t n, const void* a, const 
 
 int launch_pass(DeviceCtx& c, cudaStream_t st, const PassPlan& pp, const Lowered& lo, const void* src, void* dst,
                 uint64_t n, uint32_t level, const uint64_t* d_base, uint32_t* d_ticket, uint32_t tag,
-                const uint8_t* d_remap) {
+                const uint8_t* d_remap, const uint64_t* d_dst_tab = nullptr) {
     if (pp.word_path) {
         PassParams p;
         p.src = static_cast<const uint32_t*>(src);
@@ -305,6 +306,7 @@ int launch_pass(DeviceCtx& c, cudaStream_t st, const PassPlan& pp, const Lowered
         p.tag = tag;
         p.num_tiles = pp.num_tiles;
         p.remap = d_remap;
+        p.dst_tab = d_dst_tab;
         pp.pl.kernel<<<pp.grid, pp.pl.threads, pp.pl.smem, st>>>(p);
     } else {
         BytePassParams p;
@@ -635,7 +637,7 @@ int b200_histogram_device(const void* dev_ptr, size_t n, const b200_key_desc* de
 
 static int pass_common(const void* dev_src, void* dev_dst, size_t n, const b200_key_desc* desc, uint32_t level,
                        const uint64_t* counts, const uint32_t* split, uint32_t parts, uint64_t* part_counts_out,
-                       const b200_sort_opts* opts) {
+                       const b200_sort_opts* opts, void* const* dst_ptrs = nullptr) {
     Lowered lo;
     int rc = lower_desc(desc, &lo);
     if (rc) return rc;
@@ -659,7 +661,7 @@ static int pass_common(const void* dev_src, void* dev_dst, size_t n, const b200_
         }
         uint64_t run = 0;
         for (int q = 0; q < RADIX; ++q) {
-            h_base[q] = run;
+            h_base[q] = dst_ptrs ? 0 : run;  // with per-part destinations every part starts at its own pointer
             run += pc[q];
         }
         if (part_counts_out)
@@ -672,7 +674,16 @@ static int pass_common(const void* dev_src, void* dev_dst, size_t n, const b200_
         }
     }
     if (n == 0) return B200_OK;
-    if (!dev_src || !dev_dst) return B200_ERR_BAD_ARG;
+    if (!dev_src || (!dev_dst && !dst_ptrs)) return B200_ERR_BAD_ARG;
+    uint64_t h_dtab[RADIX] = {0};
+    if (dst_ptrs) {
+        for (uint32_t q = 0; q < parts; ++q) {
+            if (!dst_ptrs[q]) return B200_ERR_BAD_ARG;
+            h_dtab[q] = reinterpret_cast<uint64_t>(dst_ptrs[q]);
+            if (h_dtab[q] % 16 != 0 && lo.elem_size % 16 == 0) return B200_ERR_BAD_ARG;
+        }
+        dev_dst = dst_ptrs[0];
+    }
     DeviceCtx* c = nullptr;
     rc = get_ctx(opts ? opts->device : -1, &c);
     if (rc) return rc;
@@ -680,8 +691,9 @@ static int pass_common(const void* dev_src, void* dev_dst, size_t n, const b200_
     DeviceGuard guard(c->dev);
     cudaStream_t st = (opts && opts->stream) ? static_cast<cudaStream_t>(opts->stream) : c->stream;
     PassPlan pp{};
-    rc = plan_pass(*c, lo, n, dev_src, dev_dst, remap, opts ? opts->variant : -1, &pp);
+    rc = plan_pass(*c, lo, n, dev_src, dst_ptrs ? dev_src : dev_dst, remap, opts ? opts->variant : -1, &pp);
     if (rc) return rc;
+    if (dst_ptrs && !pp.word_path) return B200_ERR_BAD_DESC;  // per-part destinations need 4-byte-multiple records
     const size_t lb_bytes = size_t(pp.num_tiles) * RADIX * 8;
     rc = ensure_bytes(reinterpret_cast<void**>(&c->d_lookback), &c->lookback_bytes, lb_bytes);
     if (rc) return rc;
@@ -692,7 +704,10 @@ static int pass_common(const void* dev_src, void* dev_dst, size_t n, const b200_
     CUDA_TRY(cudaMemsetAsync(d_ticket, 0, 1024, st));
     CUDA_TRY(cudaMemcpyAsync(d_pbase, h_base, sizeof(h_base), cudaMemcpyHostToDevice, st));
     if (remap) CUDA_TRY(cudaMemcpyAsync(d_remap, h_remap, sizeof(h_remap), cudaMemcpyHostToDevice, st));
-    rc = launch_pass(*c, st, pp, lo, dev_src, dev_dst, n, level, d_pbase, d_ticket, 1, remap ? d_remap : nullptr);
+    uint64_t* d_dtab = reinterpret_cast<uint64_t*>(c->d_small + SMALL_DTAB_OFF);
+    if (dst_ptrs) CUDA_TRY(cudaMemcpyAsync(d_dtab, h_dtab, sizeof(h_dtab), cudaMemcpyHostToDevice, st));
+    rc = launch_pass(*c, st, pp, lo, dev_src, dev_dst, n, level, d_pbase, d_ticket, 1, remap ? d_remap : nullptr,
+                     dst_ptrs ? d_dtab : nullptr);
     if (rc) return rc;
     CUDA_TRY(cudaStreamSynchronize(st));
     return B200_OK;
@@ -710,6 +725,41 @@ int b200_partition_device(const void* dev_src, void* dev_dst, size_t n, const b2
     static const uint32_t none[1] = {256};
     return pass_common(dev_src, dev_dst, n, desc, level, counts, split ? split : none, parts ? parts : 1,
                        part_counts_out, opts);
+}
+
+int b200_partition_peers_device(const void* dev_src, void* const* dst_ptrs, size_t n, const b200_key_desc* desc,
+                                uint32_t level, const uint64_t* counts, const uint32_t* split, uint32_t parts,
+                                uint64_t* part_counts_out, const b200_sort_opts* opts) {
+    if (!dst_ptrs || parts == 0) return B200_ERR_BAD_ARG;
+    if (!split && parts > 1) return B200_ERR_BAD_ARG;
+    static const uint32_t none[1] = {256};
+    return pass_common(dev_src, nullptr, n, desc, level, counts, split ? split : none, parts, part_counts_out, opts,
+                       dst_ptrs);
+}
+
+// ---- CUDA IPC helpers: one process per GPU shares its receive buffer with its peers ----
+int b200_ipc_alloc(void** dev_ptr, size_t bytes, void* handle_out) {
+    if (!dev_ptr || !handle_out) return B200_ERR_BAD_ARG;
+    CUDA_TRY(cudaMalloc(dev_ptr, bytes ? bytes : 256));
+    cudaIpcMemHandle_t h;
+    CUDA_TRY(cudaIpcGetMemHandle(&h, *dev_ptr));
+    memcpy(handle_out, &h, sizeof(h));
+    return B200_OK;
+}
+int b200_ipc_open(const void* handle, void** dev_ptr) {
+    if (!handle || !dev_ptr) return B200_ERR_BAD_ARG;
+    cudaIpcMemHandle_t h;
+    memcpy(&h, handle, sizeof(h));
+    CUDA_TRY(cudaIpcOpenMemHandle(dev_ptr, h, cudaIpcMemLazyEnablePeerAccess));
+    return B200_OK;
+}
+int b200_ipc_close(void* dev_ptr) {
+    if (dev_ptr) CUDA_TRY(cudaIpcCloseMemHandle(dev_ptr));
+    return B200_OK;
+}
+int b200_ipc_free(void* dev_ptr) {
+    if (dev_ptr) CUDA_TRY(cudaFree(dev_ptr));
+    return B200_OK;
 }
 
 int b200_get_level(const void* record, const b200_key_desc* desc, uint32_t level) {

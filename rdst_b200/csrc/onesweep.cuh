@@ -31,6 +31,8 @@ struct PassParams {
     uint32_t tag;                 // pass tag, 1..255
     uint32_t num_tiles;
     const uint8_t* remap;         // optional 256 -> part table (range partition); nullptr = identity
+    const uint64_t* dst_tab;      // optional, with remap: [256] destination base pointer per part
+                                  // (peer GPUs' buffers for the fused partition + exchange)
 };
 
 template <int WORDS>

@@ -17,7 +17,7 @@ struct Or16Smem {
     static constexpr size_t OUT_BYTES = size_t(TILE) * WORDS * 4;
     static constexpr int GROUPS = THREADS / 16;
     static constexpr size_t SLOT_BYTES = size_t(GROUPS) * RADIX * 4;
-    static constexpr size_t GOFS_BYTES = RADIX * 8;
+    static constexpr size_t GOFS_BYTES = RADIX * 8 * 2;
     static constexpr size_t MISC_BYTES = 128;
     static constexpr size_t TOTAL = OUT_BYTES + SLOT_BYTES + GOFS_BYTES + MISC_BYTES;
 };
@@ -35,6 +35,7 @@ __global__ void __launch_bounds__(THREADS, MINB) lsd_pass_or16_kernel(const Pass
     uint32_t* s_out = reinterpret_cast<uint32_t*>(smem_raw);
     uint8_t* s_slot_raw = smem_raw + SM::OUT_BYTES;
     uint64_t* s_gofs = reinterpret_cast<uint64_t*>(smem_raw + SM::OUT_BYTES + SM::SLOT_BYTES);
+    uint64_t* s_gptr = s_gofs + RADIX;  // REMAP only: per-part destination base pointers
     uint8_t* misc = smem_raw + SM::OUT_BYTES + SM::SLOT_BYTES + SM::GOFS_BYTES;
     volatile uint32_t* s_tile = reinterpret_cast<volatile uint32_t*>(misc);  // [0] first, [1] next tile id
     uint32_t* s_wtot = reinterpret_cast<uint32_t*>(misc + 32);  // 8 digit-warp totals
@@ -197,7 +198,15 @@ __global__ void __launch_bounds__(THREADS, MINB) lsd_pass_or16_kernel(const Pass
                 }
                 lb_store(&p.lookback[uint64_t(tile) * RADIX + tid], lb_pack(LB_PREFIX, p.tag, excl + cnt));
             }
-            s_gofs[tid] = p.bucket_base[tid] + excl - local_off;
+            if (REMAP && p.dst_tab) {
+                // range partition with per-part destinations (possibly peer GPUs over NVLink):
+                // keep a record index relative to the part's own base pointer
+                s_gofs[tid] = p.bucket_base[tid] + excl - local_off;
+                s_gptr[tid] = p.dst_tab[tid];
+            } else {
+                s_gofs[tid] = p.bucket_base[tid] + excl - local_off;
+                if (REMAP) s_gptr[tid] = reinterpret_cast<uint64_t>(p.dst);
+            }
         }
         __syncthreads();  // (D)
 
@@ -210,14 +219,14 @@ __global__ void __launch_bounds__(THREADS, MINB) lsd_pass_or16_kernel(const Pass
                     const Rec<WORDS> x = load_rec<WORDS>(s_out, i);
                     uint32_t d = rec_digit<WORDS, FLOATK>(dp, x);
                     if (REMAP) d = p.remap[d];
-                    store_rec<WORDS>(p.dst, s_gofs[d] + i, x);
+                    store_rec<WORDS>(REMAP ? reinterpret_cast<uint32_t*>(s_gptr[d]) : p.dst, s_gofs[d] + i, x);
                 }
             } else {
                 for (uint32_t i = tid; i < valid; i += THREADS) {
                     const Rec<WORDS> x = load_rec<WORDS>(s_out, i);
                     uint32_t d = rec_digit<WORDS, FLOATK>(dp, x);
                     if (REMAP) d = p.remap[d];
-                    store_rec<WORDS>(p.dst, s_gofs[d] + i, x);
+                    store_rec<WORDS>(REMAP ? reinterpret_cast<uint32_t*>(s_gptr[d]) : p.dst, s_gofs[d] + i, x);
                 }
             }
         } else {
@@ -228,7 +237,7 @@ __global__ void __launch_bounds__(THREADS, MINB) lsd_pass_or16_kernel(const Pass
                 const uint32_t sw = FLOATK ? s_out[pos * WORDS + dp.sign_word] : 0u;
                 uint32_t d = digit_from_words<FLOATK>(dp, kw, sw);
                 if (REMAP) d = p.remap[d];
-                p.dst[(s_gofs[d] + pos) * WORDS + k] = s_out[wi];
+                (REMAP ? reinterpret_cast<uint32_t*>(s_gptr[d]) : p.dst)[(s_gofs[d] + pos) * WORDS + k] = s_out[wi];
             }
         }
         // barriers (B)..(C) of the next iteration order this write-out before the next scatter

@@ -111,6 +111,19 @@ class CudaEngine:
         self.launches += 1
         return np.array(list(pc), dtype=np.int64)
 
+    def partition_peers(self, src, dst_ptrs, n, level, row, split, parts):
+        o = self._opts()
+        pc = (C.c_uint64 * parts)()
+        row = np.ascontiguousarray(row, dtype=np.uint64)
+        split = np.ascontiguousarray(split, dtype=np.uint32)
+        ptrs = (C.c_void_p * parts)(*[C.c_void_p(int(x)) for x in dst_ptrs])
+        _abi.check(self.lib.b200_partition_peers_device(src.data_ptr(), ptrs, n, C.byref(self.desc), level,
+                                                        row.ctypes.data_as(C.POINTER(C.c_uint64)),
+                                                        split.ctypes.data_as(C.POINTER(C.c_uint32)), parts, pc,
+                                                        C.byref(o)))
+        self.launches += 1
+        return np.array(list(pc), dtype=np.int64)
+
     def sort(self, buf, n, tmp=None):
         o = self._opts()
         st = _abi.Stats()
@@ -132,6 +145,65 @@ class CudaEngine:
                                input_split_sizes=[int(x) for x in send_counts], group=group)
 
 
+class PeerBuffers:
+    """Receive buffers shared between the ranks of one box through CUDA IPC, so that the
+    partition kernel of every rank can store its runs straight into the owners' buffers over
+    NVLink (fused partition + all-to-all).  One cudaMalloc per rank, handles all-gathered once."""
+
+    def __init__(self, capacity_bytes: int, group=None):
+        import torch
+        import torch.distributed as dist
+
+        self.torch, self.group = torch, group
+        self.lib = _abi.lib()
+        self.world, self.rank = dist.get_world_size(group), dist.get_rank(group)
+        self.capacity = int(capacity_bytes)
+        ptr = C.c_void_p()
+        handle = (C.c_uint8 * 64)()
+        _abi.check(self.lib.b200_ipc_alloc(C.byref(ptr), self.capacity, handle))
+        self.local_ptr = ptr.value
+        mine = torch.tensor(list(handle), dtype=torch.uint8, device="cuda")
+        allh = [torch.empty_like(mine) for _ in range(self.world)]
+        dist.all_gather(allh, mine, group=group)
+        self.ptrs = []
+        for r in range(self.world):
+            if r == self.rank:
+                self.ptrs.append(self.local_ptr)
+                continue
+            hb = (C.c_uint8 * 64)(*allh[r].cpu().tolist())
+            pp = C.c_void_p()
+            _abi.check(self.lib.b200_ipc_open(hb, C.byref(pp)))
+            self.ptrs.append(pp.value)
+        self._flag = torch.zeros(1, dtype=torch.int32, device="cuda")
+        # a flat uint8 view of the local buffer for the local sort / the caller
+        self.local = _device_view(torch, self.local_ptr, self.capacity)
+
+    def fence(self):
+        """Stream-ordered barrier across ranks: a tiny all-reduce completes on a rank's stream
+        only when every rank's stream has reached it."""
+        import torch.distributed as dist
+
+        dist.all_reduce(self._flag, group=self.group)
+
+    def close(self):
+        for r, p in enumerate(self.ptrs):
+            if r != self.rank and p:
+                self.lib.b200_ipc_close(p)
+        self.lib.b200_ipc_free(self.local_ptr)
+        self.ptrs = []
+
+
+def _device_view(torch, ptr, nbytes):
+    """torch uint8 tensor over raw device memory (no ownership)."""
+
+    class _Holder:
+        pass
+
+    h = _Holder()
+    h.__cuda_array_interface__ = {"shape": (nbytes,), "typestr": "|u1", "data": (ptr, False), "version": 3}
+    return torch.as_tensor(h, device="cuda")
+
+
 # --------------------------------------------------------------------------- the sort
 def sharded_sort(local, n_local: int, key: RadixKey, engine=None, group=None, recv_slack: float = 1.3,
                  scratch=None, timings=None):
@@ -149,6 +221,10 @@ def sharded_sort(local, n_local: int, key: RadixKey, engine=None, group=None, re
             timings["local"] = st
         return local, n_local
 
+    ev = None
+    if timings is not None and hasattr(eng, "torch"):
+        ev = [eng.torch.cuda.Event(enable_timing=True) for _ in range(5)]
+        ev[0].record()
     # 1. K1 on the local shard, all levels in one read
     hist = eng.histogram(local, n_local)
     # 2. global histogram + every rank's rows: one small all-gather ([P, L, 256] i64)
@@ -166,18 +242,48 @@ def sharded_sort(local, n_local: int, key: RadixKey, engine=None, group=None, re
     send_counts, recv_counts = m[rank], m[:, rank]
     n_recv = int(recv_counts.sum())
     # 4. stable local partition into P contiguous send regions, then the all-to-all
-    part = scratch["part"] if scratch else eng.empty(n_local)
-    cap = int(max(n_recv, 1))
-    recv = scratch["recv"] if scratch else eng.empty(cap)
-    if recv.numel() < n_recv * key.elem_size:
-        raise _abi.B200SortError(5, f"receive buffer too small for {n_recv} records (skewed splitters)")
-    pc = eng.partition(local, part, n_local, level, hist[level], split, world)
-    assert np.array_equal(pc, send_counts), "partition counts disagree with the gathered histograms"
-    eng.exchange(part, recv, send_counts, recv_counts, group)
+    fused = bool(scratch and scratch.get("peers") is not None)
+    part = recv = None
+    if not fused:
+        part = scratch["part"] if scratch else eng.empty(n_local)
+        recv = scratch["recv"] if scratch else eng.empty(int(max(n_recv, 1)))
+        if recv.numel() < n_recv * key.elem_size:
+            raise _abi.B200SortError(5, f"receive buffer too small for {n_recv} records (skewed splitters)")
+    peers = scratch.get("peers") if scratch else None
+    if ev:
+        ev[1].record()
+    if peers is not None:
+        # fused: this rank's records for rank g start, in g's buffer, after those of the lower ranks
+        if peers.capacity < n_recv * key.elem_size:
+            raise _abi.B200SortError(5, f"peer receive buffer too small for {n_recv} records")
+        starts = np.concatenate([np.zeros((1, world), dtype=np.int64), np.cumsum(m, axis=0)])[rank]  # [g]
+        dst = [peers.ptrs[g] + int(starts[g]) * key.elem_size for g in range(world)]
+        peers.fence()  # every rank is done with the previous contents of its receive buffer
+        pc = eng.partition_peers(local, dst, n_local, level, hist[level], split, world)
+        assert np.array_equal(pc, send_counts), "partition counts disagree with the gathered histograms"
+        if ev:
+            ev[2].record()
+        peers.fence()  # every rank's partition kernel has finished: the received range is complete
+        recv = peers.local
+        if ev:
+            ev[3].record()
+    else:
+        pc = eng.partition(local, part, n_local, level, hist[level], split, world)
+        assert np.array_equal(pc, send_counts), "partition counts disagree with the gathered histograms"
+        if ev:
+            ev[2].record()
+        eng.exchange(part, recv, send_counts, recv_counts, group)
+        if ev:
+            ev[3].record()
     # 5. independent local LSD sort of the received range (levels above `level` are
     #    single-bucket per rank only by luck; K1 decides what to skip)
     st = eng.sort(recv, n_recv, scratch.get("tmp") if scratch else None)
     if timings is not None:
         timings.update({"level": level, "split": split.tolist(), "n_recv": n_recv, "local": st,
                         "sent_bytes": int((send_counts.sum() - send_counts[rank]) * key.elem_size)})
+        if ev:
+            ev[4].record()
+            ev[4].synchronize()
+            timings["phase_ms"] = {"hist_allgather_plan": ev[0].elapsed_time(ev[1]), "partition": ev[1].elapsed_time(ev[2]),
+                                   "all_to_all": ev[2].elapsed_time(ev[3]), "local_sort": ev[3].elapsed_time(ev[4])}
     return recv, n_recv

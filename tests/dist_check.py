@@ -35,12 +35,15 @@ def main():
     torch.cuda.set_device(int(os.environ["LOCAL_RANK"]))
     dist.init_process_group("nccl", device_id=torch.device("cuda", int(os.environ["LOCAL_RANK"])))
     ok = True
+    from rdst_b200.dist import PeerBuffers
+
+    peers = PeerBuffers(64 << 20) if os.environ.get("DIST_CHECK_MODE", "nccl") == "peer" else None
     for name, key, full in cases():
         es = key.elem_size
         n = len(full) // es
         lo, hi = rank * n // world, (rank + 1) * n // world
         shard = torch.from_numpy(full[lo * es: hi * es].copy()).cuda()
-        out, n_out = sharded_sort(shard, hi - lo, key)
+        out, n_out = sharded_sort(shard, hi - lo, key, scratch={"peers": peers} if peers else None)
         torch.cuda.synchronize()
         mine = out[: n_out * es].cpu()
         sizes = [torch.zeros(1, dtype=torch.int64, device="cuda") for _ in range(world)]
@@ -55,9 +58,11 @@ def main():
             got = torch.cat(bufs).cpu().numpy().tobytes()
             exp = o.stable_sorted(full, key).tobytes()
             good = got == exp
-            print(f"[dist_check] {name}: {'ok' if good else 'MISMATCH'} sizes={[s // es for s in sizes]}", flush=True)
+            print(f"[dist_check] {'peer' if peers else 'nccl'} {name}: {'ok' if good else 'MISMATCH'} sizes={[s // es for s in sizes]}", flush=True)
             ok = ok and good
     dist.barrier()
+    if peers:
+        peers.close()
     dist.destroy_process_group()
     sys.exit(0 if ok else 1)
 

@@ -9,7 +9,10 @@ pytestmark = pytest.mark.gpu
 HERE = os.path.dirname(os.path.abspath(__file__))
 
 
-def test_sharded_sort_nccl_matches_oracle():
+@pytest.mark.parametrize("mode", ["nccl", "peer"])
+def test_sharded_sort_matches_oracle(mode):
+    """nccl: partition + all_to_all_single; peer: fused partition kernel storing into the peers'
+    IPC-mapped receive buffers over NVLink."""
     import torch
 
     n = torch.cuda.device_count()
@@ -18,7 +21,7 @@ def test_sharded_sort_nccl_matches_oracle():
     world = 2 if n < 4 else 4
     cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", f"--nproc-per-node={world}",
            "--master-addr", "127.0.0.1", "--master-port", "29641", os.path.join(HERE, "dist_check.py")]
-    r = subprocess.run(cmd, capture_output=True, text=True, timeout=600)
+    r = subprocess.run(cmd, capture_output=True, text=True, timeout=600, env=dict(os.environ, DIST_CHECK_MODE=mode))
     sys.stdout.write(r.stdout[-3000:])
     assert r.returncode == 0, r.stderr[-3000:]
     assert "MISMATCH" not in r.stdout
