@@ -331,11 +331,6 @@ int launch_pass(DeviceCtx& c, cudaStream_t st, const PassPlan& pp, const Lowered
 }
 
 // ---- K1 dispatch (instantiations live in hist_w*.cu) ----
-bool hist_agg_enabled() {
-    const char* env = getenv("B200SORT_HIST_AGG");
-    return env ? atoi(env) != 0 : false;
-}
-
 // Fills d_hist [levels][256] (u64) on the stream.
 int launch_histogram(DeviceCtx& c, cudaStream_t st, const Lowered& lo, const void* src, uint64_t n,
                      unsigned long long* d_hist) {
@@ -355,19 +350,19 @@ int launch_histogram(DeviceCtx& c, cudaStream_t st, const Lowered& lo, const voi
         hp.n = n;
         hp.kw0 = lo.key_offset / 4;
         hp.sign_shift = ((lo.levels - 1) % 4) * 8 + 7;
-        for (uint32_t l = 0; l < 16; ++l) hp.xor_mask[l] = l < lo.levels ? lo.lv[l].xor_mask : 0u;
+        for (uint32_t w = 0; w < 4; ++w) hp.xorw[w] = 0u;
+        for (uint32_t l = 0; l < lo.levels && l < 16; ++l) hp.xorw[l / 4] |= (lo.lv[l].xor_mask & 0xffu) << (8 * (l % 4));
         hp.ghist = d_hist;
         const uint64_t per_thread = 8;
         const int grid =
             int(std::max<uint64_t>(1, std::min<uint64_t>(grid_full, (n + HIST_THREADS * per_thread - 1) /
                                                                          (HIST_THREADS * per_thread))));
         bool ok = false;
-        const bool agg = hist_agg_enabled();
         switch (words) {
-            case 1: ok = launch_hist_fast_w1(lo.levels, lo.is_float, agg, grid, st, hp); break;
-            case 2: ok = launch_hist_fast_w2(lo.levels, lo.is_float, agg, grid, st, hp); break;
-            case 3: ok = launch_hist_fast_w3(lo.levels, lo.is_float, agg, grid, st, hp); break;
-            case 4: ok = launch_hist_fast_w4(lo.levels, lo.is_float, agg, grid, st, hp); break;
+            case 1: ok = launch_hist_fast_w1(lo.levels, lo.is_float, grid, st, hp); break;
+            case 2: ok = launch_hist_fast_w2(lo.levels, lo.is_float, grid, st, hp); break;
+            case 3: ok = launch_hist_fast_w3(lo.levels, lo.is_float, grid, st, hp); break;
+            case 4: ok = launch_hist_fast_w4(lo.levels, lo.is_float, grid, st, hp); break;
         }
         if (ok) {
             CUDA_TRY(cudaGetLastError());

@@ -6,27 +6,20 @@
 
 namespace b200 {
 template <int WORDS, int L>
-void launch_hist_fast2(bool floatk, bool agg, int grid, cudaStream_t st, const HistParams& hp) {
-    if (floatk) {
-        if (agg)
-            hist_fast_kernel<WORDS, L, true, true><<<grid, HIST_THREADS, 0, st>>>(hp);
-        else
-            hist_fast_kernel<WORDS, L, true, false><<<grid, HIST_THREADS, 0, st>>>(hp);
-    } else {
-        if (agg)
-            hist_fast_kernel<WORDS, L, false, true><<<grid, HIST_THREADS, 0, st>>>(hp);
-        else
-            hist_fast_kernel<WORDS, L, false, false><<<grid, HIST_THREADS, 0, st>>>(hp);
-    }
+void launch_hist_fast2(bool floatk, int grid, cudaStream_t st, const HistParams& hp) {
+    if (floatk)
+        hist_fast_kernel<WORDS, L, true><<<grid, HIST_THREADS, 0, st>>>(hp);
+    else
+        hist_fast_kernel<WORDS, L, false><<<grid, HIST_THREADS, 0, st>>>(hp);
 }
 
 template <int WORDS>
-bool launch_hist_fast1(uint32_t L, bool floatk, bool agg, int grid, cudaStream_t st, const HistParams& hp) {
+bool launch_hist_fast1(uint32_t L, bool floatk, int grid, cudaStream_t st, const HistParams& hp) {
     switch (L) {
 #define B200_HCASE(LL)                                                   \
     case LL:                                                             \
         if constexpr ((LL + 3) / 4 <= WORDS) {                           \
-            launch_hist_fast2<WORDS, LL>(floatk, agg, grid, st, hp);     \
+            launch_hist_fast2<WORDS, LL>(floatk, grid, st, hp);     \
             return true;                                                 \
         }                                                                \
         return false;

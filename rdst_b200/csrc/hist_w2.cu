@@ -1,6 +1,6 @@
 #include "hist_inst.cuh"
 namespace b200 {
-bool launch_hist_fast_w2(uint32_t L, bool floatk, bool agg, int grid, cudaStream_t st, const HistParams& hp) {
-    return launch_hist_fast1<2>(L, floatk, agg, grid, st, hp);
+bool launch_hist_fast_w2(uint32_t L, bool floatk, int grid, cudaStream_t st, const HistParams& hp) {
+    return launch_hist_fast1<2>(L, floatk, grid, st, hp);
 }
 }  // namespace b200

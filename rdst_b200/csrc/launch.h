@@ -17,8 +17,8 @@ PassLaunch get_pass_launch_w2(bool floatk, bool remap, int variant);
 PassLaunch get_pass_launch_w3(bool floatk, bool remap, int variant);
 PassLaunch get_pass_launch_w4(bool floatk, bool remap, int variant);
 struct HistParams;
-bool launch_hist_fast_w1(uint32_t L, bool floatk, bool agg, int grid, cudaStream_t st, const HistParams& hp);
-bool launch_hist_fast_w2(uint32_t L, bool floatk, bool agg, int grid, cudaStream_t st, const HistParams& hp);
-bool launch_hist_fast_w3(uint32_t L, bool floatk, bool agg, int grid, cudaStream_t st, const HistParams& hp);
-bool launch_hist_fast_w4(uint32_t L, bool floatk, bool agg, int grid, cudaStream_t st, const HistParams& hp);
+bool launch_hist_fast_w1(uint32_t L, bool floatk, int grid, cudaStream_t st, const HistParams& hp);
+bool launch_hist_fast_w2(uint32_t L, bool floatk, int grid, cudaStream_t st, const HistParams& hp);
+bool launch_hist_fast_w3(uint32_t L, bool floatk, int grid, cudaStream_t st, const HistParams& hp);
+bool launch_hist_fast_w4(uint32_t L, bool floatk, int grid, cudaStream_t st, const HistParams& hp);
 }  // namespace b200

@@ -54,6 +54,9 @@ static PassLaunch pick_launch(int v) {
         case 13: return make_launch<WORDS, FLOATK, REMAP, 13>();
         case 14: return make_launch<WORDS, FLOATK, REMAP, 14>();
         case 15: return make_launch<WORDS, FLOATK, REMAP, 15>();
+        case 16: return make_launch<WORDS, FLOATK, REMAP, 16>();
+        case 17: return make_launch<WORDS, FLOATK, REMAP, 17>();
+        case 18: return make_launch<WORDS, FLOATK, REMAP, 18>();
         default: break;
     }
     PassLaunch none{};

@@ -17,7 +17,7 @@ struct Or16Smem {
     static constexpr size_t OUT_BYTES = size_t(TILE) * WORDS * 4;
     static constexpr int GROUPS = THREADS / 16;
     static constexpr size_t SLOT_BYTES = size_t(GROUPS) * RADIX * 4;
-    static constexpr size_t GOFS_BYTES = RADIX * 8 * 2;
+    static constexpr size_t GOFS_BYTES = RADIX * 8 * 2 + RADIX * 4;  // u64 offsets, REMAP pointers, u32 offsets
     static constexpr size_t MISC_BYTES = 128;
     static constexpr size_t TOTAL = OUT_BYTES + SLOT_BYTES + GOFS_BYTES + MISC_BYTES;
 };
@@ -30,12 +30,15 @@ __global__ void __launch_bounds__(THREADS, MINB) lsd_pass_or16_kernel(const Pass
     static_assert(SM::TILE <= 65536, "16-bit positions");
     constexpr int TILE = SM::TILE;
     constexpr int LB_BATCH = 4;
+    constexpr int RBITS = (16 * ITEMS <= 256) ? 8 : 16, RPR = 32 / RBITS;
+    constexpr uint32_t RMASK = (1u << RBITS) - 1u;
 
     extern __shared__ __align__(128) uint8_t smem_raw[];
     uint32_t* s_out = reinterpret_cast<uint32_t*>(smem_raw);
     uint8_t* s_slot_raw = smem_raw + SM::OUT_BYTES;
     uint64_t* s_gofs = reinterpret_cast<uint64_t*>(smem_raw + SM::OUT_BYTES + SM::SLOT_BYTES);
     uint64_t* s_gptr = s_gofs + RADIX;  // REMAP only: per-part destination base pointers
+    uint32_t* s_gofs32 = reinterpret_cast<uint32_t*>(s_gptr + RADIX);  // offsets mod 2^32 (n < 2^32)
     uint8_t* misc = smem_raw + SM::OUT_BYTES + SM::SLOT_BYTES + SM::GOFS_BYTES;
     volatile uint32_t* s_tile = reinterpret_cast<volatile uint32_t*>(misc);  // [0] first, [1] next tile id
     uint32_t* s_wtot = reinterpret_cast<uint32_t*>(misc + 32);  // 8 digit-warp totals
@@ -92,7 +95,10 @@ __global__ void __launch_bounds__(THREADS, MINB) lsd_pass_or16_kernel(const Pass
         const bool full = valid == uint32_t(TILE);
 
         // ---- rank inside the warp by OR-matching; stable: lanes in order, rounds in order ----
-        uint32_t rank[ITEMS];
+        // ranks inside the half-warp group are < 16 * ITEMS: packed 4 (or 2) per register
+        uint32_t rk[(ITEMS + RPR - 1) / RPR];
+#pragma unroll
+        for (int q = 0; q < (ITEMS + RPR - 1) / RPR; ++q) rk[q] = 0;
 #pragma unroll
         for (int j = 0; j < ITEMS; ++j) {
             const uint32_t e = e0 + j * 16;
@@ -110,16 +116,20 @@ __global__ void __launch_bounds__(THREADS, MINB) lsd_pass_or16_kernel(const Pass
             const uint32_t lt = m & lt_mask;
             if (lt == 0) sts_u32(sa, (c + __popc(m)) << 16);
             __syncwarp();
-            rank[j] = c + __popc(lt);
+            rk[j / RPR] |= (c + __popc(lt)) << ((j % RPR) * RBITS);
         }
         __syncthreads();  // (B) every warp's counts final, masks back to zero
 
         // ---- one thread per digit: tile count, publish, local bases ----
         uint32_t sum = 0, incl = 0, cnt = 0;
+        uint32_t gc[GROUPS];  // this digit's count in every half-warp group (read once)
         if (tid < RADIX) {
             const uint32_t ca = slot_base + uint32_t(tid) * 4;
 #pragma unroll
-            for (int w = 0; w < GROUPS; ++w) sum += lds_u32(ca + w * RADIX * 4) >> 16;
+            for (int w = 0; w < GROUPS; ++w) {
+                gc[w] = lds_u32(ca + w * RADIX * 4) >> 16;
+                sum += gc[w];
+            }
             cnt = sum;
             if (tid == RADIX - 1) cnt -= uint32_t(TILE) - valid;
             lb_store(&p.lookback[uint64_t(tile) * RADIX + tid], lb_pack(tile == 0 ? LB_PREFIX : LB_AGG, p.tag, cnt));
@@ -139,14 +149,13 @@ __global__ void __launch_bounds__(THREADS, MINB) lsd_pass_or16_kernel(const Pass
             for (int w = 0; w < RADIX / 32; ++w)
                 if (w < warp) wbase += s_wtot[w];
             local_off = wbase + incl - sum;
-            // slot count := position of the (warp, digit) group inside the locally sorted tile
+            // slot count := position of the (group, digit) run inside the locally sorted tile
             const uint32_t ca = slot_base + uint32_t(tid) * 4;
             uint32_t run = local_off;
 #pragma unroll
             for (int w = 0; w < GROUPS; ++w) {
-                const uint32_t c = lds_u32(ca + w * RADIX * 4) >> 16;
                 sts_u32(ca + w * RADIX * 4, run << 16);
-                run += c;
+                run += gc[w];
             }
         }
         __syncthreads();  // (C)
@@ -160,7 +169,7 @@ __global__ void __launch_bounds__(THREADS, MINB) lsd_pass_or16_kernel(const Pass
                 d = rec_digit<WORDS, FLOATK>(dp, r[j]);
                 if (REMAP) d = p.remap[d];
             }
-            const uint32_t pos = (lds_u32(my_slots + d * 4) >> 16) + rank[j];
+            const uint32_t pos = (lds_u32(my_slots + d * 4) >> 16) + ((rk[j / RPR] >> ((j % RPR) * RBITS)) & RMASK);
             store_rec<WORDS>(s_out, pos, r[j]);
         }
         const uint32_t next_tile = s_tile[1];
@@ -180,6 +189,7 @@ __global__ void __launch_bounds__(THREADS, MINB) lsd_pass_or16_kernel(const Pass
                 int64_t t = int64_t(tile) - 1;
                 bool done = false;
                 while (!done) {
+                    const int64_t t_before = t;
                     uint64_t v[LB_BATCH];
 #pragma unroll
                     for (int b = 0; b < LB_BATCH; ++b) {
@@ -195,6 +205,7 @@ __global__ void __launch_bounds__(THREADS, MINB) lsd_pass_or16_kernel(const Pass
                         --t;
                         if (st == LB_PREFIX) done = true;
                     }
+                    if (!done && t == t_before) __nanosleep(64);  // predecessor not published yet: back off
                 }
                 lb_store(&p.lookback[uint64_t(tile) * RADIX + tid], lb_pack(LB_PREFIX, p.tag, excl + cnt));
             }
@@ -204,7 +215,9 @@ __global__ void __launch_bounds__(THREADS, MINB) lsd_pass_or16_kernel(const Pass
                 s_gofs[tid] = p.bucket_base[tid] + excl - local_off;
                 s_gptr[tid] = p.dst_tab[tid];
             } else {
-                s_gofs[tid] = p.bucket_base[tid] + excl - local_off;
+                const uint64_t go = p.bucket_base[tid] + excl - local_off;
+                s_gofs[tid] = go;
+                s_gofs32[tid] = uint32_t(go);
                 if (REMAP) s_gptr[tid] = reinterpret_cast<uint64_t>(p.dst);
             }
         }
@@ -212,7 +225,16 @@ __global__ void __launch_bounds__(THREADS, MINB) lsd_pass_or16_kernel(const Pass
 
         // ---- write-out: runs of equal digits are contiguous in s_out and in dst ----
         if constexpr (WORDS == 1 || WORDS == 2 || WORDS == 4) {
-            if (full) {
+            if (!REMAP && full && p.n <= 0xffffffffull) {
+                // record indices fit 32 bits: 32-bit offset table (half the shared-memory wavefronts)
+#pragma unroll 4
+                for (int k = 0; k < ITEMS; ++k) {
+                    const uint32_t i = tid + k * THREADS;
+                    const Rec<WORDS> x = load_rec<WORDS>(s_out, i);
+                    const uint32_t d = rec_digit<WORDS, FLOATK>(dp, x);
+                    store_rec<WORDS>(p.dst, uint64_t(s_gofs32[d] + i), x);
+                }
+            } else if (full) {
 #pragma unroll 4
                 for (int k = 0; k < ITEMS; ++k) {
                     const uint32_t i = tid + k * THREADS;

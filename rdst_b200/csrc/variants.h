@@ -17,7 +17,7 @@ struct VariantInfo {
                    // 2 = half-warp OR-matching kernel (pass_or16.cuh)
 };
 
-constexpr int NUM_VARIANTS = 16;
+constexpr int NUM_VARIANTS = 19;
 
 constexpr VariantInfo kVariants[NUM_VARIANTS] = {
     {"t512_ldg", 512, {16, 16, 12, 8}, false, false, 1, 0},
@@ -36,6 +36,9 @@ constexpr VariantInfo kVariants[NUM_VARIANTS] = {
     {"h256_i12", 256, {12, 12, 8, 6}, false, false, 4, 2},
     {"h384_i18", 384, {18, 12, 8, 6}, false, false, 2, 2},
     {"h256_i24", 256, {24, 20, 12, 10}, false, false, 2, 2},
+    {"h256_i20_occ3", 256, {20, 20, 12, 10}, false, false, 3, 2},
+    {"h256_i24_occ3", 256, {24, 24, 14, 12}, false, false, 3, 2},
+    {"h256_i32_occ2", 256, {32, 32, 20, 16}, false, false, 2, 2},
 };
 
 // Defaults measured on B200 (profiles/r1e_sweep.txt): best variant per record width in words.
