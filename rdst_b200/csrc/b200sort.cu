@@ -233,14 +233,18 @@ PassLaunch get_pass_launch(uint32_t words, bool floatk, bool remap, int variant)
     return PassLaunch{};
 }
 
-int default_variant(uint32_t words, uint64_t n) {
-    (void)n;
+int default_variant(uint32_t words, uint64_t n, int sm_count) {
     const char* env = getenv("B200SORT_VARIANT");
     if (env) {
         int v = atoi(env);
         if (v >= 0 && v < NUM_VARIANTS) return v;
     }
-    return kDefaultVariant[words - 1];
+    // the Tuner's job on the GPU (reference src/tuners/standard_tuner.rs:13-63 picks by input_len):
+    // large tiles amortise the per-tile digit scan, small inputs need enough tiles for every SM
+    const int v = kDefaultVariant[words - 1];
+    const uint64_t big_tile = uint64_t(kVariants[v].threads) * kVariants[v].items[words - 1];
+    if (n < big_tile * uint64_t(sm_count) * 2) return kSmallVariant;
+    return v;
 }
 
 constexpr int BYTE_THREADS = 256, BYTE_ITEMS = 4;
@@ -261,7 +265,7 @@ int plan_pass(DeviceCtx& c, const Lowered& lo, uint64_t n, const void* a, const 
     pp.word_path = word_path_ok(lo, a, b);
     if (pp.word_path) {
         pp.words = lo.elem_size / 4;
-        if (variant < 0) variant = default_variant(pp.words, n);
+        if (variant < 0) variant = default_variant(pp.words, n, c.sm_count);
         if (variant >= NUM_VARIANTS) return B200_ERR_BAD_ARG;
         if (remap) variant = kRemapVariant;
         pp.variant = variant;

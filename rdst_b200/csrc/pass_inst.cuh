@@ -57,6 +57,8 @@ static PassLaunch pick_launch(int v) {
         case 16: return make_launch<WORDS, FLOATK, REMAP, 16>();
         case 17: return make_launch<WORDS, FLOATK, REMAP, 17>();
         case 18: return make_launch<WORDS, FLOATK, REMAP, 18>();
+        case 19: return make_launch<WORDS, FLOATK, REMAP, 19>();
+        case 20: return make_launch<WORDS, FLOATK, REMAP, 20>();
         default: break;
     }
     PassLaunch none{};

@@ -19,7 +19,8 @@ struct Or16Smem {
     static constexpr size_t SLOT_BYTES = size_t(GROUPS) * RADIX * 4;
     static constexpr size_t GOFS_BYTES = RADIX * 8 * 2 + RADIX * 4;  // u64 offsets, REMAP pointers, u32 offsets
     static constexpr size_t MISC_BYTES = 128;
-    static constexpr size_t TOTAL = OUT_BYTES + SLOT_BYTES + GOFS_BYTES + MISC_BYTES;
+    static constexpr size_t PART_BYTES = THREADS >= 2 * RADIX ? size_t(THREADS) * 4 : 0;
+    static constexpr size_t TOTAL = OUT_BYTES + SLOT_BYTES + GOFS_BYTES + MISC_BYTES + PART_BYTES;
 };
 
 template <int WORDS, int THREADS, int ITEMS, bool FLOATK, bool REMAP, int MINB>
@@ -30,6 +31,8 @@ __global__ void __launch_bounds__(THREADS, MINB) lsd_pass_or16_kernel(const Pass
     static_assert(SM::TILE <= 65536, "16-bit positions");
     constexpr int TILE = SM::TILE;
     constexpr int LB_BATCH = 4;
+    constexpr int DSPLIT = (THREADS % RADIX == 0) ? THREADS / RADIX : 1;  // threads per digit in the digit phase
+    constexpr int GPH = GROUPS / DSPLIT;
     constexpr int RBITS = (16 * ITEMS <= 256) ? 8 : 16, RPR = 32 / RBITS;
     constexpr uint32_t RMASK = (1u << RBITS) - 1u;
 
@@ -42,6 +45,7 @@ __global__ void __launch_bounds__(THREADS, MINB) lsd_pass_or16_kernel(const Pass
     uint8_t* misc = smem_raw + SM::OUT_BYTES + SM::SLOT_BYTES + SM::GOFS_BYTES;
     volatile uint32_t* s_tile = reinterpret_cast<volatile uint32_t*>(misc);  // [0] first, [1] next tile id
     uint32_t* s_wtot = reinterpret_cast<uint32_t*>(misc + 32);  // 8 digit-warp totals
+    uint32_t* s_part = reinterpret_cast<uint32_t*>(misc + SM::MISC_BYTES);  // DSPLIT > 1: per-part digit counts
 
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const uint32_t lane_bit = 1u << (lane & 15);
@@ -120,40 +124,58 @@ __global__ void __launch_bounds__(THREADS, MINB) lsd_pass_or16_kernel(const Pass
         }
         __syncthreads();  // (B) every warp's counts final, masks back to zero
 
-        // ---- one thread per digit: tile count, publish, local bases ----
-        uint32_t sum = 0, incl = 0, cnt = 0;
-        uint32_t gc[GROUPS];  // this digit's count in every half-warp group (read once)
-        if (tid < RADIX) {
-            const uint32_t ca = slot_base + uint32_t(tid) * 4;
+        // ---- DSPLIT threads per digit: tile count, publish, local bases ----
+        // thread (digit dg, part h) owns the GPH half-warp groups h*GPH .. of its digit
+        uint32_t sum = 0, incl = 0, cnt = 0, part = 0, before = 0;
+        uint32_t gc[GPH];  // this digit's count in each of my groups (read once)
+        const uint32_t dg = tid & (RADIX - 1), h = tid / RADIX;
+        const bool dthread = tid < RADIX * DSPLIT;
+        if (dthread) {
+            const uint32_t ca = slot_base + (h * GPH * RADIX + dg) * 4;
 #pragma unroll
-            for (int w = 0; w < GROUPS; ++w) {
+            for (int w = 0; w < GPH; ++w) {
                 gc[w] = lds_u32(ca + w * RADIX * 4) >> 16;
-                sum += gc[w];
+                part += gc[w];
+            }
+            if (DSPLIT > 1) s_part[tid] = part;
+        }
+        if (DSPLIT > 1) __syncthreads();  // (B1)
+        if (dthread) {
+            sum = part;
+            if (DSPLIT > 1) {
+                sum = 0;
+#pragma unroll
+                for (int q = 0; q < DSPLIT; ++q) {
+                    const uint32_t x = s_part[q * RADIX + dg];
+                    sum += x;
+                    if (uint32_t(q) < h) before += x;
+                }
             }
             cnt = sum;
-            if (tid == RADIX - 1) cnt -= uint32_t(TILE) - valid;
-            lb_store(&p.lookback[uint64_t(tile) * RADIX + tid], lb_pack(tile == 0 ? LB_PREFIX : LB_AGG, p.tag, cnt));
+            if (dg == RADIX - 1) cnt -= uint32_t(TILE) - valid;
+            if (h == 0)
+                lb_store(&p.lookback[uint64_t(tile) * RADIX + dg], lb_pack(tile == 0 ? LB_PREFIX : LB_AGG, p.tag, cnt));
             incl = sum;
 #pragma unroll
             for (int o = 1; o < 32; o <<= 1) {
                 const uint32_t y = __shfl_up_sync(0xffffffffu, incl, o);
                 if (lane >= o) incl += y;
             }
-            if (lane == 31) s_wtot[warp] = incl;
+            if (h == 0 && lane == 31) s_wtot[warp] = incl;
         }
         __syncthreads();  // (B2)
         uint32_t local_off = 0;
-        if (tid < RADIX) {
+        if (dthread) {
             uint32_t wbase = 0;
 #pragma unroll
             for (int w = 0; w < RADIX / 32; ++w)
-                if (w < warp) wbase += s_wtot[w];
+                if (uint32_t(w) < dg / 32) wbase += s_wtot[w];
             local_off = wbase + incl - sum;
             // slot count := position of the (group, digit) run inside the locally sorted tile
-            const uint32_t ca = slot_base + uint32_t(tid) * 4;
-            uint32_t run = local_off;
+            const uint32_t ca = slot_base + (h * GPH * RADIX + dg) * 4;
+            uint32_t run = local_off + before;
 #pragma unroll
-            for (int w = 0; w < GROUPS; ++w) {
+            for (int w = 0; w < GPH; ++w) {
                 sts_u32(ca + w * RADIX * 4, run << 16);
                 run += gc[w];
             }

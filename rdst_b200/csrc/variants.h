@@ -17,7 +17,7 @@ struct VariantInfo {
                    // 2 = half-warp OR-matching kernel (pass_or16.cuh)
 };
 
-constexpr int NUM_VARIANTS = 19;
+constexpr int NUM_VARIANTS = 21;
 
 constexpr VariantInfo kVariants[NUM_VARIANTS] = {
     {"t512_ldg", 512, {16, 16, 12, 8}, false, false, 1, 0},
@@ -39,10 +39,15 @@ constexpr VariantInfo kVariants[NUM_VARIANTS] = {
     {"h256_i20_occ3", 256, {20, 20, 12, 10}, false, false, 3, 2},
     {"h256_i24_occ3", 256, {24, 24, 14, 12}, false, false, 3, 2},
     {"h256_i32_occ2", 256, {32, 32, 20, 16}, false, false, 2, 2},
+    {"h512_i16_occ2", 512, {16, 16, 10, 8}, false, false, 2, 2},
+    {"h512_i12_occ2", 512, {20, 12, 8, 6}, false, false, 2, 2},
 };
 
-// Defaults measured on B200 (profiles/r1e_sweep.txt): best variant per record width in words.
-constexpr int kDefaultVariant[4] = {14, 12, 6, 12};
-constexpr int kRemapVariant = 12;
+// Defaults measured on B200 (profiles/r1h_sweep_k2_polish.txt, r1i_*): best variant per record
+// width in words for inputs that fill the GPU with large tiles; below kSmallInputTiles tiles of
+// the large variant per SM slot the 4096-record variant keeps every SM busy.
+constexpr int kDefaultVariant[4] = {18, 18, 17, 16};
+constexpr int kSmallVariant = 12;
+constexpr int kRemapVariant = 18;
 
 }  // namespace b200
