@@ -16,8 +16,9 @@ static PassLaunch make_launch() {
     constexpr int ITEMS = vi.items[WORDS - 1];
     PassLaunch pl;
     if constexpr (vi.algo == 2) {
-        using SM = Or16Smem<WORDS, vi.threads, ITEMS>;
-        pl.kernel = &lsd_pass_or16_kernel<WORDS, vi.threads, ITEMS, FLOATK, REMAP, vi.min_blocks>;
+        constexpr int SUB = vi.sub ? vi.sub : 1;
+        using SM = Or16Smem<WORDS, vi.threads, ITEMS, SUB>;
+        pl.kernel = &lsd_pass_or16_kernel<WORDS, vi.threads, ITEMS, FLOATK, REMAP, vi.min_blocks, SUB>;
         pl.smem = SM::TOTAL;
         pl.tile = SM::TILE;
     } else if constexpr (vi.algo == 1) {
@@ -59,6 +60,8 @@ static PassLaunch pick_launch(int v) {
         case 18: return make_launch<WORDS, FLOATK, REMAP, 18>();
         case 19: return make_launch<WORDS, FLOATK, REMAP, 19>();
         case 20: return make_launch<WORDS, FLOATK, REMAP, 20>();
+        case 21: return make_launch<WORDS, FLOATK, REMAP, 21>();
+        case 22: return make_launch<WORDS, FLOATK, REMAP, 22>();
         default: break;
     }
     PassLaunch none{};

@@ -10,12 +10,12 @@
 
 namespace b200 {
 
-template <int WORDS, int THREADS, int ITEMS>
+template <int WORDS, int THREADS, int ITEMS, int SUB = 1>
 struct Or16Smem {
     static constexpr int WARPS = THREADS / 32;
     static constexpr int TILE = THREADS * ITEMS;
     static constexpr size_t OUT_BYTES = size_t(TILE) * WORDS * 4;
-    static constexpr int GROUPS = THREADS / 16;
+    static constexpr int GROUPS = THREADS / 16 * SUB;  // SUB slot tables per half-warp (rounds split in SUB runs)
     static constexpr size_t SLOT_BYTES = size_t(GROUPS) * RADIX * 4;
     static constexpr size_t GOFS_BYTES = RADIX * 8 * 2 + RADIX * 4;  // u64 offsets, REMAP pointers, u32 offsets
     static constexpr size_t MISC_BYTES = 128;
@@ -23,17 +23,19 @@ struct Or16Smem {
     static constexpr size_t TOTAL = OUT_BYTES + SLOT_BYTES + GOFS_BYTES + MISC_BYTES + PART_BYTES;
 };
 
-template <int WORDS, int THREADS, int ITEMS, bool FLOATK, bool REMAP, int MINB>
+template <int WORDS, int THREADS, int ITEMS, bool FLOATK, bool REMAP, int MINB, int SUB = 1>
 __global__ void __launch_bounds__(THREADS, MINB) lsd_pass_or16_kernel(const PassParams p) {
+    static_assert(ITEMS % SUB == 0, "rounds split evenly over the sub-tables");
+    constexpr int JH = ITEMS / SUB;  // rounds per sub-table
     static_assert(THREADS >= RADIX && THREADS % 32 == 0, "one thread per digit is needed for the look-back");
-    using SM = Or16Smem<WORDS, THREADS, ITEMS>;
+    using SM = Or16Smem<WORDS, THREADS, ITEMS, SUB>;
     constexpr int GROUPS = SM::GROUPS;
     static_assert(SM::TILE <= 65536, "16-bit positions");
     constexpr int TILE = SM::TILE;
     constexpr int LB_BATCH = 4;
     constexpr int DSPLIT = (THREADS % RADIX == 0) ? THREADS / RADIX : 1;  // threads per digit in the digit phase
     constexpr int GPH = GROUPS / DSPLIT;
-    constexpr int RBITS = (16 * ITEMS <= 256) ? 8 : 16, RPR = 32 / RBITS;
+    constexpr int RBITS = (16 * JH <= 256) ? 8 : 16, RPR = 32 / RBITS;
     constexpr uint32_t RMASK = (1u << RBITS) - 1u;
 
     extern __shared__ __align__(128) uint8_t smem_raw[];
@@ -51,7 +53,7 @@ __global__ void __launch_bounds__(THREADS, MINB) lsd_pass_or16_kernel(const Pass
     const uint32_t lane_bit = 1u << (lane & 15);
     const uint32_t lt_mask = lane_bit - 1u;                                  // lanes below me in my half-warp
     const uint32_t slot_base = smem_u32(s_slot_raw);                         // [GROUPS][256] x 4 B
-    const uint32_t my_slots = slot_base + uint32_t(tid >> 4) * RADIX * 4;    // this half-warp's 256 slots
+    const uint32_t my_slots = slot_base + uint32_t(tid >> 4) * SUB * RADIX * 4;  // this half-warp's SUB x 256 slots
     const DigitParams dp = p.dp;
 
     // all slots start as {mask 0, count 0}
@@ -103,24 +105,37 @@ __global__ void __launch_bounds__(THREADS, MINB) lsd_pass_or16_kernel(const Pass
         uint32_t rk[(ITEMS + RPR - 1) / RPR];
 #pragma unroll
         for (int q = 0; q < (ITEMS + RPR - 1) / RPR; ++q) rk[q] = 0;
+        // SUB independent rounds (one per sub-table) are in flight together: their RED / LDS / STS
+        // chains do not touch the same slots, which hides the shared-memory round trip
 #pragma unroll
-        for (int j = 0; j < ITEMS; ++j) {
-            const uint32_t e = e0 + j * 16;
-            uint32_t d = 255u;  // padding sorts to the very end of the tile
-            if (full || e < valid) {
-                d = rec_digit<WORDS, FLOATK>(dp, r[j]);
-                if (REMAP) d = p.remap[d];
+        for (int jj = 0; jj < JH; ++jj) {
+            uint32_t sa[SUB], v[SUB];
+#pragma unroll
+            for (int q = 0; q < SUB; ++q) {
+                const int j = q * JH + jj;
+                const uint32_t e = e0 + j * 16;
+                uint32_t d = 255u;  // padding sorts to the very end of the tile
+                if (full || e < valid) {
+                    d = rec_digit<WORDS, FLOATK>(dp, r[j]);
+                    if (REMAP) d = p.remap[d];
+                }
+                sa[q] = my_slots + q * RADIX * 4 + d * 4;
+                slot_or(sa[q], lane_bit);
             }
-            const uint32_t sa = my_slots + d * 4;
-            slot_or(sa, lane_bit);
             __syncwarp();
-            const uint32_t v = lds_u32(sa);  // [15:0] lanes with my digit, [31:16] records of my digit in earlier rounds
+#pragma unroll
+            for (int q = 0; q < SUB; ++q)
+                v[q] = lds_u32(sa[q]);  // [15:0] lanes with my digit, [31:16] records of my digit in earlier rounds
             __syncwarp();
-            const uint32_t m = v & 0xffffu, c = v >> 16;
-            const uint32_t lt = m & lt_mask;
-            if (lt == 0) sts_u32(sa, (c + __popc(m)) << 16);
+#pragma unroll
+            for (int q = 0; q < SUB; ++q) {
+                const int j = q * JH + jj;
+                const uint32_t m = v[q] & 0xffffu, c = v[q] >> 16;
+                const uint32_t lt = m & lt_mask;
+                if (lt == 0) sts_u32(sa[q], (c + __popc(m)) << 16);
+                rk[j / RPR] |= (c + __popc(lt)) << ((j % RPR) * RBITS);
+            }
             __syncwarp();
-            rk[j / RPR] |= (c + __popc(lt)) << ((j % RPR) * RBITS);
         }
         __syncthreads();  // (B) every warp's counts final, masks back to zero
 
@@ -191,7 +206,7 @@ __global__ void __launch_bounds__(THREADS, MINB) lsd_pass_or16_kernel(const Pass
                 d = rec_digit<WORDS, FLOATK>(dp, r[j]);
                 if (REMAP) d = p.remap[d];
             }
-            const uint32_t pos = (lds_u32(my_slots + d * 4) >> 16) + ((rk[j / RPR] >> ((j % RPR) * RBITS)) & RMASK);
+            const uint32_t pos = (lds_u32(my_slots + (j / JH) * RADIX * 4 + d * 4) >> 16) + ((rk[j / RPR] >> ((j % RPR) * RBITS)) & RMASK);
             store_rec<WORDS>(s_out, pos, r[j]);
         }
         const uint32_t next_tile = s_tile[1];
@@ -199,9 +214,9 @@ __global__ void __launch_bounds__(THREADS, MINB) lsd_pass_or16_kernel(const Pass
         __syncwarp();
         // this warp's slots are only read by this warp: reset them for the next tile now
         {
-            uint4* z = reinterpret_cast<uint4*>(s_slot_raw + size_t(warp) * 2 * RADIX * 4);
+            uint4* z = reinterpret_cast<uint4*>(s_slot_raw + size_t(warp) * 2 * SUB * RADIX * 4);
 #pragma unroll
-            for (int i = lane; i < 2 * RADIX * 4 / 16; i += 32) z[i] = make_uint4(0, 0, 0, 0);
+            for (int i = lane; i < 2 * SUB * RADIX * 4 / 16; i += 32) z[i] = make_uint4(0, 0, 0, 0);
         }
 
         // ---- decoupled look-back, one thread per digit, LB_BATCH predecessors per round trip ----

@@ -15,9 +15,10 @@ struct VariantInfo {
     int min_blocks;
     int algo;      // 0 = ballot-matching kernel (onesweep.cuh), 1 = OR-matching kernel (pass_or.cuh),
                    // 2 = half-warp OR-matching kernel (pass_or16.cuh)
+    int sub;       // half-warp kernel: independent slot tables per half-warp (0 means 1)
 };
 
-constexpr int NUM_VARIANTS = 21;
+constexpr int NUM_VARIANTS = 23;
 
 constexpr VariantInfo kVariants[NUM_VARIANTS] = {
     {"t512_ldg", 512, {16, 16, 12, 8}, false, false, 1, 0},
@@ -41,12 +42,14 @@ constexpr VariantInfo kVariants[NUM_VARIANTS] = {
     {"h256_i32_occ2", 256, {32, 32, 20, 16}, false, false, 2, 2},
     {"h512_i16_occ2", 512, {16, 16, 10, 8}, false, false, 2, 2},
     {"h512_i12_occ2", 512, {20, 12, 8, 6}, false, false, 2, 2},
+    {"h256_i48_occ2", 256, {48, 40, 24, 20}, false, false, 2, 2},
+    {"h256_i40_occ2", 256, {40, 36, 22, 18}, false, false, 2, 2},
 };
 
-// Defaults measured on B200 (profiles/r1h_sweep_k2_polish.txt, r1i_*): best variant per record
+// Defaults measured on B200 (profiles/r1h_sweep_k2_polish.txt, r1l_sweep_large_tiles.txt): best variant per record
 // width in words for inputs that fill the GPU with large tiles; below kSmallInputTiles tiles of
 // the large variant per SM slot the 4096-record variant keeps every SM busy.
-constexpr int kDefaultVariant[4] = {18, 18, 17, 16};
+constexpr int kDefaultVariant[4] = {18, 18, 21, 22};
 constexpr int kSmallVariant = 12;
 constexpr int kRemapVariant = 18;
 
