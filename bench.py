@@ -42,6 +42,8 @@ WORKLOADS = {
     "f32_500m": ("f4", 500_000_000, "uniform", "BASELINE configs[2]: f32 random bit patterns, 500M"),
     "i64_500m": ("i8", 500_000_000, "uniform", "BASELINE configs[2]: i64, 500M incl. negatives"),
     "u64_1b_zipf": ("u8", 1_000_000_000, "zipf", "configs[4] skewed: Zipf(1.1) ranks as u64 keys"),
+    "u64_1b_zipf_hashed": ("u8", 1_000_000_000, "zipf_hashed",
+                           "configs[4] skewed: hashed Zipf(1.1) ranks (heavy duplicates, every level non-trivial)"),
 }
 CPU_SAMPLE = 200_000_000  # records of the same generator the CPU baseline sorts per step
 
@@ -49,8 +51,11 @@ CPU_SAMPLE = 200_000_000  # records of the same generator the CPU baseline sorts
 def gen_host(dtype, n, gen, seed):
     rng = np.random.default_rng(seed)
     dt = np.dtype(dtype)
-    if gen == "zipf":
-        return np.minimum(rng.zipf(1.1, n), 2**32).astype(dt)
+    if gen in ("zipf", "zipf_hashed"):
+        r = np.minimum(rng.zipf(1.1, n), 2**32).astype(np.uint64)
+        if gen == "zipf_hashed":
+            r = (r * np.uint64(0x9E3779B97F4A7C15)) ^ (r >> np.uint64(7))
+        return r.astype(dt)
     a = rng.integers(0, 2**64, n, dtype=np.uint64) if dt.itemsize == 8 else rng.integers(0, 2**32, n, dtype=np.uint32)
     if gen == "low40":
         a &= np.uint64((1 << 40) - 1)
@@ -64,12 +69,15 @@ def gen_device(torch, dtype, n, gen, seed):
     g = torch.Generator(device="cuda").manual_seed(seed)
     dt = np.dtype(dtype)
     if dt.itemsize == 8:
-        if gen == "zipf":
+        if gen in ("zipf", "zipf_hashed"):
             u = torch.rand(n, dtype=torch.float64, device="cuda", generator=g)
             # inverse-CDF approximation of Zipf(s=1.1) over 2^32 ranks: r = (1 - u*(1 - R^(1-s)))^(1/(1-s))
             s, R = 1.1, 2.0**32
             r = (1.0 - u * (1.0 - R ** (1.0 - s))) ** (1.0 / (1.0 - s))
-            return r.clamp_(1, R).to(torch.int64)
+            r = r.clamp_(1, R).to(torch.int64)
+            if gen == "zipf_hashed":
+                r = (r * -7046029254386353131) ^ (r >> 7)  # 0x9E3779B97F4A7C15 as int64; r < 2^33 so >> is logical
+            return r
         t = torch.randint(-2**63, 2**63 - 1, (n,), dtype=torch.int64, device="cuda", generator=g)
         if gen == "low40":
             t &= (1 << 40) - 1
@@ -82,7 +90,9 @@ def gen_device(torch, dtype, n, gen, seed):
 
 
 class ClockSampler:
-    """nvidia-smi clocks / throttle reasons sampled DURING the timed region."""
+    """SM clocks / throttle reasons sampled DURING the timed region: NVML polled every 10 ms from
+    a thread (the timed region is a fraction of a second, too short for an nvidia-smi loop to
+    start up), `nvidia-smi -lms` as the fallback."""
 
     Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,clocks_event_reasons.hw_slowdown,"
          "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
@@ -90,8 +100,51 @@ class ClockSampler:
 
     def __init__(self, index):
         self.index, self.proc, self.lines = index, None, []
+        self.sm, self.mx, self.reasons = [], [], set()
+        self.nvml, self.handle, self.stop_flag, self.t = None, None, False, None
+
+    def _nvml_handle(self):
+        import pynvml
+
+        pynvml.nvmlInit()
+        try:
+            import torch
+
+            uuid = str(torch.cuda.get_device_properties(self.index).uuid)
+            if not uuid.startswith("GPU-"):
+                uuid = "GPU-" + uuid
+            h = pynvml.nvmlDeviceGetHandleByUUID(uuid.encode() if hasattr(uuid, "encode") else uuid)
+        except Exception:
+            h = pynvml.nvmlDeviceGetHandleByIndex(self.index)
+        return pynvml, h
+
+    def _poll(self):
+        n = self.nvml
+        bits = {"hw_slowdown": getattr(n, "nvmlClocksEventReasonHwSlowdown", 0x8),
+                "hw_thermal_slowdown": getattr(n, "nvmlClocksEventReasonHwThermalSlowdown", 0x40),
+                "sw_thermal_slowdown": getattr(n, "nvmlClocksEventReasonSwThermalSlowdown", 0x20),
+                "sw_power_cap": getattr(n, "nvmlClocksEventReasonSwPowerCap", 0x4)}
+        get_reasons = getattr(n, "nvmlDeviceGetCurrentClocksEventReasons", None) or n.nvmlDeviceGetCurrentClocksThrottleReasons
+        while not self.stop_flag:
+            try:
+                self.sm.append(float(n.nvmlDeviceGetClockInfo(self.handle, n.NVML_CLOCK_SM)))
+                r = int(get_reasons(self.handle))
+                for name, bit in bits.items():
+                    if r & bit:
+                        self.reasons.add(name)
+            except Exception:
+                pass
+            time.sleep(0.01)
 
     def start(self):
+        try:
+            self.nvml, self.handle = self._nvml_handle()
+            self.mx.append(float(self.nvml.nvmlDeviceGetMaxClockInfo(self.handle, self.nvml.NVML_CLOCK_SM)))
+            self.t = threading.Thread(target=self._poll, daemon=True)
+            self.t.start()
+            return
+        except Exception:
+            self.nvml = None
         try:
             self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.index), f"--query-gpu={self.Q}",
                                           "--format=csv,noheader,nounits", "-lms", "100"],
@@ -106,6 +159,11 @@ class ClockSampler:
             self.lines.append(line.strip())
 
     def stop(self):
+        if self.nvml is not None:
+            self.stop_flag = True
+            self.t.join(timeout=2)
+            return {"sm_mhz": statistics.median(self.sm) if self.sm else None, "sm_max_mhz": max(self.mx) if self.mx else None,
+                    "reasons": sorted(self.reasons), "samples": len(self.sm), "how": "NVML polled every 10 ms during the timed region"}
         if not self.proc:
             return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
         self.proc.terminate()
@@ -127,7 +185,7 @@ class ClockSampler:
                 if val.lower().startswith("active"):
                     reasons.add(name)
         return {"sm_mhz": statistics.median(sm) if sm else None, "sm_max_mhz": max(mx) if mx else None,
-                "reasons": sorted(reasons), "samples": len(sm)}
+                "reasons": sorted(reasons), "samples": len(sm), "how": "nvidia-smi -lms 100"}
 
 
 def cpu_baseline(dtype, gen, steps, warmup, sample=CPU_SAMPLE):
@@ -300,6 +358,11 @@ def run_b200(args):
     if world > 1:
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
     ms_total_max = float(t.item())
+    max_n_recv = n
+    if world > 1:
+        nr = torch.tensor([int(last.get("n_recv", 0))], dtype=torch.int64, device="cuda")
+        dist.all_reduce(nr, op=dist.ReduceOp.MAX)
+        max_n_recv = int(nr.item())
     if rank != 0:
         if world > 1:
             dist.destroy_process_group()
@@ -347,7 +410,9 @@ def run_b200(args):
     }
     if world > 1:
         line["exchange"] = {"mode": args.exchange}
-        line["exchange"].update({k: last.get(k) for k in ("level", "n_recv", "sent_bytes", "phase_ms")})
+        line["exchange"].update({k: last.get(k) for k in ("level", "n_recv", "sent_bytes", "phase_ms", "splitter_mode")})
+        line["exchange"]["max_n_recv_over_ranks"] = max_n_recv
+        line["exchange"]["imbalance"] = max_n_recv / float(n)
         pm = last.get("phase_ms") or {}
         if pm.get("all_to_all"):
             t_x = pm["all_to_all"] + (pm["partition"] if args.exchange == "peer" else 0.0)

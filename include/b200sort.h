@@ -171,6 +171,34 @@ int b200_partition_peers_device(const void* dev_src, void* const* dst_ptrs, size
                                 uint32_t level, const uint64_t* counts, const uint32_t* split, uint32_t parts,
                                 uint64_t* part_counts_out, const b200_sort_opts* opts);
 
+/*
+ * Full-resolution splitters for skewed keys (sample-sort style).  When one
+ * digit of the partition level holds far more than N/P records, digit boundaries cannot balance
+ * the ranks.  The caller then samples 64-bit key prefixes (the record's top min(LEVELS, 8) levels
+ * as one order-preserving integer, level LEVELS-1 most significant: the bytes
+ * RadixKey::get_level returns, reference src/radix_key.rs:1-5), picks P-1 splitter prefixes from
+ * the gathered samples, counts every rank's records against them, and partitions with
+ *   part(record) = #{ g : prefix > splitters[g]  or  (prefix == splitters[g] and incl_mask bit g) }.
+ * incl_mask differs per source rank, which splits a key value heavier than one part between
+ * adjacent parts by source rank and keeps the exchange stable.
+ * Supported for 4-byte-multiple records up to 16 bytes with a word-aligned UINT / SINT / FLOAT
+ * key (b200_key_prefix_supported); other keys keep the digit splitters.
+ */
+int b200_key_prefix_supported(const b200_key_desc* desc);
+/* prefixes_out[i] (HOST) = prefix of record i * stride, i < count; (count - 1) * stride < n */
+int b200_key_prefix_sample_device(const void* dev_ptr, size_t n, const b200_key_desc* desc, size_t stride,
+                                  size_t count, uint64_t* prefixes_out, const b200_sort_opts* opts);
+/* less_out[g] / equal_out[g] (HOST) = records whose prefix is < / == splitters[g]; splitters ascending, nsplit <= 15 */
+int b200_splitter_count_device(const void* dev_ptr, size_t n, const b200_key_desc* desc, const uint64_t* splitters,
+                               uint32_t nsplit, uint64_t* less_out, uint64_t* equal_out, const b200_sort_opts* opts);
+/* Stable partition into nsplit + 1 parts by the rule above.  part_counts (HOST, nsplit + 1 entries,
+ * sum n) are this rank's exact per-part counts, derived from b200_splitter_count_device.  Either
+ * dev_dst (parts contiguous in one buffer) or dst_ptrs (one device pointer per part, possibly peer
+ * GPUs' buffers as in b200_partition_peers_device) is given. */
+int b200_partition_splitters_device(const void* dev_src, void* dev_dst, void* const* dst_ptrs, size_t n,
+                                    const b200_key_desc* desc, const uint64_t* splitters, uint32_t nsplit,
+                                    uint32_t incl_mask, const uint64_t* part_counts, const b200_sort_opts* opts);
+
 /* CUDA IPC helpers for the one-process-per-GPU exchange: allocate a shareable device buffer and
  * its 64-byte handle; open / close a peer's handle; free. */
 #define B200_IPC_HANDLE_BYTES 64

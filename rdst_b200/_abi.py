@@ -134,6 +134,21 @@ SYMBOLS = {
             C.POINTER(SortOpts),
         ],
     ),
+    "b200_key_prefix_supported": (C.c_int, [C.POINTER(KeyDesc)]),
+    "b200_key_prefix_sample_device": (
+        C.c_int,
+        [C.c_void_p, C.c_size_t, C.POINTER(KeyDesc), C.c_size_t, C.c_size_t, C.POINTER(C.c_uint64), C.POINTER(SortOpts)],
+    ),
+    "b200_splitter_count_device": (
+        C.c_int,
+        [C.c_void_p, C.c_size_t, C.POINTER(KeyDesc), C.POINTER(C.c_uint64), C.c_uint32, C.POINTER(C.c_uint64),
+         C.POINTER(C.c_uint64), C.POINTER(SortOpts)],
+    ),
+    "b200_partition_splitters_device": (
+        C.c_int,
+        [C.c_void_p, C.c_void_p, C.POINTER(C.c_void_p), C.c_size_t, C.POINTER(KeyDesc), C.POINTER(C.c_uint64),
+         C.c_uint32, C.c_uint32, C.POINTER(C.c_uint64), C.POINTER(SortOpts)],
+    ),
     "b200_ipc_alloc": (C.c_int, [C.POINTER(C.c_void_p), C.c_size_t, C.c_void_p]),
     "b200_ipc_open": (C.c_int, [C.c_void_p, C.POINTER(C.c_void_p)]),
     "b200_ipc_close": (C.c_int, [C.c_void_p]),

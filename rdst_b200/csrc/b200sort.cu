@@ -23,6 +23,7 @@
 #include <vector>
 
 #include "hist.cuh"
+#include "splitters.cuh"
 #include "launch.h"
 #include "onesweep.cuh"
 #include "variants.h"
@@ -144,7 +145,8 @@ constexpr size_t SMALL_TICKET_OFF = SMALL_BASE_OFF + size_t(MAX_LEVELS) * RADIX 
 constexpr size_t SMALL_REMAP_OFF = SMALL_TICKET_OFF + 1024;
 constexpr size_t SMALL_PBASE_OFF = SMALL_REMAP_OFF + 256;
 constexpr size_t SMALL_DTAB_OFF = SMALL_PBASE_OFF + RADIX * 8;
-constexpr size_t SMALL_BYTES = SMALL_DTAB_OFF + RADIX * 8;
+constexpr size_t SMALL_SPLIT_OFF = SMALL_DTAB_OFF + RADIX * 8;  // less[15] | equal[15] (u64), 256 bytes
+constexpr size_t SMALL_BYTES = SMALL_SPLIT_OFF + 256;
 
 constexpr int MAX_DEVICES = 64;
 DeviceCtx g_ctx[MAX_DEVICES];
@@ -297,9 +299,11 @@ int plan_pass(DeviceCtx& c, const Lowered& lo, uint64_t n, const void* a, const 
 
 int launch_pass(DeviceCtx& c, cudaStream_t st, const PassPlan& pp, const Lowered& lo, const void* src, void* dst,
                 uint64_t n, uint32_t level, const uint64_t* d_base, uint32_t* d_ticket, uint32_t tag,
-                const uint8_t* d_remap, const uint64_t* d_dst_tab = nullptr) {
+                const uint8_t* d_remap, const uint64_t* d_dst_tab = nullptr, const SplitParams* sp = nullptr) {
     if (pp.word_path) {
         PassParams p;
+        memset(&p.sp, 0, sizeof(p.sp));
+        if (sp) p.sp = *sp;
         p.src = static_cast<const uint32_t*>(src);
         p.dst = static_cast<uint32_t*>(dst);
         p.n = n;
@@ -734,6 +738,169 @@ int b200_partition_peers_device(const void* dev_src, void* const* dst_ptrs, size
     static const uint32_t none[1] = {256};
     return pass_common(dev_src, nullptr, n, desc, level, counts, split ? split : none, parts, part_counts_out, opts,
                        dst_ptrs);
+}
+
+// ---- full-resolution splitters (sample-sort style) for the sharded sort ----
+// Word indices / xor / mask of the 64-bit key prefix (top min(LEVELS, 8) levels).  Only word-path
+// records with a contiguous key are supported; the caller falls back to digit splitters otherwise.
+static int lower_prefix(const Lowered& lo, SplitParams* sp) {
+    memset(sp, 0, sizeof(*sp));
+    if (!lo.contiguous || lo.elem_size % 4 != 0 || lo.elem_size > 16 || lo.key_offset % 4 != 0) return B200_ERR_BAD_DESC;
+    if (lo.is_float && lo.levels != lo.key_width) return B200_ERR_BAD_DESC;
+    const uint32_t L = lo.levels, words = lo.elem_size / 4, kw0 = lo.key_offset / 4;
+    if (L > 16 || (L > 8 && (L - 8) % 4 != 0)) return B200_ERR_BAD_DESC;
+    const uint32_t first = L > 8 ? L - 8 : 0;  // lowest level inside the prefix
+    const uint32_t nl = L - first;              // 1..8 levels
+    sp->lo_word = kw0 + first / 4;
+    sp->hi_word = nl > 4 ? sp->lo_word + 1 : 0xffffffffu;
+    if (sp->lo_word >= words || (nl > 4 && sp->hi_word >= words)) return B200_ERR_BAD_DESC;
+    sp->mask = nl >= 8 ? ~0ull : ((1ull << (8 * nl)) - 1);
+    for (uint32_t i = 0; i < nl; ++i) sp->xorv |= uint64_t(lo.lv[first + i].xor_mask & 0xffu) << (8 * i);
+    sp->sign_word = kw0 + (L - 1) / 4;
+    sp->sign_shift = ((L - 1) % 4) * 8 + 7;
+    return B200_OK;
+}
+
+static int prefix_src(const void* dev_ptr, size_t n, const b200_key_desc* desc, Lowered* lo, PrefixSrc* ps) {
+    int rc = lower_desc(desc, lo);
+    if (rc) return rc;
+    rc = lower_prefix(*lo, &ps->sp);
+    if (rc) return rc;
+    if (reinterpret_cast<uintptr_t>(dev_ptr) % 4 != 0) return B200_ERR_BAD_DESC;
+    ps->src = static_cast<const uint32_t*>(dev_ptr);
+    ps->n = n;
+    ps->words = lo->elem_size / 4;
+    ps->is_float = lo->is_float ? 1u : 0u;
+    return B200_OK;
+}
+
+int b200_key_prefix_supported(const b200_key_desc* desc) {
+    Lowered lo;
+    if (lower_desc(desc, &lo)) return 0;
+    SplitParams sp;
+    return lower_prefix(lo, &sp) == B200_OK ? 1 : 0;
+}
+
+int b200_key_prefix_sample_device(const void* dev_ptr, size_t n, const b200_key_desc* desc, size_t stride,
+                                  size_t count, uint64_t* prefixes_out, const b200_sort_opts* opts) {
+    Lowered lo;
+    PrefixSrc ps;
+    int rc = prefix_src(dev_ptr, n, desc, &lo, &ps);
+    if (rc) return rc;
+    if (count == 0) return B200_OK;
+    if (!dev_ptr || !prefixes_out || stride == 0 || (count - 1) * stride >= n) return B200_ERR_BAD_ARG;
+    DeviceCtx* c = nullptr;
+    rc = get_ctx(opts ? opts->device : -1, &c);
+    if (rc) return rc;
+    std::lock_guard<std::mutex> lk(c->mu);
+    DeviceGuard guard(c->dev);
+    cudaStream_t st = (opts && opts->stream) ? static_cast<cudaStream_t>(opts->stream) : c->stream;
+    unsigned long long* d_out = nullptr;
+    CUDA_TRY(cudaMallocAsync(&d_out, count * 8, st));
+    prefix_sample_kernel<<<unsigned((count + 255) / 256), 256, 0, st>>>(ps, stride, count, d_out);
+    CUDA_TRY(cudaGetLastError());
+    CUDA_TRY(cudaMemcpyAsync(prefixes_out, d_out, count * 8, cudaMemcpyDeviceToHost, st));
+    CUDA_TRY(cudaFreeAsync(d_out, st));
+    CUDA_TRY(cudaStreamSynchronize(st));
+    return B200_OK;
+}
+
+int b200_splitter_count_device(const void* dev_ptr, size_t n, const b200_key_desc* desc, const uint64_t* splitters,
+                               uint32_t nsplit, uint64_t* less_out, uint64_t* equal_out, const b200_sort_opts* opts) {
+    Lowered lo;
+    PrefixSrc ps;
+    int rc = prefix_src(dev_ptr, n, desc, &lo, &ps);
+    if (rc) return rc;
+    if (nsplit == 0 || nsplit > uint32_t(MAX_SPLITTERS) || !splitters || !less_out || !equal_out) return B200_ERR_BAD_ARG;
+    for (uint32_t g = 0; g < nsplit; ++g) {
+        if (g && splitters[g] < splitters[g - 1]) return B200_ERR_BAD_ARG;
+        ps.sp.split[g] = splitters[g];
+        less_out[g] = equal_out[g] = 0;
+    }
+    ps.sp.nsplit = nsplit;
+    if (n == 0) return B200_OK;
+    if (!dev_ptr) return B200_ERR_BAD_ARG;
+    DeviceCtx* c = nullptr;
+    rc = get_ctx(opts ? opts->device : -1, &c);
+    if (rc) return rc;
+    std::lock_guard<std::mutex> lk(c->mu);
+    DeviceGuard guard(c->dev);
+    cudaStream_t st = (opts && opts->stream) ? static_cast<cudaStream_t>(opts->stream) : c->stream;
+    unsigned long long* d_cnt = reinterpret_cast<unsigned long long*>(c->d_small + SMALL_SPLIT_OFF);
+    CUDA_TRY(cudaMemsetAsync(d_cnt, 0, 256, st));
+    const int grid = int(std::max<uint64_t>(1, std::min<uint64_t>(uint64_t(c->sm_count) * 8, (n + COUNT_THREADS - 1) / COUNT_THREADS)));
+    splitter_count_kernel<<<grid, COUNT_THREADS, 0, st>>>(ps, d_cnt, d_cnt + 16);
+    CUDA_TRY(cudaGetLastError());
+    uint64_t h[32];
+    CUDA_TRY(cudaMemcpyAsync(h, d_cnt, 256, cudaMemcpyDeviceToHost, st));
+    CUDA_TRY(cudaStreamSynchronize(st));
+    for (uint32_t g = 0; g < nsplit; ++g) {
+        less_out[g] = h[g];
+        equal_out[g] = h[16 + g];
+    }
+    return B200_OK;
+}
+
+int b200_partition_splitters_device(const void* dev_src, void* dev_dst, void* const* dst_ptrs, size_t n,
+                                    const b200_key_desc* desc, const uint64_t* splitters, uint32_t nsplit,
+                                    uint32_t incl_mask, const uint64_t* part_counts, const b200_sort_opts* opts) {
+    Lowered lo;
+    int rc = lower_desc(desc, &lo);
+    if (rc) return rc;
+    SplitParams sp;
+    rc = lower_prefix(lo, &sp);
+    if (rc) return rc;
+    if (nsplit == 0 || nsplit > uint32_t(MAX_SPLITTERS) || !splitters || !part_counts) return B200_ERR_BAD_ARG;
+    const uint32_t parts = nsplit + 1;
+    uint64_t total = 0;
+    uint64_t h_base[RADIX] = {0};
+    for (uint32_t q = 0; q < parts; ++q) {
+        h_base[q] = dst_ptrs ? 0 : total;  // with per-part destinations every part starts at its own pointer
+        total += part_counts[q];
+    }
+    if (total != n) return B200_ERR_BAD_ARG;
+    for (uint32_t g = 0; g < nsplit; ++g) {
+        if (g && splitters[g] < splitters[g - 1]) return B200_ERR_BAD_ARG;
+        sp.split[g] = splitters[g];
+    }
+    sp.nsplit = nsplit;
+    sp.incl_mask = incl_mask;
+    if (n == 0) return B200_OK;
+    if (!dev_src || (!dev_dst && !dst_ptrs)) return B200_ERR_BAD_ARG;
+    uint64_t h_dtab[RADIX] = {0};
+    if (dst_ptrs) {
+        for (uint32_t q = 0; q < parts; ++q) {
+            if (!dst_ptrs[q]) return B200_ERR_BAD_ARG;
+            h_dtab[q] = reinterpret_cast<uint64_t>(dst_ptrs[q]);
+            if (h_dtab[q] % 16 != 0 && lo.elem_size % 16 == 0) return B200_ERR_BAD_ARG;
+        }
+        dev_dst = dst_ptrs[0];
+    }
+    DeviceCtx* c = nullptr;
+    rc = get_ctx(opts ? opts->device : -1, &c);
+    if (rc) return rc;
+    std::lock_guard<std::mutex> lk(c->mu);
+    DeviceGuard guard(c->dev);
+    cudaStream_t st = (opts && opts->stream) ? static_cast<cudaStream_t>(opts->stream) : c->stream;
+    PassPlan pp{};
+    rc = plan_pass(*c, lo, n, dev_src, dst_ptrs ? dev_src : dev_dst, true, -1, &pp);
+    if (rc) return rc;
+    if (!pp.word_path) return B200_ERR_BAD_DESC;
+    const size_t lb_bytes = size_t(pp.num_tiles) * RADIX * 8;
+    rc = ensure_bytes(reinterpret_cast<void**>(&c->d_lookback), &c->lookback_bytes, lb_bytes);
+    if (rc) return rc;
+    uint64_t* d_pbase = reinterpret_cast<uint64_t*>(c->d_small + SMALL_PBASE_OFF);
+    uint8_t* d_remap = c->d_small + SMALL_REMAP_OFF;
+    uint32_t* d_ticket = reinterpret_cast<uint32_t*>(c->d_small + SMALL_TICKET_OFF);
+    uint64_t* d_dtab = reinterpret_cast<uint64_t*>(c->d_small + SMALL_DTAB_OFF);
+    CUDA_TRY(cudaMemsetAsync(c->d_lookback, 0, lb_bytes, st));
+    CUDA_TRY(cudaMemsetAsync(d_ticket, 0, 1024, st));
+    CUDA_TRY(cudaMemcpyAsync(d_pbase, h_base, sizeof(h_base), cudaMemcpyHostToDevice, st));
+    if (dst_ptrs) CUDA_TRY(cudaMemcpyAsync(d_dtab, h_dtab, sizeof(h_dtab), cudaMemcpyHostToDevice, st));
+    rc = launch_pass(*c, st, pp, lo, dev_src, dev_dst, n, 0, d_pbase, d_ticket, 1, d_remap, dst_ptrs ? d_dtab : nullptr, &sp);
+    if (rc) return rc;
+    CUDA_TRY(cudaStreamSynchronize(st));
+    return B200_OK;
 }
 
 // ---- CUDA IPC helpers: one process per GPU shares its receive buffer with its peers ----

@@ -20,6 +20,21 @@
 
 namespace b200 {
 
+// Range partition on full-resolution splitters (sample-sort style):
+// the record's 64-bit key prefix = its top min(LEVELS, 8) levels as an order-preserving
+// integer, and part = #{g : prefix > split[g] or (prefix == split[g] and incl bit g)}.
+// The incl bits differ per source rank so that a key value heavier than one part is split
+// between adjacent parts by source rank (which keeps the exchange stable).
+constexpr int MAX_SPLITTERS = 15;
+struct SplitParams {
+    uint32_t nsplit;      // 0 = partition on one digit through `remap`
+    uint32_t incl_mask;
+    uint32_t lo_word, hi_word;  // record words holding prefix bits [31:0] / [63:32] (hi_word >= WORDS: none)
+    uint32_t sign_word, sign_shift;
+    uint64_t mask, xorv;
+    uint64_t split[MAX_SPLITTERS];
+};
+
 struct PassParams {
     const uint32_t* src;
     uint32_t* dst;
@@ -33,6 +48,7 @@ struct PassParams {
     const uint8_t* remap;         // optional 256 -> part table (range partition); nullptr = identity
     const uint64_t* dst_tab;      // optional, with remap: [256] destination base pointer per part
                                   // (peer GPUs' buffers for the fused partition + exchange)
+    SplitParams sp;               // remap kernels only: splitter mode when sp.nsplit != 0
 };
 
 template <int WORDS>
@@ -85,6 +101,40 @@ __device__ __forceinline__ uint32_t rec_digit(const DigitParams& dp, const Rec<W
     const uint32_t kw = pick_word<WORDS>(r, dp.word);
     const uint32_t sw = FLOATK ? pick_word<WORDS>(r, dp.sign_word) : 0u;
     return digit_from_words<FLOATK>(dp, kw, sw);
+}
+
+template <int WORDS, bool FLOATK>
+__device__ __forceinline__ uint64_t rec_prefix(const SplitParams& sp, const Rec<WORDS>& r) {
+    const uint32_t lo = pick_word<WORDS>(r, sp.lo_word);
+    const uint32_t hi = sp.hi_word < uint32_t(WORDS) ? pick_word<WORDS>(r, sp.hi_word) : 0u;
+    uint64_t k = (uint64_t(hi) << 32) | lo;
+    if (FLOATK) {
+        const uint32_t neg = (pick_word<WORDS>(r, sp.sign_word) >> sp.sign_shift) & 1u;
+        k ^= neg ? ~0ull : sp.xorv;
+    } else {
+        k ^= sp.xorv;
+    }
+    return k & sp.mask;
+}
+
+__device__ __forceinline__ uint32_t prefix_part(const SplitParams& sp, uint64_t k) {
+    uint32_t part = 0;
+#pragma unroll
+    for (int g = 0; g < MAX_SPLITTERS; ++g)
+        if (uint32_t(g) < sp.nsplit) part += (k > sp.split[g] || (k == sp.split[g] && ((sp.incl_mask >> g) & 1u))) ? 1u : 0u;
+    return part;
+}
+
+// The bucket a record goes to in this pass: its digit, the digit's part (range partition on
+// one level) or the part its key prefix falls in (range partition on splitters).
+template <int WORDS, bool FLOATK, bool REMAP>
+__device__ __forceinline__ uint32_t pass_bucket(const PassParams& p, const DigitParams& dp, const Rec<WORDS>& r) {
+    if constexpr (REMAP) {
+        if (p.sp.nsplit) return prefix_part(p.sp, rec_prefix<WORDS, FLOATK>(p.sp, r));
+    }
+    uint32_t d = rec_digit<WORDS, FLOATK>(dp, r);
+    if (REMAP) d = p.remap[d];
+    return d;
 }
 
 template <int WORDS, int THREADS, int ITEMS, bool TMA>

@@ -116,8 +116,7 @@ __global__ void __launch_bounds__(THREADS, MINB) lsd_pass_or16_kernel(const Pass
                 const uint32_t e = e0 + j * 16;
                 uint32_t d = 255u;  // padding sorts to the very end of the tile
                 if (full || e < valid) {
-                    d = rec_digit<WORDS, FLOATK>(dp, r[j]);
-                    if (REMAP) d = p.remap[d];
+                    d = pass_bucket<WORDS, FLOATK, REMAP>(p, dp, r[j]);
                 }
                 sa[q] = my_slots + q * RADIX * 4 + d * 4;
                 slot_or(sa[q], lane_bit);
@@ -203,8 +202,7 @@ __global__ void __launch_bounds__(THREADS, MINB) lsd_pass_or16_kernel(const Pass
             const uint32_t e = e0 + j * 16;
             uint32_t d = 255u;
             if (full || e < valid) {
-                d = rec_digit<WORDS, FLOATK>(dp, r[j]);
-                if (REMAP) d = p.remap[d];
+                d = pass_bucket<WORDS, FLOATK, REMAP>(p, dp, r[j]);
             }
             const uint32_t pos = (lds_u32(my_slots + (j / JH) * RADIX * 4 + d * 4) >> 16) + ((rk[j / RPR] >> ((j % RPR) * RBITS)) & RMASK);
             store_rec<WORDS>(s_out, pos, r[j]);
@@ -276,15 +274,13 @@ __global__ void __launch_bounds__(THREADS, MINB) lsd_pass_or16_kernel(const Pass
                 for (int k = 0; k < ITEMS; ++k) {
                     const uint32_t i = tid + k * THREADS;
                     const Rec<WORDS> x = load_rec<WORDS>(s_out, i);
-                    uint32_t d = rec_digit<WORDS, FLOATK>(dp, x);
-                    if (REMAP) d = p.remap[d];
+                    const uint32_t d = pass_bucket<WORDS, FLOATK, REMAP>(p, dp, x);
                     store_rec<WORDS>(REMAP ? reinterpret_cast<uint32_t*>(s_gptr[d]) : p.dst, s_gofs[d] + i, x);
                 }
             } else {
                 for (uint32_t i = tid; i < valid; i += THREADS) {
                     const Rec<WORDS> x = load_rec<WORDS>(s_out, i);
-                    uint32_t d = rec_digit<WORDS, FLOATK>(dp, x);
-                    if (REMAP) d = p.remap[d];
+                    const uint32_t d = pass_bucket<WORDS, FLOATK, REMAP>(p, dp, x);
                     store_rec<WORDS>(REMAP ? reinterpret_cast<uint32_t*>(s_gptr[d]) : p.dst, s_gofs[d] + i, x);
                 }
             }
@@ -294,8 +290,13 @@ __global__ void __launch_bounds__(THREADS, MINB) lsd_pass_or16_kernel(const Pass
                 const uint32_t k = wi - pos * WORDS;
                 const uint32_t kw = s_out[pos * WORDS + dp.word];
                 const uint32_t sw = FLOATK ? s_out[pos * WORDS + dp.sign_word] : 0u;
-                uint32_t d = digit_from_words<FLOATK>(dp, kw, sw);
-                if (REMAP) d = p.remap[d];
+                uint32_t d;
+                if (REMAP && p.sp.nsplit) {
+                    d = prefix_part(p.sp, rec_prefix<WORDS, FLOATK>(p.sp, load_rec<WORDS>(s_out, pos)));
+                } else {
+                    d = digit_from_words<FLOATK>(dp, kw, sw);
+                    if (REMAP) d = p.remap[d];
+                }
                 (REMAP ? reinterpret_cast<uint32_t*>(s_gptr[d]) : p.dst)[(s_gofs[d] + pos) * WORDS + k] = s_out[wi];
             }
         }

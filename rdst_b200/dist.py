@@ -66,6 +66,81 @@ def send_matrix(rows: np.ndarray, split: np.ndarray, parts: int) -> np.ndarray:
     return m
 
 
+# ---- full-resolution splitters for skewed keys (sample-sort style) ----
+def digit_split_imbalance(m: np.ndarray) -> float:
+    """max records any rank would receive / the even share, for a send matrix M[r, g]."""
+    total = int(m.sum())
+    return float(m.sum(axis=0).max()) * m.shape[1] / total if total else 1.0
+
+
+def choose_sample_splitters(samples: np.ndarray, weights: np.ndarray, parts: int) -> np.ndarray:
+    """P-1 splitter prefixes = weighted quantiles g/P of the gathered samples (weights =
+    records each sample stands for).  Duplicates are kept: a value heavier than one part
+    yields several equal splitters, and the tie thresholds split it by source rank."""
+    order = np.argsort(samples, kind="stable")
+    v, w = samples[order], weights[order].astype(np.float64)
+    cum = np.cumsum(w)
+    total = cum[-1]
+    idx = [min(len(v) - 1, int(np.searchsorted(cum, total * g / parts, side="left"))) for g in range(1, parts)]
+    return v[idx].astype(np.uint64)
+
+
+def splitter_left_counts(less: np.ndarray, equal: np.ndarray, t: np.ndarray) -> np.ndarray:
+    """left[r, b] = rank r's records left of boundary b."""
+    R = less.shape[0]
+    ranks = np.arange(R)[:, None]
+    return less + np.where(ranks < t[None, :], equal, 0)
+
+
+def plan_splitter_exchange(less: np.ndarray, equal: np.ndarray, n_per_rank: np.ndarray, splitters: np.ndarray, parts: int,
+                           exact_ties: bool = True):
+    """-> (t [P-1], M [R, P]): tie thresholds and the send matrix M[r, g] for the splitter partition.
+    Boundary b puts a record LEFT when prefix < s_b, or prefix == s_b and source rank < t_b; t_b (0..R)
+    is the threshold whose left count is closest to the target (b + 1) * N / P, non-decreasing over
+    equal splitters.  exact_ties=False (keys longer than the 8-level prefix): equal prefixes are not
+    equal keys, so a tie group is never split between ranks (t_b is 0 or R)."""
+    R, S = less.shape
+    total = int(n_per_rank.sum())
+    t = np.zeros(S, dtype=np.int64)
+    for b in range(S):
+        target = total * (b + 1) / parts
+        base = int(less[:, b].sum())
+        cand = base + np.concatenate([[0], np.cumsum(equal[:, b])])  # left count for t = 0..R
+        if not exact_ties:
+            cand = cand[[0, R]]
+        tb = int(np.argmin(np.abs(cand - target)))
+        if not exact_ties:
+            tb *= R
+        if b and splitters[b] == splitters[b - 1]:
+            tb = max(tb, int(t[b - 1]))
+        t[b] = tb
+    left = splitter_left_counts(less, equal, t)
+    edges = np.concatenate([np.zeros((R, 1), dtype=np.int64), left.astype(np.int64), n_per_rank.astype(np.int64)[:, None]], axis=1)
+    m = np.diff(edges, axis=1)
+    assert (m >= 0).all(), "splitter boundaries out of order"
+    return t, m
+
+
+def incl_mask_for_rank(t: np.ndarray, rank: int) -> int:
+    """bit b set = on this rank a record EQUAL to splitter b goes right of boundary b."""
+    mask = 0
+    for b, tb in enumerate(t):
+        if rank >= int(tb):
+            mask |= 1 << b
+    return mask
+
+
+def part_of_prefix(prefix: np.ndarray, splitters: np.ndarray, incl_mask: int) -> np.ndarray:
+    """numpy model of the partition rule (used by the CPU test double)."""
+    part = np.zeros(len(prefix), dtype=np.int64)
+    for b, sb in enumerate(splitters):
+        right = prefix > sb
+        if (incl_mask >> b) & 1:
+            right |= prefix == sb
+        part += right
+    return part
+
+
 # --------------------------------------------------------------------------- CUDA engine
 class CudaEngine:
     """The product engine: K1 / K2-partition / local sort through the C ABI on the
@@ -123,6 +198,44 @@ class CudaEngine:
                                                         C.byref(o)))
         self.launches += 1
         return np.array(list(pc), dtype=np.int64)
+
+    # ---- splitter mode (skewed keys) ----
+    def prefix_supported(self):
+        return bool(self.lib.b200_key_prefix_supported(C.byref(self.desc)))
+
+    def prefix_sample(self, buf, n, stride, count):
+        out = np.zeros(count, dtype=np.uint64)
+        if count:
+            o = self._opts()
+            _abi.check(self.lib.b200_key_prefix_sample_device(buf.data_ptr(), n, C.byref(self.desc), stride, count,
+                                                              out.ctypes.data_as(C.POINTER(C.c_uint64)), C.byref(o)))
+            self.launches += 1
+        return out
+
+    def splitter_count(self, buf, n, splitters):
+        sp = np.ascontiguousarray(splitters, dtype=np.uint64)
+        less, equal = np.zeros(len(sp), dtype=np.uint64), np.zeros(len(sp), dtype=np.uint64)
+        o = self._opts()
+        _abi.check(self.lib.b200_splitter_count_device(buf.data_ptr(), n, C.byref(self.desc),
+                                                       sp.ctypes.data_as(C.POINTER(C.c_uint64)), len(sp),
+                                                       less.ctypes.data_as(C.POINTER(C.c_uint64)),
+                                                       equal.ctypes.data_as(C.POINTER(C.c_uint64)), C.byref(o)))
+        self.launches += 1
+        return less.astype(np.int64), equal.astype(np.int64)
+
+    def partition_splitters(self, src, dst, dst_ptrs, n, splitters, incl_mask, part_counts):
+        sp = np.ascontiguousarray(splitters, dtype=np.uint64)
+        pc = np.ascontiguousarray(part_counts, dtype=np.uint64)
+        ptrs = None
+        if dst_ptrs is not None:
+            ptrs = (C.c_void_p * len(dst_ptrs))(*[C.c_void_p(int(x)) for x in dst_ptrs])
+        o = self._opts()
+        _abi.check(self.lib.b200_partition_splitters_device(src.data_ptr(), dst.data_ptr() if dst is not None else None,
+                                                            ptrs, n, C.byref(self.desc),
+                                                            sp.ctypes.data_as(C.POINTER(C.c_uint64)), len(sp),
+                                                            int(incl_mask), pc.ctypes.data_as(C.POINTER(C.c_uint64)),
+                                                            C.byref(o)))
+        self.launches += 1
 
     def sort(self, buf, n, tmp=None):
         o = self._opts()
@@ -205,8 +318,12 @@ def _device_view(torch, ptr, nbytes):
 
 
 # --------------------------------------------------------------------------- the sort
+MAX_SPLITTERS = 15        # include/b200sort.h: nsplit <= 15
+SAMPLES_PER_RANK = 8192   # key prefixes each rank contributes to the splitter choice
+
+
 def sharded_sort(local, n_local: int, key: RadixKey, engine=None, group=None, recv_slack: float = 1.3,
-                 scratch=None, timings=None):
+                 scratch=None, timings=None, balance_tol: float = 1.25):
     """Sort the logical array whose rank-r shard is `local` (a flat uint8 device buffer of
     n_local records).  Returns (buffer, n_out): this rank's sorted key range.
     `scratch` may carry pre-allocated {"part", "recv", "tmp"} buffers (bench reuses them)."""
@@ -239,6 +356,34 @@ def sharded_sort(local, n_local: int, key: RadixKey, engine=None, group=None, re
     # 3. splitters on digit boundaries of that level
     split = choose_splitters(global_hist[level], world)
     m = send_matrix(all_hist[:, level, :], split, world)
+    # 3b. skewed keys: digit boundaries cannot balance the ranks -> full-resolution splitters
+    splitters = t_thr = None
+    if (digit_split_imbalance(m) > balance_tol and world - 1 <= MAX_SPLITTERS and hasattr(eng, "prefix_supported")
+            and eng.prefix_supported()):
+        n_per_rank = all_hist[:, 0, :].sum(axis=1).astype(np.int64)
+        cnt = int(min(n_local, SAMPLES_PER_RANK))
+        stride = max(1, n_local // cnt) if cnt else 1
+        smp = np.zeros(SAMPLES_PER_RANK + 1, dtype=np.int64)
+        smp[0] = cnt
+        smp[1: 1 + cnt] = eng.prefix_sample(local, n_local, stride, cnt).view(np.int64)
+        mine_s = eng.to_comm(smp)
+        gs = [mine_s.new_empty(mine_s.shape) for _ in range(world)]
+        dist.all_gather(gs, mine_s, group=group)
+        vals, wts = [], []
+        for r, g in enumerate(gs):
+            a = g.cpu().numpy()
+            c = int(a[0])
+            if c:
+                vals.append(a[1: 1 + c].view(np.uint64))
+                wts.append(np.full(c, n_per_rank[r] / c))
+        splitters = choose_sample_splitters(np.concatenate(vals), np.concatenate(wts), world)
+        less, equal = eng.splitter_count(local, n_local, splitters)
+        mine_c = eng.to_comm(np.stack([less, equal]).astype(np.int64))
+        gc = [mine_c.new_empty(mine_c.shape) for _ in range(world)]
+        dist.all_gather(gc, mine_c, group=group)
+        allc = np.stack([g.cpu().numpy() for g in gc])  # [P, 2, P-1]
+        t_thr, m = plan_splitter_exchange(allc[:, 0, :], allc[:, 1, :], n_per_rank, splitters, world,
+                                          exact_ties=key.levels <= 8)
     send_counts, recv_counts = m[rank], m[:, rank]
     n_recv = int(recv_counts.sum())
     # 4. stable local partition into P contiguous send regions, then the all-to-all
@@ -259,8 +404,11 @@ def sharded_sort(local, n_local: int, key: RadixKey, engine=None, group=None, re
         starts = np.concatenate([np.zeros((1, world), dtype=np.int64), np.cumsum(m, axis=0)])[rank]  # [g]
         dst = [peers.ptrs[g] + int(starts[g]) * key.elem_size for g in range(world)]
         peers.fence()  # every rank is done with the previous contents of its receive buffer
-        pc = eng.partition_peers(local, dst, n_local, level, hist[level], split, world)
-        assert np.array_equal(pc, send_counts), "partition counts disagree with the gathered histograms"
+        if splitters is not None:
+            eng.partition_splitters(local, None, dst, n_local, splitters, incl_mask_for_rank(t_thr, rank), send_counts)
+        else:
+            pc = eng.partition_peers(local, dst, n_local, level, hist[level], split, world)
+            assert np.array_equal(pc, send_counts), "partition counts disagree with the gathered histograms"
         if ev:
             ev[2].record()
         peers.fence()  # every rank's partition kernel has finished: the received range is complete
@@ -268,8 +416,11 @@ def sharded_sort(local, n_local: int, key: RadixKey, engine=None, group=None, re
         if ev:
             ev[3].record()
     else:
-        pc = eng.partition(local, part, n_local, level, hist[level], split, world)
-        assert np.array_equal(pc, send_counts), "partition counts disagree with the gathered histograms"
+        if splitters is not None:
+            eng.partition_splitters(local, part, None, n_local, splitters, incl_mask_for_rank(t_thr, rank), send_counts)
+        else:
+            pc = eng.partition(local, part, n_local, level, hist[level], split, world)
+            assert np.array_equal(pc, send_counts), "partition counts disagree with the gathered histograms"
         if ev:
             ev[2].record()
         eng.exchange(part, recv, send_counts, recv_counts, group)
@@ -280,6 +431,7 @@ def sharded_sort(local, n_local: int, key: RadixKey, engine=None, group=None, re
     st = eng.sort(recv, n_recv, scratch.get("tmp") if scratch else None)
     if timings is not None:
         timings.update({"level": level, "split": split.tolist(), "n_recv": n_recv, "local": st,
+                        "splitter_mode": "prefix" if splitters is not None else "digit",
                         "sent_bytes": int((send_counts.sum() - send_counts[rank]) * key.elem_size)})
         if ev:
             ev[4].record()

@@ -23,6 +23,19 @@ def cases():
     yield "all_equal", RadixKey.for_dtype("u4"), np.full(100_000, 9, dtype="u4").view(np.uint8)
     yield "zipf", RadixKey.for_dtype("u8"), np.minimum(rng.zipf(1.1, 2_000_000), 2**32).astype("u8").view(np.uint8)
     yield "f32", RadixKey.for_dtype("f4"), rng.standard_normal(1_500_003).astype("f4").view(np.uint8)
+    zr = np.minimum(rng.zipf(1.1, 2_500_000), 2**32).astype("u8")
+    yield "zipf_hashed", RadixKey.for_dtype("u8"), ((zr * np.uint64(0x9E3779B97F4A7C15)) ^ (zr >> np.uint64(7))).view(np.uint8)
+    yield "two_values", RadixKey.for_dtype("u8"), np.where(rng.random(1_000_000) < 0.8, 5, 1 << 40).astype("u8").view(np.uint8)
+    yield "f64_normal", RadixKey.for_dtype("f8"), rng.standard_normal(1_300_001).view(np.uint8)
+    b = np.zeros((400_000, 2), dtype="u8")
+    b[:, 0] = rng.integers(0, 2**63, len(b))
+    b[:, 1] = np.where(rng.random(len(b)) < 0.9, 7, rng.integers(0, 2**63, len(b)))
+    yield "u128_skewed", RadixKey.u128(), b.reshape(-1).view(np.uint8)
+    recd = np.dtype([("key", "<u4"), ("idx", "<u8")])
+    ad = np.zeros(900_000, dtype=recd)
+    ad["key"] = np.where(rng.random(len(ad)) < 0.7, 3, rng.integers(0, 1 << 30, len(ad)))
+    ad["idx"] = np.arange(len(ad))
+    yield "struct12_dups_stable", RadixKey.field(recd, "key", 4), ad.view(np.uint8)
     rec = np.dtype([("key", "<u4"), ("idx", "<u8")])
     a = np.zeros(1_200_000, dtype=rec)
     a["key"] = rng.integers(0, 1 << 22, len(a))
@@ -43,7 +56,8 @@ def main():
         n = len(full) // es
         lo, hi = rank * n // world, (rank + 1) * n // world
         shard = torch.from_numpy(full[lo * es: hi * es].copy()).cuda()
-        out, n_out = sharded_sort(shard, hi - lo, key, scratch={"peers": peers} if peers else None)
+        tm = {}
+        out, n_out = sharded_sort(shard, hi - lo, key, scratch={"peers": peers} if peers else None, timings=tm)
         torch.cuda.synchronize()
         mine = out[: n_out * es].cpu()
         sizes = [torch.zeros(1, dtype=torch.int64, device="cuda") for _ in range(world)]
@@ -58,7 +72,7 @@ def main():
             got = torch.cat(bufs).cpu().numpy().tobytes()
             exp = o.stable_sorted(full, key).tobytes()
             good = got == exp
-            print(f"[dist_check] {'peer' if peers else 'nccl'} {name}: {'ok' if good else 'MISMATCH'} sizes={[s // es for s in sizes]}", flush=True)
+            print(f"[dist_check] {'peer' if peers else 'nccl'} {name}: {'ok' if good else 'MISMATCH'} splitters={tm.get('splitter_mode')} sizes={[s // es for s in sizes]}", flush=True)
             ok = ok and good
     dist.barrier()
     if peers:

@@ -14,7 +14,8 @@ import torch.multiprocessing as mp
 
 import oracle_ffi as o
 from rdst_b200 import RadixKey
-from rdst_b200.dist import choose_splitters, part_of_digit, pick_partition_level, send_matrix, sharded_sort
+from rdst_b200.dist import (choose_sample_splitters, choose_splitters, incl_mask_for_rank, part_of_digit, part_of_prefix,
+                            pick_partition_level, plan_splitter_exchange, send_matrix, sharded_sort)
 
 
 class OracleEngine:
@@ -40,6 +41,35 @@ class OracleEngine:
         order = np.argsort(part, kind="stable")
         dst.numpy()[: n * self.key.elem_size] = a[order].reshape(-1)
         return np.bincount(part, minlength=parts).astype(np.int64)
+
+    # ---- splitter mode ----
+    def prefix_supported(self):
+        return True
+
+    def _prefix(self, buf, n):
+        km = o.key_matrix(self._np(buf, n), self.key).astype(np.uint64)  # [n, L], column = level
+        L = self.key.levels
+        nl = min(L, 8)
+        p = np.zeros(n, dtype=np.uint64)
+        for i in range(nl):
+            p |= km[:, L - 1 - i] << np.uint64(8 * (nl - 1 - i))
+        return p
+
+    def prefix_sample(self, buf, n, stride, count):
+        return self._prefix(buf, n)[::stride][:count].copy()
+
+    def splitter_count(self, buf, n, splitters):
+        p = self._prefix(buf, n)
+        return (np.array([(p < s).sum() for s in splitters], dtype=np.int64),
+                np.array([(p == s).sum() for s in splitters], dtype=np.int64))
+
+    def partition_splitters(self, src, dst, dst_ptrs, n, splitters, incl_mask, part_counts):
+        assert dst_ptrs is None
+        a = self._np(src, n).reshape(n, self.key.elem_size)
+        part = part_of_prefix(self._prefix(src, n), splitters, incl_mask)
+        assert np.array_equal(np.bincount(part, minlength=len(splitters) + 1), np.asarray(part_counts, dtype=np.int64))
+        order = np.argsort(part, kind="stable")
+        dst.numpy()[: n * self.key.elem_size] = a[order].reshape(-1)
 
     def sort(self, buf, n, tmp=None):
         a = self._np(buf, n)
@@ -79,6 +109,8 @@ def _worker(rank, world, port, case, ret):
         t = {}
         out, n_out = sharded_sort(shard, hi - lo, key, engine=OracleEngine(key), timings=t)
         ret[rank] = out.numpy()[: n_out * key.elem_size].tobytes()
+        ret[f"mode{rank}"] = t.get("splitter_mode", "none")
+        ret[f"n{rank}"] = n_out
     finally:
         dist.destroy_process_group()
 
@@ -93,6 +125,24 @@ def make_case(case):
         return RadixKey.for_dtype("u4"), np.full(10_000, 77, dtype="u4").view(np.uint8)
     if case == "zipf":
         return RadixKey.for_dtype("u8"), np.minimum(rng.zipf(1.1, 120_000), 2**32).astype("u8").view(np.uint8)
+    if case == "zipf_hashed":  # heavy duplicates, every level non-trivial
+        r = np.minimum(rng.zipf(1.1, 160_000), 2**32).astype("u8")
+        h = (r * np.uint64(0x9E3779B97F4A7C15)) ^ (r >> np.uint64(7))
+        return RadixKey.for_dtype("u8"), h.view(np.uint8)
+    if case == "two_values":  # one value heavier than a part: ties are split by source rank
+        a = np.where(rng.random(100_000) < 0.8, 5, 1 << 40).astype("u8")
+        return RadixKey.for_dtype("u8"), a.view(np.uint8)
+    if case == "struct_dup_stable":  # stability across the tie split
+        rec = np.dtype([("key", "<u4"), ("idx", "<u8")])
+        a = np.zeros(80_000, dtype=rec)
+        a["key"] = np.where(rng.random(len(a)) < 0.7, 3, rng.integers(0, 1 << 30, len(a)))
+        a["idx"] = np.arange(len(a))
+        return RadixKey.field(rec, "key", 4), a.view(np.uint8)
+    if case == "u128_skewed":  # keys longer than the 8-level prefix: tie groups are never split
+        a = np.zeros((60_000, 2), dtype="u8")  # little-endian u128 = (low u64, high u64)
+        a[:, 0] = rng.integers(0, 2**63, len(a))
+        a[:, 1] = np.where(rng.random(len(a)) < 0.9, 7, rng.integers(0, 2**63, len(a)))
+        return RadixKey.u128(), a.reshape(-1).view(np.uint8)
     if case == "struct_stable":
         rec = np.dtype([("key", "<u4"), ("idx", "<u8")])
         a = np.zeros(90_000, dtype=rec)
@@ -113,16 +163,25 @@ def _free_port():
 
 
 @pytest.mark.parametrize("world", [2, 4])
-@pytest.mark.parametrize("case", ["u64_uniform", "u64_small_values", "all_equal", "zipf", "struct_stable", "f32"])
+@pytest.mark.parametrize("case", ["u64_uniform", "u64_small_values", "all_equal", "zipf", "zipf_hashed", "two_values",
+                                  "struct_dup_stable", "u128_skewed", "struct_stable", "f32"])
 def test_sharded_sort_gloo(world, case):
-    if world == 4 and case not in ("u64_uniform", "struct_stable"):
-        pytest.skip("world 4 covered by two cases")
+    if world == 4 and case not in ("u64_uniform", "struct_stable", "zipf", "zipf_hashed", "two_values", "struct_dup_stable"):
+        pytest.skip("world 4 covered by the other cases")
     mgr = mp.Manager()
     ret = mgr.dict()
     mp.spawn(_worker, args=(world, _free_port(), case, ret), nprocs=world, join=True)
     key, full = make_case(case)
     got = b"".join(ret[r] for r in range(world))
     assert got == o.stable_sorted(full, key).tobytes()
+    if case in ("zipf", "zipf_hashed", "two_values", "struct_dup_stable"):
+        # skew: digit splitters cannot balance these, the prefix splitters must
+        if case in ("zipf", "two_values"):
+            assert all(ret[f"mode{r}"] == "prefix" for r in range(world))
+        n = len(full) // key.elem_size
+        # a value heavier than a part is split between ranks at source-rank granularity
+        tol = 1.65 if case in ("two_values", "struct_dup_stable") else 1.25
+        assert max(ret[f"n{r}"] for r in range(world)) <= tol * n / world + 1
 
 
 def test_splitter_logic():
@@ -143,3 +202,32 @@ def test_splitter_logic():
     assert pick_partition_level(h) == -1
     h[2, 0], h[2, 5] = 60, 40
     assert pick_partition_level(h) == 2
+
+
+def test_splitter_exchange_plan():
+    """Host logic of the skewed-key path: weighted sample quantiles, tie thresholds, send matrix."""
+    rng = np.random.default_rng(5)
+    R, P = 4, 4
+    shards = [np.where(rng.random(10_000) < 0.6, 42, rng.integers(0, 1 << 40, 10_000)).astype(np.uint64) for _ in range(R)]
+    samples = np.concatenate([s[::10] for s in shards])
+    sp = choose_sample_splitters(samples, np.full(len(samples), 10.0), P)
+    assert len(sp) == P - 1 and (np.diff(sp.astype(np.float64)) >= 0).all() and (sp == 42).sum() >= 2
+    less = np.array([[(s < x).sum() for x in sp] for s in shards])
+    equal = np.array([[(s == x).sum() for x in sp] for s in shards])
+    n_per = np.array([len(s) for s in shards])
+    t, m = plan_splitter_exchange(less, equal, n_per, sp, P)
+    assert (np.diff(t[sp == 42]) >= 0).all()
+    assert (m >= 0).all() and (m.sum(axis=1) == n_per).all()
+    # every rank's own partition reproduces its row of the matrix
+    for r, s in enumerate(shards):
+        part = part_of_prefix(s, sp, incl_mask_for_rank(t, r))
+        assert np.array_equal(np.bincount(part, minlength=P), m[r])
+    # destination ranges are ordered: max key of part g <= min key of part g+1, ties only from lower source ranks
+    parts = [[s[part_of_prefix(s, sp, incl_mask_for_rank(t, r)) == g] for r, s in enumerate(shards)] for g in range(P)]
+    for g in range(P - 1):
+        hi = max((x.max() for x in parts[g] if len(x)), default=0)
+        lo = min((x.min() for x in parts[g + 1] if len(x)), default=np.uint64(2**63))
+        assert hi <= lo
+    # keys longer than the prefix: a tie group is never split
+    t2, m2 = plan_splitter_exchange(less, equal, n_per, sp, P, exact_ties=False)
+    assert set(t2.tolist()) <= {0, R} and (m2.sum(axis=1) == n_per).all()

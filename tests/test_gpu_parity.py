@@ -332,6 +332,81 @@ def test_partition_pass():
     assert list(pc) == np.bincount(part, minlength=parts).tolist()
 
 
+def _np_prefix(a, key):
+    """numpy model of the 64-bit key prefix: top min(LEVELS, 8) levels, level LEVELS-1 most significant."""
+    km = o.key_matrix(a.view(np.uint8).reshape(-1), key).astype(np.uint64)
+    L = key.levels
+    nl = min(L, 8)
+    p = np.zeros(km.shape[0], dtype=np.uint64)
+    for i in range(nl):
+        p |= km[:, L - 1 - i] << np.uint64(8 * (nl - 1 - i))
+    return p
+
+
+def _splitter_cases():
+    rng = np.random.default_rng(211)
+    n = 300_007
+    yield "u64", RadixKey.for_dtype("u8"), rng.integers(0, 2**64, n, dtype="u8")
+    yield "u64_dups", RadixKey.for_dtype("u8"), rng.integers(0, 40, n, dtype="u8") * np.uint64(0x0101010101010101)
+    yield "i64", RadixKey.for_dtype("i8"), rng.integers(-2**62, 2**62, n, dtype="i8")
+    yield "u32", RadixKey.for_dtype("u4"), rng.integers(0, 2**32, n, dtype="u4")
+    yield "f32", RadixKey.for_dtype("f4"), rand_bits(rng, "f4", n)
+    yield "f64", RadixKey.for_dtype("f8"), rng.standard_normal(n)
+    yield "u32_partial3", RadixKey.for_dtype("u4", levels=3), rng.integers(0, 2**32, n, dtype="u4")
+    a = np.zeros(n, dtype=REC12)
+    a["key"] = rng.integers(0, 1 << 20, n)
+    a["idx"] = np.arange(n)
+    yield "rec12", RadixKey.field(REC12, "key", 3), a
+    b = np.zeros((n, 2), dtype="u8")
+    b[:, 0] = rng.integers(0, 2**64, n, dtype="u8")
+    b[:, 1] = rng.integers(0, 1000, n, dtype="u8")
+    yield "u128", RadixKey.u128(), b.reshape(-1)
+
+
+@pytest.mark.parametrize("name,key,a", list(_splitter_cases()), ids=[c[0] for c in _splitter_cases()])
+def test_splitter_entry_points_match_numpy_model(name, key, a):
+    """b200_key_prefix_sample_device / b200_splitter_count_device / b200_partition_splitters_device
+    (the skewed-key range partition of the sharded sort) against a numpy model of the same rule."""
+    from rdst_b200.dist import part_of_prefix
+
+    torch = torch_mod()
+    l = _abi.lib()
+    d = key.to_desc()
+    assert l.b200_key_prefix_supported(C.byref(d)) == 1
+    n = a.nbytes // key.elem_size
+    pref = _np_prefix(a, key)
+    src = _dev(a)
+    stride, count = 37, n // 37
+    out = np.zeros(count, dtype=np.uint64)
+    _abi.check(l.b200_key_prefix_sample_device(src.data_ptr(), n, C.byref(d), stride, count,
+                                               out.ctypes.data_as(C.POINTER(C.c_uint64)), None))
+    assert np.array_equal(out, pref[::stride][:count])
+    srt = np.sort(pref)
+    splitters = np.array([srt[n // 5], srt[n // 5], srt[n // 2], srt[(4 * n) // 5]], dtype=np.uint64)
+    less, equal = np.zeros(4, dtype=np.uint64), np.zeros(4, dtype=np.uint64)
+    _abi.check(l.b200_splitter_count_device(src.data_ptr(), n, C.byref(d), splitters.ctypes.data_as(C.POINTER(C.c_uint64)),
+                                            4, less.ctypes.data_as(C.POINTER(C.c_uint64)),
+                                            equal.ctypes.data_as(C.POINTER(C.c_uint64)), None))
+    assert less.tolist() == [int((pref < s).sum()) for s in splitters]
+    assert equal.tolist() == [int((pref == s).sum()) for s in splitters]
+    for incl in (0b0000, 0b0110, 0b1111):
+        part = part_of_prefix(pref, splitters, incl)
+        pc = np.bincount(part, minlength=5).astype(np.uint64)
+        dst = torch.zeros(a.nbytes, dtype=torch.uint8, device="cuda")
+        _abi.check(l.b200_partition_splitters_device(src.data_ptr(), dst.data_ptr(), None, n, C.byref(d),
+                                                     splitters.ctypes.data_as(C.POINTER(C.c_uint64)), 4, incl,
+                                                     pc.ctypes.data_as(C.POINTER(C.c_uint64)), None))
+        rows = a.view(np.uint8).reshape(n, key.elem_size)
+        exp = rows[np.argsort(part, kind="stable")]
+        assert dst.cpu().numpy().tobytes() == exp.tobytes(), (name, incl)
+
+
+def test_splitter_mode_unsupported_keys_are_reported():
+    key = RadixKey.byte_array(6)
+    d = key.to_desc()
+    assert _abi.lib().b200_key_prefix_supported(C.byref(d)) == 0
+
+
 def test_every_variant_and_tile_boundaries():
     rng = np.random.default_rng(83)
     l = _abi.lib()
