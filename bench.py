@@ -41,6 +41,7 @@ WORKLOADS = {
     "u64_1b_40bit": ("u8", 1_000_000_000, "low40", "configs[1] variant: keys < 2^40, 3 trivial levels skipped"),
     "f32_500m": ("f4", 500_000_000, "uniform", "BASELINE configs[2]: f32 random bit patterns, 500M"),
     "i64_500m": ("i8", 500_000_000, "uniform", "BASELINE configs[2]: i64, 500M incl. negatives"),
+    "u64_1b_lowcard": ("u8", 1_000_000_000, "lowcard", "skew stress: every key byte is 0 or 1 (two buckets per level)"),
     "u64_1b_zipf": ("u8", 1_000_000_000, "zipf", "configs[4] skewed: Zipf(1.1) ranks as u64 keys"),
     "u64_1b_zipf_hashed": ("u8", 1_000_000_000, "zipf_hashed",
                            "configs[4] skewed: hashed Zipf(1.1) ranks (heavy duplicates, every level non-trivial)"),
@@ -59,6 +60,8 @@ def gen_host(dtype, n, gen, seed):
     a = rng.integers(0, 2**64, n, dtype=np.uint64) if dt.itemsize == 8 else rng.integers(0, 2**32, n, dtype=np.uint32)
     if gen == "low40":
         a &= np.uint64((1 << 40) - 1)
+    if gen == "lowcard":
+        a &= np.uint64(0x0101010101010101)
     if dt.kind == "f":  # NaN/Inf-free random bit patterns (BASELINE configs[2])
         a = np.where((a >> 23) & 0xFF == 0xFF, a & np.uint32(0x807FFFFF), a).astype(np.uint32)
     return a.view(dt)
@@ -81,6 +84,8 @@ def gen_device(torch, dtype, n, gen, seed):
         t = torch.randint(-2**63, 2**63 - 1, (n,), dtype=torch.int64, device="cuda", generator=g)
         if gen == "low40":
             t &= (1 << 40) - 1
+        if gen == "lowcard":
+            t &= 0x0101010101010101
         return t
     t = torch.randint(-2**31, 2**31, (n,), dtype=torch.int32, device="cuda", generator=g)
     if dt.kind == "f":
@@ -410,7 +415,7 @@ def run_b200(args):
     }
     if world > 1:
         line["exchange"] = {"mode": args.exchange}
-        line["exchange"].update({k: last.get(k) for k in ("level", "n_recv", "sent_bytes", "phase_ms", "splitter_mode")})
+        line["exchange"].update({k: last.get(k) for k in ("level", "n_recv", "sent_bytes", "phase_ms", "splitter_mode", "splitter_plan_ms")})
         line["exchange"]["max_n_recv_over_ranks"] = max_n_recv
         line["exchange"]["imbalance"] = max_n_recv / float(n)
         pm = last.get("phase_ms") or {}

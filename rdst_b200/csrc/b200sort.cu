@@ -132,6 +132,8 @@ struct DeviceCtx {
     size_t tmp_bytes = 0;
     uint64_t* d_lookback = nullptr;
     size_t lookback_bytes = 0;
+    uint8_t* d_sample = nullptr;  // key-prefix samples (splitter choice of the sharded sort)
+    size_t sample_bytes = 0;
     void* d_stage = nullptr;  // device copy of host data for b200_sort_host
     size_t stage_bytes = 0;
     void* h_bounce[2] = {nullptr, nullptr};  // pinned bounce buffers for pageable host memory
@@ -225,12 +227,12 @@ bool word_path_ok(const Lowered& lo, const void* a, const void* b) {
     return pa % 16 == 0 && pb % 16 == 0;
 }
 
-PassLaunch get_pass_launch(uint32_t words, bool floatk, bool remap, int variant) {
+PassLaunch get_pass_launch(uint32_t words, bool floatk, bool remap, int variant, bool hot) {
     switch (words) {
-        case 1: return get_pass_launch_w1(floatk, remap, variant);
-        case 2: return get_pass_launch_w2(floatk, remap, variant);
-        case 3: return get_pass_launch_w3(floatk, remap, variant);
-        case 4: return get_pass_launch_w4(floatk, remap, variant);
+        case 1: return get_pass_launch_w1(floatk, remap, variant, hot);
+        case 2: return get_pass_launch_w2(floatk, remap, variant, hot);
+        case 3: return get_pass_launch_w3(floatk, remap, variant, hot);
+        case 4: return get_pass_launch_w4(floatk, remap, variant, hot);
     }
     return PassLaunch{};
 }
@@ -262,7 +264,7 @@ struct PassPlan {
 };
 
 int plan_pass(DeviceCtx& c, const Lowered& lo, uint64_t n, const void* a, const void* b, bool remap, int variant,
-              PassPlan* out) {
+              PassPlan* out, bool hot = false) {
     PassPlan pp{};
     pp.word_path = word_path_ok(lo, a, b);
     if (pp.word_path) {
@@ -271,7 +273,7 @@ int plan_pass(DeviceCtx& c, const Lowered& lo, uint64_t n, const void* a, const 
         if (variant >= NUM_VARIANTS) return B200_ERR_BAD_ARG;
         if (remap) variant = kRemapVariant;
         pp.variant = variant;
-        pp.pl = get_pass_launch(pp.words, lo.is_float, remap, variant);
+        pp.pl = get_pass_launch(pp.words, lo.is_float, remap, variant, hot);
         if (!pp.pl.kernel) return B200_ERR_BAD_ARG;
         pp.tile = pp.pl.tile;
         CUDA_TRY(cudaFuncSetAttribute(pp.pl.kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, int(pp.pl.smem)));
@@ -299,7 +301,8 @@ int plan_pass(DeviceCtx& c, const Lowered& lo, uint64_t n, const void* a, const 
 
 int launch_pass(DeviceCtx& c, cudaStream_t st, const PassPlan& pp, const Lowered& lo, const void* src, void* dst,
                 uint64_t n, uint32_t level, const uint64_t* d_base, uint32_t* d_ticket, uint32_t tag,
-                const uint8_t* d_remap, const uint64_t* d_dst_tab = nullptr, const SplitParams* sp = nullptr) {
+                const uint8_t* d_remap, const uint64_t* d_dst_tab = nullptr, const SplitParams* sp = nullptr,
+                const uint32_t* hot = nullptr, uint32_t match_bits = 0) {
     if (pp.word_path) {
         PassParams p;
         memset(&p.sp, 0, sizeof(p.sp));
@@ -315,6 +318,9 @@ int launch_pass(DeviceCtx& c, cudaStream_t st, const PassPlan& pp, const Lowered
         p.num_tiles = pp.num_tiles;
         p.remap = d_remap;
         p.dst_tab = d_dst_tab;
+        p.hot[0] = hot ? hot[0] : 0xffffffffu;
+        p.hot[1] = hot ? hot[1] : 0xffffffffu;
+        p.match_bits = match_bits;
         pp.pl.kernel<<<pp.grid, pp.pl.threads, pp.pl.smem, st>>>(p);
     } else {
         BytePassParams p;
@@ -399,6 +405,34 @@ int launch_histogram(DeviceCtx& c, cudaStream_t st, const Lowered& lo, const voi
     return B200_OK;
 }
 
+// Buckets holding more than 1/8 of the records are "hot": the half-warp pass kernel matches them by
+// ballot instead of a same-address shared-memory RED.OR (which serialises).  Measured gain is small
+// (+3 % on two-bucket levels, profiles/r1s_skew.txt), so only clearly skewed levels take this path.
+static void pick_hot_buckets(const uint64_t* hist, uint64_t n, uint32_t hot[2]) {
+    static const bool off = getenv("B200SORT_NO_HOT") != nullptr;
+    hot[0] = hot[1] = 0xffffffffu;
+    if (off) return;
+    uint64_t best0 = n / 8, best1 = n / 8;
+    for (uint32_t b = 0; b < uint32_t(RADIX); ++b) {
+        const uint64_t cnt = hist[b];
+        if (cnt > best0) {
+            best1 = best0, hot[1] = hot[0];
+            best0 = cnt, hot[0] = b;
+        } else if (cnt > best1) {
+            best1 = cnt, hot[1] = b;
+        }
+    }
+    if (hot[0] == 0xffffffffu) hot[1] = 0xffffffffu;
+}
+
+static uint32_t match_bits_for(uint32_t parts) {
+    static const bool off = getenv("B200SORT_NO_BALLOT_PARTS") != nullptr;
+    if (off || parts > 4) return 0;  // measured: ballots win at 2 parts, lose to OR-matching at 8
+    uint32_t b = 1;
+    while ((1u << b) < parts) ++b;
+    return b;
+}
+
 // ---------------------------------------------------------------------------
 // The sort proper, device resident.
 // ---------------------------------------------------------------------------
@@ -439,6 +473,9 @@ int sort_device_impl(DeviceCtx& c, cudaStream_t st, void* data, void* tmp, uint6
     PassPlan pp{};
     rc = plan_pass(c, lo, n, data, tmp, false, variant, &pp);
     if (rc) return rc;
+    PassPlan pp_hot{};  // same tiles, the instantiation with the hot-bucket ballot path
+    rc = plan_pass(c, lo, n, data, tmp, false, pp.variant, &pp_hot, true);
+    if (rc) return rc;
     void* src = data;
     void* dst = tmp;
     if (!active.empty()) {
@@ -450,8 +487,12 @@ int sort_device_impl(DeviceCtx& c, cudaStream_t st, void* data, void* tmp, uint6
     }
     uint32_t pass = 0;
     for (uint32_t l : active) {
-        rc = launch_pass(c, st, pp, lo, src, dst, n, l, reinterpret_cast<const uint64_t*>(d_base + size_t(l) * RADIX),
-                         d_ticket + pass, pass + 1, nullptr);
+        uint32_t hot[2];
+        pick_hot_buckets(c.h_hist + size_t(l) * RADIX, n, hot);
+        const bool use_hot = hot[0] != 0xffffffffu && pp_hot.word_path && pp_hot.pl.hot;
+        rc = launch_pass(c, st, use_hot ? pp_hot : pp, lo, src, dst, n, l,
+                         reinterpret_cast<const uint64_t*>(d_base + size_t(l) * RADIX), d_ticket + pass, pass + 1, nullptr,
+                         nullptr, nullptr, use_hot ? hot : nullptr);
         if (rc) return rc;
         std::swap(src, dst);
         ++pass;
@@ -694,7 +735,10 @@ static int pass_common(const void* dev_src, void* dev_dst, size_t n, const b200_
     DeviceGuard guard(c->dev);
     cudaStream_t st = (opts && opts->stream) ? static_cast<cudaStream_t>(opts->stream) : c->stream;
     PassPlan pp{};
-    rc = plan_pass(*c, lo, n, dev_src, dst_ptrs ? dev_src : dev_dst, remap, opts ? opts->variant : -1, &pp);
+    uint32_t hot[2];
+    pick_hot_buckets(counts, n, hot);
+    rc = plan_pass(*c, lo, n, dev_src, dst_ptrs ? dev_src : dev_dst, remap, opts ? opts->variant : -1, &pp,
+                   !remap && hot[0] != 0xffffffffu);
     if (rc) return rc;
     if (dst_ptrs && !pp.word_path) return B200_ERR_BAD_DESC;  // per-part destinations need 4-byte-multiple records
     const size_t lb_bytes = size_t(pp.num_tiles) * RADIX * 8;
@@ -710,7 +754,8 @@ static int pass_common(const void* dev_src, void* dev_dst, size_t n, const b200_
     uint64_t* d_dtab = reinterpret_cast<uint64_t*>(c->d_small + SMALL_DTAB_OFF);
     if (dst_ptrs) CUDA_TRY(cudaMemcpyAsync(d_dtab, h_dtab, sizeof(h_dtab), cudaMemcpyHostToDevice, st));
     rc = launch_pass(*c, st, pp, lo, dev_src, dev_dst, n, level, d_pbase, d_ticket, 1, remap ? d_remap : nullptr,
-                     dst_ptrs ? d_dtab : nullptr);
+                     dst_ptrs ? d_dtab : nullptr, nullptr, (pp.word_path && pp.pl.hot) ? hot : nullptr,
+                     remap ? match_bits_for(parts) : 0);
     if (rc) return rc;
     CUDA_TRY(cudaStreamSynchronize(st));
     return B200_OK;
@@ -795,12 +840,12 @@ int b200_key_prefix_sample_device(const void* dev_ptr, size_t n, const b200_key_
     std::lock_guard<std::mutex> lk(c->mu);
     DeviceGuard guard(c->dev);
     cudaStream_t st = (opts && opts->stream) ? static_cast<cudaStream_t>(opts->stream) : c->stream;
-    unsigned long long* d_out = nullptr;
-    CUDA_TRY(cudaMallocAsync(&d_out, count * 8, st));
+    rc = ensure_bytes(reinterpret_cast<void**>(&c->d_sample), &c->sample_bytes, count * 8);
+    if (rc) return rc;
+    unsigned long long* d_out = reinterpret_cast<unsigned long long*>(c->d_sample);
     prefix_sample_kernel<<<unsigned((count + 255) / 256), 256, 0, st>>>(ps, stride, count, d_out);
     CUDA_TRY(cudaGetLastError());
     CUDA_TRY(cudaMemcpyAsync(prefixes_out, d_out, count * 8, cudaMemcpyDeviceToHost, st));
-    CUDA_TRY(cudaFreeAsync(d_out, st));
     CUDA_TRY(cudaStreamSynchronize(st));
     return B200_OK;
 }
@@ -859,12 +904,27 @@ int b200_partition_splitters_device(const void* dev_src, void* dev_dst, void* co
         total += part_counts[q];
     }
     if (total != n) return B200_ERR_BAD_ARG;
+    // fold the tie rule into strict thresholds: right of boundary g  <=>  prefix > s_g - incl_g.
+    // (s_g = 0 with incl: always right -> part0; thresholds must ascend, as the parts are ordered)
+    uint32_t part0 = 0, nth = 0;
+    uint64_t prev = 0;
     for (uint32_t g = 0; g < nsplit; ++g) {
         if (g && splitters[g] < splitters[g - 1]) return B200_ERR_BAD_ARG;
-        sp.split[g] = splitters[g];
+        const bool incl = (incl_mask >> g) & 1u;
+        if (incl && splitters[g] == 0) {
+            if (nth) return B200_ERR_BAD_ARG;
+            ++part0;
+            continue;
+        }
+        const uint64_t th = splitters[g] - (incl ? 1 : 0);
+        if (nth && th < prev) return B200_ERR_BAD_ARG;  // incl flags of equal splitters must not increase
+        sp.split[nth++] = prev = th;
     }
+    for (uint32_t g = nth; g < uint32_t(MAX_SPLITTERS); ++g) sp.split[g] = ~0ull;
     sp.nsplit = nsplit;
     sp.incl_mask = incl_mask;
+    sp.part0 = part0;
+    sp.ncmp = nth <= 1 ? 1 : nth <= 3 ? 3 : nth <= 7 ? 7 : uint32_t(MAX_SPLITTERS);
     if (n == 0) return B200_OK;
     if (!dev_src || (!dev_dst && !dst_ptrs)) return B200_ERR_BAD_ARG;
     uint64_t h_dtab[RADIX] = {0};
@@ -897,7 +957,8 @@ int b200_partition_splitters_device(const void* dev_src, void* dev_dst, void* co
     CUDA_TRY(cudaMemsetAsync(d_ticket, 0, 1024, st));
     CUDA_TRY(cudaMemcpyAsync(d_pbase, h_base, sizeof(h_base), cudaMemcpyHostToDevice, st));
     if (dst_ptrs) CUDA_TRY(cudaMemcpyAsync(d_dtab, h_dtab, sizeof(h_dtab), cudaMemcpyHostToDevice, st));
-    rc = launch_pass(*c, st, pp, lo, dev_src, dev_dst, n, 0, d_pbase, d_ticket, 1, d_remap, dst_ptrs ? d_dtab : nullptr, &sp);
+    rc = launch_pass(*c, st, pp, lo, dev_src, dev_dst, n, 0, d_pbase, d_ticket, 1, d_remap, dst_ptrs ? d_dtab : nullptr, &sp,
+                     nullptr, match_bits_for(parts));
     if (rc) return rc;
     CUDA_TRY(cudaStreamSynchronize(st));
     return B200_OK;
@@ -953,9 +1014,10 @@ int b200_release_scratch(int device) {
     if (rc) return rc;
     std::lock_guard<std::mutex> lk(c->mu);
     DeviceGuard guard(c->dev);
-    void** ptrs[] = {&c->d_tmp, reinterpret_cast<void**>(&c->d_lookback), &c->d_stage};
-    size_t* sizes[] = {&c->tmp_bytes, &c->lookback_bytes, &c->stage_bytes};
-    for (int i = 0; i < 3; ++i) {
+    void** ptrs[] = {&c->d_tmp, reinterpret_cast<void**>(&c->d_lookback), &c->d_stage,
+                     reinterpret_cast<void**>(&c->d_sample)};
+    size_t* sizes[] = {&c->tmp_bytes, &c->lookback_bytes, &c->stage_bytes, &c->sample_bytes};
+    for (int i = 0; i < 4; ++i) {
         if (*ptrs[i]) cudaFree(*ptrs[i]);
         *ptrs[i] = nullptr;
         *sizes[i] = 0;

@@ -11,11 +11,12 @@ struct PassLaunch {
     size_t smem;
     int tile;
     int threads;
+    bool hot;  // instantiation with the hot-bucket ballot path
 };
-PassLaunch get_pass_launch_w1(bool floatk, bool remap, int variant);
-PassLaunch get_pass_launch_w2(bool floatk, bool remap, int variant);
-PassLaunch get_pass_launch_w3(bool floatk, bool remap, int variant);
-PassLaunch get_pass_launch_w4(bool floatk, bool remap, int variant);
+PassLaunch get_pass_launch_w1(bool floatk, bool remap, int variant, bool hot);
+PassLaunch get_pass_launch_w2(bool floatk, bool remap, int variant, bool hot);
+PassLaunch get_pass_launch_w3(bool floatk, bool remap, int variant, bool hot);
+PassLaunch get_pass_launch_w4(bool floatk, bool remap, int variant, bool hot);
 struct HistParams;
 bool launch_hist_fast_w1(uint32_t L, bool floatk, int grid, cudaStream_t st, const HistParams& hp);
 bool launch_hist_fast_w2(uint32_t L, bool floatk, int grid, cudaStream_t st, const HistParams& hp);

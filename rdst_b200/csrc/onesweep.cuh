@@ -29,6 +29,9 @@ constexpr int MAX_SPLITTERS = 15;
 struct SplitParams {
     uint32_t nsplit;      // 0 = partition on one digit through `remap`
     uint32_t incl_mask;
+    // partition kernel: part = part0 + #{g < ncmp : prefix > split[g]} with the tie rule folded into
+    // the thresholds by the host (split[g] = s_g - incl_g; ncmp = 1, 3, 7 or 15, padded with ~0)
+    uint32_t part0, ncmp;
     uint32_t lo_word, hi_word;  // record words holding prefix bits [31:0] / [63:32] (hi_word >= WORDS: none)
     uint32_t sign_word, sign_shift;
     uint64_t mask, xorv;
@@ -49,6 +52,8 @@ struct PassParams {
     const uint64_t* dst_tab;      // optional, with remap: [256] destination base pointer per part
                                   // (peer GPUs' buffers for the fused partition + exchange)
     SplitParams sp;               // remap kernels only: splitter mode when sp.nsplit != 0
+    uint32_t hot[2];              // half-warp kernel: buckets matched by ballot (0xffffffff = none)
+    uint32_t match_bits;          // half-warp remap kernel: match the part id by this many ballots (0 = OR-matching)
 };
 
 template <int WORDS>
@@ -117,12 +122,18 @@ __device__ __forceinline__ uint64_t rec_prefix(const SplitParams& sp, const Rec<
     return k & sp.mask;
 }
 
-__device__ __forceinline__ uint32_t prefix_part(const SplitParams& sp, uint64_t k) {
-    uint32_t part = 0;
+template <int N>
+__device__ __forceinline__ uint32_t count_above(const SplitParams& sp, uint64_t k) {
+    uint32_t c = 0;
 #pragma unroll
-    for (int g = 0; g < MAX_SPLITTERS; ++g)
-        if (uint32_t(g) < sp.nsplit) part += (k > sp.split[g] || (k == sp.split[g] && ((sp.incl_mask >> g) & 1u))) ? 1u : 0u;
-    return part;
+    for (int g = 0; g < N; ++g) c += k > sp.split[g] ? 1u : 0u;
+    return c;
+}
+__device__ __forceinline__ uint32_t prefix_part(const SplitParams& sp, uint64_t k) {
+    if (sp.ncmp <= 1) return sp.part0 + count_above<1>(sp, k);
+    if (sp.ncmp <= 3) return sp.part0 + count_above<3>(sp, k);
+    if (sp.ncmp <= 7) return sp.part0 + count_above<7>(sp, k);
+    return sp.part0 + count_above<MAX_SPLITTERS>(sp, k);
 }
 
 // The bucket a record goes to in this pass: its digit, the digit's part (range partition on

@@ -10,15 +10,25 @@
 
 namespace b200 {
 
+// variants that also exist with the hot-bucket ballot path (the per-width defaults)
+constexpr bool variant_has_hot(int v) { return v == 12 || v == 18 || v == 21 || v == 22; }
+
 template <int WORDS, bool FLOATK, bool REMAP, int V>
-static PassLaunch make_launch() {
+static PassLaunch make_launch(bool hot = false) {
     constexpr VariantInfo vi = kVariants[V];
     constexpr int ITEMS = vi.items[WORDS - 1];
-    PassLaunch pl;
+    PassLaunch pl{};
     if constexpr (vi.algo == 2) {
         constexpr int SUB = vi.sub ? vi.sub : 1;
         using SM = Or16Smem<WORDS, vi.threads, ITEMS, SUB>;
-        pl.kernel = &lsd_pass_or16_kernel<WORDS, vi.threads, ITEMS, FLOATK, REMAP, vi.min_blocks, SUB>;
+        pl.kernel = &lsd_pass_or16_kernel<WORDS, vi.threads, ITEMS, FLOATK, REMAP, vi.min_blocks, SUB, false>;
+        pl.hot = false;
+        if constexpr (!REMAP && variant_has_hot(V)) {
+            if (hot) {
+                pl.kernel = &lsd_pass_or16_kernel<WORDS, vi.threads, ITEMS, FLOATK, REMAP, vi.min_blocks, SUB, true>;
+                pl.hot = true;
+            }
+        }
         pl.smem = SM::TOTAL;
         pl.tile = SM::TILE;
     } else if constexpr (vi.algo == 1) {
@@ -37,31 +47,31 @@ static PassLaunch make_launch() {
 }
 
 template <int WORDS, bool FLOATK, bool REMAP>
-static PassLaunch pick_launch(int v) {
+static PassLaunch pick_launch(int v, bool hot) {
     switch (v) {
-        case 0: return make_launch<WORDS, FLOATK, REMAP, 0>();
-        case 1: return make_launch<WORDS, FLOATK, REMAP, 1>();
-        case 2: return make_launch<WORDS, FLOATK, REMAP, 2>();
-        case 3: return make_launch<WORDS, FLOATK, REMAP, 3>();
-        case 4: return make_launch<WORDS, FLOATK, REMAP, 4>();
-        case 5: return make_launch<WORDS, FLOATK, REMAP, 5>();
-        case 6: return make_launch<WORDS, FLOATK, REMAP, 6>();
-        case 7: return make_launch<WORDS, FLOATK, REMAP, 7>();
-        case 8: return make_launch<WORDS, FLOATK, REMAP, 8>();
-        case 9: return make_launch<WORDS, FLOATK, REMAP, 9>();
-        case 10: return make_launch<WORDS, FLOATK, REMAP, 10>();
-        case 11: return make_launch<WORDS, FLOATK, REMAP, 11>();
-        case 12: return make_launch<WORDS, FLOATK, REMAP, 12>();
-        case 13: return make_launch<WORDS, FLOATK, REMAP, 13>();
-        case 14: return make_launch<WORDS, FLOATK, REMAP, 14>();
-        case 15: return make_launch<WORDS, FLOATK, REMAP, 15>();
-        case 16: return make_launch<WORDS, FLOATK, REMAP, 16>();
-        case 17: return make_launch<WORDS, FLOATK, REMAP, 17>();
-        case 18: return make_launch<WORDS, FLOATK, REMAP, 18>();
-        case 19: return make_launch<WORDS, FLOATK, REMAP, 19>();
-        case 20: return make_launch<WORDS, FLOATK, REMAP, 20>();
-        case 21: return make_launch<WORDS, FLOATK, REMAP, 21>();
-        case 22: return make_launch<WORDS, FLOATK, REMAP, 22>();
+        case 0: return make_launch<WORDS, FLOATK, REMAP, 0>(hot);
+        case 1: return make_launch<WORDS, FLOATK, REMAP, 1>(hot);
+        case 2: return make_launch<WORDS, FLOATK, REMAP, 2>(hot);
+        case 3: return make_launch<WORDS, FLOATK, REMAP, 3>(hot);
+        case 4: return make_launch<WORDS, FLOATK, REMAP, 4>(hot);
+        case 5: return make_launch<WORDS, FLOATK, REMAP, 5>(hot);
+        case 6: return make_launch<WORDS, FLOATK, REMAP, 6>(hot);
+        case 7: return make_launch<WORDS, FLOATK, REMAP, 7>(hot);
+        case 8: return make_launch<WORDS, FLOATK, REMAP, 8>(hot);
+        case 9: return make_launch<WORDS, FLOATK, REMAP, 9>(hot);
+        case 10: return make_launch<WORDS, FLOATK, REMAP, 10>(hot);
+        case 11: return make_launch<WORDS, FLOATK, REMAP, 11>(hot);
+        case 12: return make_launch<WORDS, FLOATK, REMAP, 12>(hot);
+        case 13: return make_launch<WORDS, FLOATK, REMAP, 13>(hot);
+        case 14: return make_launch<WORDS, FLOATK, REMAP, 14>(hot);
+        case 15: return make_launch<WORDS, FLOATK, REMAP, 15>(hot);
+        case 16: return make_launch<WORDS, FLOATK, REMAP, 16>(hot);
+        case 17: return make_launch<WORDS, FLOATK, REMAP, 17>(hot);
+        case 18: return make_launch<WORDS, FLOATK, REMAP, 18>(hot);
+        case 19: return make_launch<WORDS, FLOATK, REMAP, 19>(hot);
+        case 20: return make_launch<WORDS, FLOATK, REMAP, 20>(hot);
+        case 21: return make_launch<WORDS, FLOATK, REMAP, 21>(hot);
+        case 22: return make_launch<WORDS, FLOATK, REMAP, 22>(hot);
         default: break;
     }
     PassLaunch none{};
@@ -69,12 +79,12 @@ static PassLaunch pick_launch(int v) {
 }
 
 template <int WORDS>
-static PassLaunch pick_launch_w(bool floatk, bool remap, int v) {
+static PassLaunch pick_launch_w(bool floatk, bool remap, int v, bool hot) {
     if (remap) {
         // the range-partition pass exists in one variant only (kRemapVariant)
         return floatk ? make_launch<WORDS, true, true, kRemapVariant>() : make_launch<WORDS, false, true, kRemapVariant>();
     }
-    return floatk ? pick_launch<WORDS, true, false>(v) : pick_launch<WORDS, false, false>(v);
+    return floatk ? pick_launch<WORDS, true, false>(v, hot) : pick_launch<WORDS, false, false>(v, hot);
 }
 
 }  // namespace b200

@@ -23,9 +23,9 @@ struct Or16Smem {
     static constexpr size_t TOTAL = OUT_BYTES + SLOT_BYTES + GOFS_BYTES + MISC_BYTES + PART_BYTES;
 };
 
-template <int WORDS, int THREADS, int ITEMS, bool FLOATK, bool REMAP, int MINB, int SUB = 1>
+template <int WORDS, int THREADS, int ITEMS, bool FLOATK, bool REMAP, int MINB, int SUB = 1, bool HOT = false>
 __global__ void __launch_bounds__(THREADS, MINB) lsd_pass_or16_kernel(const PassParams p) {
-    static_assert(ITEMS % SUB == 0, "rounds split evenly over the sub-tables");
+    static_assert(SUB == 1, "one slot table per half-warp");
     constexpr int JH = ITEMS / SUB;  // rounds per sub-table
     static_assert(THREADS >= RADIX && THREADS % 32 == 0, "one thread per digit is needed for the look-back");
     using SM = Or16Smem<WORDS, THREADS, ITEMS, SUB>;
@@ -105,36 +105,77 @@ __global__ void __launch_bounds__(THREADS, MINB) lsd_pass_or16_kernel(const Pass
         uint32_t rk[(ITEMS + RPR - 1) / RPR];
 #pragma unroll
         for (int q = 0; q < (ITEMS + RPR - 1) / RPR; ++q) rk[q] = 0;
-        // SUB independent rounds (one per sub-table) are in flight together: their RED / LDS / STS
-        // chains do not touch the same slots, which hides the shared-memory round trip
+        uint32_t dcache[REMAP ? (ITEMS + 3) / 4 : 1];
 #pragma unroll
-        for (int jj = 0; jj < JH; ++jj) {
-            uint32_t sa[SUB], v[SUB];
+        for (int q = 0; q < (REMAP ? (ITEMS + 3) / 4 : 1); ++q) dcache[q] = 0;
+        // Three ways to find the lanes of my half-warp that hold my bucket:
+        //  * OR-matching through the slot's mask field (default: 1.6 cycles per warp-op on random
+        //    digits, but same-address RED.OR serialises: 6.6 .. 12 cycles when lanes share a digit,
+        //    profiles/r1r_microbench_skew.txt);
+        //  * hot buckets (up to two per pass, chosen by the host from the K1 histogram when a bucket
+        //    holds more than ~3 % of the records): matched by one ballot each, counted in a register,
+        //    never touching shared memory in this loop;
+        //  * range partitions into few parts (REMAP, match_bits = ceil(log2 parts) <= 4): every lane
+        //    collides, so the bucket id is matched bit by bit with ballots.
+        const uint32_t hshift = lane & 16u;
+        const bool use_hot = HOT && p.hot[0] != 0xffffffffu;  // HOT = false instantiations ignore p.hot
+        const uint32_t mbits = REMAP ? p.match_bits : 0u;
+        uint32_t hot_cnt0 = 0, hot_cnt1 = 0;  // hot records of this half-warp so far (uniform over its lanes)
 #pragma unroll
-            for (int q = 0; q < SUB; ++q) {
-                const int j = q * JH + jj;
-                const uint32_t e = e0 + j * 16;
-                uint32_t d = 255u;  // padding sorts to the very end of the tile
-                if (full || e < valid) {
-                    d = pass_bucket<WORDS, FLOATK, REMAP>(p, dp, r[j]);
+        for (int j = 0; j < ITEMS; ++j) {
+            const uint32_t e = e0 + j * 16;
+            uint32_t d = 255u;  // padding sorts to the very end of the tile
+            if (full || e < valid) {
+                d = pass_bucket<WORDS, FLOATK, REMAP>(p, dp, r[j]);
+            }
+            if (REMAP) dcache[j / 4] |= d << ((j % 4) * 8);  // the part id is costly to recompute
+            const uint32_t sa = my_slots + d * 4;
+            uint32_t rank;
+            if (REMAP && mbits) {
+                uint32_t m = 0xffffu;
+                if constexpr (REMAP) {
+#pragma unroll 1
+                    for (uint32_t bit = 0; bit < mbits; ++bit) {
+                        const bool on = (d >> bit) & 1u;
+                        const uint32_t bal = (__ballot_sync(0xffffffffu, on) >> hshift) & 0xffffu;
+                        m &= on ? bal : ~bal;
+                    }
                 }
-                sa[q] = my_slots + q * RADIX * 4 + d * 4;
-                slot_or(sa[q], lane_bit);
-            }
-            __syncwarp();
-#pragma unroll
-            for (int q = 0; q < SUB; ++q)
-                v[q] = lds_u32(sa[q]);  // [15:0] lanes with my digit, [31:16] records of my digit in earlier rounds
-            __syncwarp();
-#pragma unroll
-            for (int q = 0; q < SUB; ++q) {
-                const int j = q * JH + jj;
-                const uint32_t m = v[q] & 0xffffu, c = v[q] >> 16;
+                const uint32_t c = lds_u32(sa) >> 16;
+                __syncwarp();
                 const uint32_t lt = m & lt_mask;
-                if (lt == 0) sts_u32(sa[q], (c + __popc(m)) << 16);
-                rk[j / RPR] |= (c + __popc(lt)) << ((j % RPR) * RBITS);
+                if (lt == 0) sts_u32(sa, (c + __popc(m)) << 16);
+                __syncwarp();
+                rank = c + __popc(lt);
+            } else {
+                bool cold = true;
+                uint32_t hrank = 0;
+                if (HOT && use_hot) {
+                    const bool h0 = d == p.hot[0], h1 = d == p.hot[1];
+                    const uint32_t b0 = (__ballot_sync(0xffffffffu, h0) >> hshift) & 0xffffu;
+                    const uint32_t b1 = (__ballot_sync(0xffffffffu, h1) >> hshift) & 0xffffu;
+                    cold = !(h0 || h1);
+                    hrank = h0 ? hot_cnt0 + __popc(b0 & lt_mask) : hot_cnt1 + __popc(b1 & lt_mask);
+                    hot_cnt0 += __popc(b0);
+                    hot_cnt1 += __popc(b1);
+                }
+                if (cold) slot_or(sa, lane_bit);
+                __syncwarp();
+                uint32_t v = 0;
+                if (cold) v = lds_u32(sa);  // [15:0] lanes with my digit, [31:16] records of my digit in earlier rounds
+                __syncwarp();
+                const uint32_t m = v & 0xffffu, c = v >> 16;
+                const uint32_t lt = m & lt_mask;
+                if (cold && lt == 0) sts_u32(sa, (c + __popc(m)) << 16);
+                __syncwarp();
+                rank = cold ? c + __popc(lt) : hrank;
             }
-            __syncwarp();
+            rk[j / RPR] |= rank << ((j % RPR) * RBITS);
+        }
+        if (HOT && use_hot && (lane & 15) == 0) {
+            // the hot buckets' counts join the slot table for the digit phase (nobody else wrote these slots)
+            if (hot_cnt0) sts_u32(my_slots + p.hot[0] * 4, hot_cnt0 << 16);
+            if (hot_cnt1) sts_u32(my_slots + p.hot[1] * 4, hot_cnt1 << 16);
         }
         __syncthreads();  // (B) every warp's counts final, masks back to zero
 
@@ -201,8 +242,10 @@ __global__ void __launch_bounds__(THREADS, MINB) lsd_pass_or16_kernel(const Pass
         for (int j = 0; j < ITEMS; ++j) {
             const uint32_t e = e0 + j * 16;
             uint32_t d = 255u;
-            if (full || e < valid) {
-                d = pass_bucket<WORDS, FLOATK, REMAP>(p, dp, r[j]);
+            if (REMAP) {
+                d = (dcache[j / 4] >> ((j % 4) * 8)) & 0xffu;
+            } else if (full || e < valid) {
+                d = rec_digit<WORDS, FLOATK>(dp, r[j]);
             }
             const uint32_t pos = (lds_u32(my_slots + (j / JH) * RADIX * 4 + d * 4) >> 16) + ((rk[j / RPR] >> ((j % RPR) * RBITS)) & RMASK);
             store_rec<WORDS>(s_out, pos, r[j]);

@@ -1,4 +1,6 @@
 #include "pass_inst.cuh"
 namespace b200 {
-PassLaunch get_pass_launch_w3(bool floatk, bool remap, int variant) { return pick_launch_w<3>(floatk, remap, variant); }
+PassLaunch get_pass_launch_w3(bool floatk, bool remap, int variant, bool hot) {
+    return pick_launch_w<3>(floatk, remap, variant, hot);
+}
 }  // namespace b200

@@ -42,48 +42,40 @@ static __global__ void prefix_sample_kernel(const PrefixSrc ps, uint64_t stride,
     if (i < count) out[i] = prefix_of(ps, i * stride);
 }
 
-// less[g] = #records with prefix < split[g], equal[g] = #records with prefix == split[g]
+// less[g] = #records with prefix < split[g], equal[g] = #records with prefix == split[g].
+// The splitters ascend, so a record is described by lo = #splitters < prefix and
+// up = #splitters <= prefix: it is "equal" to splitters lo .. up-1 and "less" than up .. nsplit-1.
+// Each CTA histograms (lo, up) in shared memory (two 16-bin tables) and prefix-sums at the end.
 constexpr int COUNT_THREADS = 256;
 static __global__ void __launch_bounds__(COUNT_THREADS) splitter_count_kernel(const PrefixSrc ps,
                                                                              unsigned long long* less,
                                                                              unsigned long long* equal) {
-    uint32_t lt[MAX_SPLITTERS], eq[MAX_SPLITTERS];
-#pragma unroll
-    for (int g = 0; g < MAX_SPLITTERS; ++g) lt[g] = eq[g] = 0;
+    __shared__ uint32_t h_lo[MAX_SPLITTERS + 1], h_up[MAX_SPLITTERS + 1];  // a CTA sees < 2^32 records
+    if (threadIdx.x <= MAX_SPLITTERS) h_lo[threadIdx.x] = h_up[threadIdx.x] = 0;
+    __syncthreads();
     const uint64_t stride = uint64_t(gridDim.x) * COUNT_THREADS;
-    // a thread sees at most n / stride + 1 records: 32-bit counters hold for any n the engine accepts per launch
     for (uint64_t rec = uint64_t(blockIdx.x) * COUNT_THREADS + threadIdx.x; rec < ps.n; rec += stride) {
         const uint64_t k = prefix_of(ps, rec);
-#pragma unroll
-        for (int g = 0; g < MAX_SPLITTERS; ++g) {
-            if (uint32_t(g) < ps.sp.nsplit) {
-                lt[g] += k < ps.sp.split[g] ? 1u : 0u;
-                eq[g] += k == ps.sp.split[g] ? 1u : 0u;
-            }
+        uint32_t lo = 0, up = 0;
+#pragma unroll 1
+        for (uint32_t g = 0; g < ps.sp.nsplit; ++g) {
+            const uint64_t sv = ps.sp.split[g];
+            lo += sv < k ? 1u : 0u;
+            up += sv <= k ? 1u : 0u;
         }
-    }
-    __shared__ unsigned long long s_lt[MAX_SPLITTERS], s_eq[MAX_SPLITTERS];
-    if (threadIdx.x < MAX_SPLITTERS) s_lt[threadIdx.x] = s_eq[threadIdx.x] = 0;
-    __syncthreads();
-#pragma unroll
-    for (int g = 0; g < MAX_SPLITTERS; ++g) {
-        if (uint32_t(g) < ps.sp.nsplit) {
-            uint32_t a = lt[g], b = eq[g];
-#pragma unroll
-            for (int o = 16; o > 0; o >>= 1) {
-                a += __shfl_down_sync(0xffffffffu, a, o);
-                b += __shfl_down_sync(0xffffffffu, b, o);
-            }
-            if ((threadIdx.x & 31) == 0) {
-                atomicAdd(&s_lt[g], (unsigned long long)a);
-                atomicAdd(&s_eq[g], (unsigned long long)b);
-            }
-        }
+        atomicAdd(&h_lo[lo], 1u);
+        atomicAdd(&h_up[up], 1u);
     }
     __syncthreads();
     if (threadIdx.x < ps.sp.nsplit) {
-        atomicAdd(&less[threadIdx.x], s_lt[threadIdx.x]);
-        atomicAdd(&equal[threadIdx.x], s_eq[threadIdx.x]);
+        // less[g] = #(up <= g); equal[g] = #(lo <= g) - #(up <= g)
+        unsigned long long cu = 0, cl = 0;
+        for (uint32_t x = 0; x <= threadIdx.x; ++x) {
+            cu += h_up[x];
+            cl += h_lo[x];
+        }
+        if (cu) atomicAdd(&less[threadIdx.x], cu);
+        if (cl - cu) atomicAdd(&equal[threadIdx.x], cl - cu);
     }
 }
 

@@ -358,14 +358,20 @@ def sharded_sort(local, n_local: int, key: RadixKey, engine=None, group=None, re
     m = send_matrix(all_hist[:, level, :], split, world)
     # 3b. skewed keys: digit boundaries cannot balance the ranks -> full-resolution splitters
     splitters = t_thr = None
+    import time as _time
+
+    plan_t = {}
     if (digit_split_imbalance(m) > balance_tol and world - 1 <= MAX_SPLITTERS and hasattr(eng, "prefix_supported")
             and eng.prefix_supported()):
         n_per_rank = all_hist[:, 0, :].sum(axis=1).astype(np.int64)
         cnt = int(min(n_local, SAMPLES_PER_RANK))
         stride = max(1, n_local // cnt) if cnt else 1
+        _t0 = _time.perf_counter()
         smp = np.zeros(SAMPLES_PER_RANK + 1, dtype=np.int64)
         smp[0] = cnt
         smp[1: 1 + cnt] = eng.prefix_sample(local, n_local, stride, cnt).view(np.int64)
+        plan_t["sample_ms"] = (_time.perf_counter() - _t0) * 1e3
+        _t0 = _time.perf_counter()
         mine_s = eng.to_comm(smp)
         gs = [mine_s.new_empty(mine_s.shape) for _ in range(world)]
         dist.all_gather(gs, mine_s, group=group)
@@ -377,13 +383,18 @@ def sharded_sort(local, n_local: int, key: RadixKey, engine=None, group=None, re
                 vals.append(a[1: 1 + c].view(np.uint64))
                 wts.append(np.full(c, n_per_rank[r] / c))
         splitters = choose_sample_splitters(np.concatenate(vals), np.concatenate(wts), world)
+        plan_t["gather_choose_ms"] = (_time.perf_counter() - _t0) * 1e3
+        _t0 = _time.perf_counter()
         less, equal = eng.splitter_count(local, n_local, splitters)
+        plan_t["count_ms"] = (_time.perf_counter() - _t0) * 1e3
+        _t0 = _time.perf_counter()
         mine_c = eng.to_comm(np.stack([less, equal]).astype(np.int64))
         gc = [mine_c.new_empty(mine_c.shape) for _ in range(world)]
         dist.all_gather(gc, mine_c, group=group)
         allc = np.stack([g.cpu().numpy() for g in gc])  # [P, 2, P-1]
         t_thr, m = plan_splitter_exchange(allc[:, 0, :], allc[:, 1, :], n_per_rank, splitters, world,
                                           exact_ties=key.levels <= 8)
+        plan_t["gather_plan_ms"] = (_time.perf_counter() - _t0) * 1e3
     send_counts, recv_counts = m[rank], m[:, rank]
     n_recv = int(recv_counts.sum())
     # 4. stable local partition into P contiguous send regions, then the all-to-all
@@ -431,7 +442,7 @@ def sharded_sort(local, n_local: int, key: RadixKey, engine=None, group=None, re
     st = eng.sort(recv, n_recv, scratch.get("tmp") if scratch else None)
     if timings is not None:
         timings.update({"level": level, "split": split.tolist(), "n_recv": n_recv, "local": st,
-                        "splitter_mode": "prefix" if splitters is not None else "digit",
+                        "splitter_mode": "prefix" if splitters is not None else "digit", "splitter_plan_ms": plan_t,
                         "sent_bytes": int((send_counts.sum() - send_counts[rank]) * key.elem_size)})
         if ev:
             ev[4].record()

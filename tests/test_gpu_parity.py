@@ -389,7 +389,7 @@ def test_splitter_entry_points_match_numpy_model(name, key, a):
                                             equal.ctypes.data_as(C.POINTER(C.c_uint64)), None))
     assert less.tolist() == [int((pref < s).sum()) for s in splitters]
     assert equal.tolist() == [int((pref == s).sum()) for s in splitters]
-    for incl in (0b0000, 0b0110, 0b1111):
+    for incl in (0b0000, 0b0101, 0b1001, 0b1111):
         part = part_of_prefix(pref, splitters, incl)
         pc = np.bincount(part, minlength=5).astype(np.uint64)
         dst = torch.zeros(a.nbytes, dtype=torch.uint8, device="cuda")
@@ -399,6 +399,13 @@ def test_splitter_entry_points_match_numpy_model(name, key, a):
         rows = a.view(np.uint8).reshape(n, key.elem_size)
         exp = rows[np.argsort(part, kind="stable")]
         assert dst.cpu().numpy().tobytes() == exp.tobytes(), (name, incl)
+    # equal splitters whose tie flags would put the parts out of order are rejected
+    pc = np.zeros(5, dtype=np.uint64)
+    pc[0] = n
+    rc = l.b200_partition_splitters_device(src.data_ptr(), dst.data_ptr(), None, n, C.byref(d),
+                                           splitters.ctypes.data_as(C.POINTER(C.c_uint64)), 4, 0b0010,
+                                           pc.ctypes.data_as(C.POINTER(C.c_uint64)), None)
+    assert rc != 0
 
 
 def test_splitter_mode_unsupported_keys_are_reported():
