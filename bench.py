@@ -392,6 +392,13 @@ def run_b200(args):
                 "algorithmic_bytes_per_launch": per_launch_bytes, "launches_per_step": passes,
                 "avg_launch_ms": ms_passes / passes,
                 "how": "CUDA events recorded by the library on the launch stream around the K2 passes of the last step"}
+        try:  # dram bytes per launch from the committed ncu --set full capture of this workload
+            tr = json.load(open(os.path.join(ROOT, "profiles", "k2_traffic.json"))).get(args.workload)
+            if tr and tr["records"] == n_sorted:
+                roof["traffic"] = tr["traffic_bytes_per_launch"]
+                roof["traffic_source"] = "profiles/k2_traffic.json (ncu dram__bytes_read.sum + dram__bytes_write.sum, one launch)"
+        except Exception:
+            pass
         whole = n_sorted * es * (1 + 2 * passes) / ((st_local["ms_hist"] + ms_passes) * 1e-3) / 1e9
         roof["whole_sort"] = {"algorithmic_bytes": n_sorted * es * (1 + 2 * passes), "achieved": whole,
                               "frac": whole / peak, "frac_of_8TBs_nominal": whole / 8000.0,
