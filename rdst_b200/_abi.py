@@ -67,6 +67,8 @@ class Stats(C.Structure):
         ("tiles_per_pass", C.c_uint64),
         ("already_sorted", C.c_uint32),
         ("kernel_launches", C.c_uint32),
+        ("hybrid", C.c_uint32),
+        ("slow_segments", C.c_uint32),
     ]
 
     def as_dict(self):

@@ -24,6 +24,7 @@
 
 #include "hist.cuh"
 #include "splitters.cuh"
+#include "local_sort.cuh"
 #include "launch.h"
 #include "onesweep.cuh"
 #include "variants.h"
@@ -134,6 +135,12 @@ struct DeviceCtx {
     size_t lookback_bytes = 0;
     uint8_t* d_sample = nullptr;  // key-prefix samples (splitter choice of the sharded sort)
     size_t sample_bytes = 0;
+    // hybrid path: joint histogram [256][256] u64 | segment offsets [65537] u64 | tickets [512] u32
+    uint8_t* d_hyb = nullptr;
+    size_t hyb_bytes = 0;
+    uint64_t* h_joint = nullptr;  // pinned [65537]
+    cudaStream_t aux[4] = {};
+    cudaEvent_t aux_ev[5] = {};
     void* d_stage = nullptr;  // device copy of host data for b200_sort_host
     size_t stage_bytes = 0;
     void* h_bounce[2] = {nullptr, nullptr};  // pinned bounce buffers for pageable host memory
@@ -185,6 +192,9 @@ int get_ctx(int device, DeviceCtx** out) {
         for (auto& ev : c.bounce_ev) CUDA_TRY(cudaEventCreateWithFlags(&ev, cudaEventDisableTiming));
         CUDA_TRY(cudaMalloc(&c.d_small, SMALL_BYTES));
         CUDA_TRY(cudaMallocHost(&c.h_hist, size_t(MAX_LEVELS) * RADIX * 8));
+        CUDA_TRY(cudaMallocHost(&c.h_joint, size_t(RADIX * RADIX + 1) * 8));
+        for (auto& a : c.aux) CUDA_TRY(cudaStreamCreateWithFlags(&a, cudaStreamNonBlocking));
+        for (auto& ev : c.aux_ev) CUDA_TRY(cudaEventCreateWithFlags(&ev, cudaEventDisableTiming));
         c.ready = true;
     }
     *out = &c;
@@ -264,9 +274,10 @@ struct PassPlan {
 };
 
 int plan_pass(DeviceCtx& c, const Lowered& lo, uint64_t n, const void* a, const void* b, bool remap, int variant,
-              PassPlan* out, bool hot = false) {
+              PassPlan* out, bool hot = false, bool sub_array = false) {
     PassPlan pp{};
-    pp.word_path = word_path_ok(lo, a, b);
+    // sub-arrays of an aligned array start on a record boundary, which is all the word kernels need
+    pp.word_path = sub_array ? (lo.elem_size % 4 == 0 && lo.elem_size <= 16) : word_path_ok(lo, a, b);
     if (pp.word_path) {
         pp.words = lo.elem_size / 4;
         if (variant < 0) variant = default_variant(pp.words, n, c.sm_count);
@@ -302,7 +313,9 @@ int plan_pass(DeviceCtx& c, const Lowered& lo, uint64_t n, const void* a, const 
 int launch_pass(DeviceCtx& c, cudaStream_t st, const PassPlan& pp, const Lowered& lo, const void* src, void* dst,
                 uint64_t n, uint32_t level, const uint64_t* d_base, uint32_t* d_ticket, uint32_t tag,
                 const uint8_t* d_remap, const uint64_t* d_dst_tab = nullptr, const SplitParams* sp = nullptr,
-                const uint32_t* hot = nullptr, uint32_t match_bits = 0) {
+                const uint32_t* hot = nullptr, uint32_t match_bits = 0, uint64_t* lookback = nullptr,
+                const uint32_t* seg_tile_start = nullptr, const uint64_t* seg_rec_start = nullptr,
+                const uint64_t* seg_bases = nullptr) {
     if (pp.word_path) {
         PassParams p;
         memset(&p.sp, 0, sizeof(p.sp));
@@ -312,7 +325,7 @@ int launch_pass(DeviceCtx& c, cudaStream_t st, const PassPlan& pp, const Lowered
         p.n = n;
         p.dp = digit_params(lo, level);
         p.bucket_base = d_base;
-        p.lookback = c.d_lookback;
+        p.lookback = lookback ? lookback : c.d_lookback;
         p.ticket = d_ticket;
         p.tag = tag;
         p.num_tiles = pp.num_tiles;
@@ -321,6 +334,9 @@ int launch_pass(DeviceCtx& c, cudaStream_t st, const PassPlan& pp, const Lowered
         p.hot[0] = hot ? hot[0] : 0xffffffffu;
         p.hot[1] = hot ? hot[1] : 0xffffffffu;
         p.match_bits = match_bits;
+        p.seg_tile_start = seg_tile_start;
+        p.seg_rec_start = seg_rec_start;
+        p.seg_bases = seg_bases;
         pp.pl.kernel<<<pp.grid, pp.pl.threads, pp.pl.smem, st>>>(p);
     } else {
         BytePassParams p;
@@ -405,6 +421,26 @@ int launch_histogram(DeviceCtx& c, cudaStream_t st, const Lowered& lo, const voi
     return B200_OK;
 }
 
+// Word indices / xor / mask of the 64-bit key prefix (top min(LEVELS, 8) levels).  Only word-path
+// records with a contiguous key are supported; the caller falls back to digit splitters otherwise.
+int lower_prefix(const Lowered& lo, SplitParams* sp) {
+    memset(sp, 0, sizeof(*sp));
+    if (!lo.contiguous || lo.elem_size % 4 != 0 || lo.elem_size > 16 || lo.key_offset % 4 != 0) return B200_ERR_BAD_DESC;
+    if (lo.is_float && lo.levels != lo.key_width) return B200_ERR_BAD_DESC;
+    const uint32_t L = lo.levels, words = lo.elem_size / 4, kw0 = lo.key_offset / 4;
+    if (L > 16 || (L > 8 && (L - 8) % 4 != 0)) return B200_ERR_BAD_DESC;
+    const uint32_t first = L > 8 ? L - 8 : 0;  // lowest level inside the prefix
+    const uint32_t nl = L - first;              // 1..8 levels
+    sp->lo_word = kw0 + first / 4;
+    sp->hi_word = nl > 4 ? sp->lo_word + 1 : 0xffffffffu;
+    if (sp->lo_word >= words || (nl > 4 && sp->hi_word >= words)) return B200_ERR_BAD_DESC;
+    sp->mask = nl >= 8 ? ~0ull : ((1ull << (8 * nl)) - 1);
+    for (uint32_t i = 0; i < nl; ++i) sp->xorv |= uint64_t(lo.lv[first + i].xor_mask & 0xffu) << (8 * i);
+    sp->sign_word = kw0 + (L - 1) / 4;
+    sp->sign_shift = ((L - 1) % 4) * 8 + 7;
+    return B200_OK;
+}
+
 // Buckets holding more than 1/8 of the records are "hot": the half-warp pass kernel matches them by
 // ballot instead of a same-address shared-memory RED.OR (which serialises).  Measured gain is small
 // (+3 % on two-bucket levels, profiles/r1s_skew.txt), so only clearly skewed levels take this path.
@@ -431,6 +467,223 @@ static uint32_t match_bits_for(uint32_t parts) {
     uint32_t b = 1;
     while ((1u << b) < parts) ++b;
     return b;
+}
+
+// ---------------------------------------------------------------------------
+// Hybrid path: two global MSD passes (K2 on the two most significant active levels), then K3 sorts
+// every one of the 65 536 segments inside one SM's shared memory (local_sort.cuh).  The GPU form
+// of rdst's own MSB-then-LSB route (reference src/sorter.rs:24-171); results are identical to
+// the pure LSD path (both are THE stable order by the key).
+// ---------------------------------------------------------------------------
+constexpr size_t HYB_JOINT_OFF = 0;
+constexpr size_t HYB_SEG_OFF = size_t(RADIX) * RADIX * 8;
+constexpr size_t HYB_TICKET_OFF = HYB_SEG_OFF + (size_t(RADIX) * RADIX + 1) * 8 + 8;
+constexpr size_t HYB_TILESTART_OFF = HYB_TICKET_OFF + 4096;  // [257] u32
+constexpr size_t HYB_RECSTART_OFF = HYB_TILESTART_OFF + 2048;  // [257] u64
+constexpr size_t HYB_BYTES = HYB_RECSTART_OFF + 4096;
+
+int hybrid_mode() {  // 0 = never, 1 = whenever the key shape allows (tests), 2 = auto (default)
+    const char* env = getenv("B200SORT_HYBRID");
+    if (!env) return 2;
+    return atoi(env) == 0 ? 0 : (atoi(env) == 1 ? 1 : 2);
+}
+
+template <int WORDS>
+int launch_local_sort_w(bool floatk, int grid, cudaStream_t st, const LocalSortParams& lp) {
+    const size_t smem = LocalSmem<WORDS>::TOTAL;
+    if (floatk) {
+        CUDA_TRY(cudaFuncSetAttribute(local_sort_kernel<WORDS, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, int(smem)));
+        local_sort_kernel<WORDS, true><<<grid, LS_THREADS, smem, st>>>(lp);
+    } else {
+        CUDA_TRY(cudaFuncSetAttribute(local_sort_kernel<WORDS, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, int(smem)));
+        local_sort_kernel<WORDS, false><<<grid, LS_THREADS, smem, st>>>(lp);
+    }
+    CUDA_TRY(cudaGetLastError());
+    return B200_OK;
+}
+
+template <int WORDS>
+int launch_hist2_w(bool floatk, int grid, cudaStream_t st, const Hist2Params& hp) {
+    if (floatk)
+        hist2_kernel<WORDS, true><<<grid, H2_THREADS, 0, st>>>(hp);
+    else
+        hist2_kernel<WORDS, false><<<grid, H2_THREADS, 0, st>>>(hp);
+    CUDA_TRY(cudaGetLastError());
+    return B200_OK;
+}
+
+// Returns B200_OK with *done = true when the array was sorted here (result in `data`);
+// *done = false means "not eligible / segments too large": the caller runs the LSD passes.
+// *src_out tells the caller where the (possibly re-partitioned) records are.
+int sort_hybrid(DeviceCtx& c, cudaStream_t st, void* data, void* tmp, uint64_t n, const Lowered& lo,
+                const std::vector<uint32_t>& active, const unsigned long long* d_base, uint32_t* d_ticket, bool* done,
+                void** src_out, uint32_t* launches, uint32_t* slow_segments) {
+    *done = false;
+    *src_out = data;
+    const int mode = hybrid_mode();
+    if (mode == 0 || active.size() < 3) return B200_OK;
+    const uint32_t words = lo.elem_size / 4;
+    if (lo.elem_size % 4 != 0 || (words != 1 && words != 2) || lo.levels > 8) return B200_OK;
+    if (!word_path_ok(lo, data, tmp) || n >= (1ull << 32)) return B200_OK;
+    SplitParams key;
+    if (lower_prefix(lo, &key) != B200_OK) return B200_OK;
+    const uint32_t A1 = active[active.size() - 1], A2 = active[active.size() - 2];
+    const uint64_t* h1 = c.h_hist + size_t(A1) * RADIX;
+    const uint64_t* h2 = c.h_hist + size_t(A2) * RADIX;
+    if (mode == 2) {
+        // worth it from four active levels and ~16 M records on; and only when the segments can be
+        // expected to fit one SM (independence estimate; the exact check follows the joint histogram)
+        // (K3 handles one segment per SM at a time: segments below a few thousand records leave it idle)
+        if (active.size() < 4 || n < (256ull << 20)) return B200_OK;
+        uint64_t m1 = 0, m2 = 0;
+        for (int b = 0; b < RADIX; ++b) m1 = std::max(m1, h1[b]), m2 = std::max(m2, h2[b]);
+        if (double(m1) * double(m2) / double(n) > 0.97 * LS_CAP) return B200_OK;
+    }
+    int rc = ensure_bytes(reinterpret_cast<void**>(&c.d_hyb), &c.hyb_bytes, HYB_BYTES);
+    if (rc) return rc;
+    unsigned long long* d_joint = reinterpret_cast<unsigned long long*>(c.d_hyb + HYB_JOINT_OFF);
+    uint64_t* d_seg = reinterpret_cast<uint64_t*>(c.d_hyb + HYB_SEG_OFF);
+    uint32_t* d_tk = reinterpret_cast<uint32_t*>(c.d_hyb + HYB_TICKET_OFF);
+
+    static const bool dbg = getenv("B200SORT_DEBUG_TIMING") != nullptr;
+    if (dbg) cudaEventRecord(c.ev[3], st);
+    // ---- MSD pass 1: data -> tmp on level A1 (plain K2 pass) ----
+    PassPlan pp{};
+    rc = plan_pass(c, lo, n, data, tmp, false, -1, &pp);
+    if (rc) return rc;
+    const uint64_t tiles1 = pp.num_tiles;
+    // look-back words: pass 1 needs tiles1 rows; pass 2 at most n / small_tile + 256 rows
+    const uint64_t small_tile = 4096;
+    const size_t lb_rows = size_t(std::max<uint64_t>(tiles1, n / small_tile + 2 * RADIX + 1));
+    rc = ensure_bytes(reinterpret_cast<void**>(&c.d_lookback), &c.lookback_bytes, lb_rows * RADIX * 8);
+    if (rc) return rc;
+    CUDA_TRY(cudaMemsetAsync(c.d_lookback, 0, size_t(tiles1) * RADIX * 8, st));
+    CUDA_TRY(cudaMemsetAsync(d_ticket, 0, 1024, st));
+    CUDA_TRY(cudaMemsetAsync(c.d_hyb, 0, HYB_SEG_OFF, st));
+    CUDA_TRY(cudaMemsetAsync(d_tk, 0, 4096, st));
+    rc = launch_pass(c, st, pp, lo, data, tmp, n, A1, reinterpret_cast<const uint64_t*>(d_base + size_t(A1) * RADIX),
+                     d_ticket, 1, nullptr);
+    if (rc) return rc;
+    *launches += 1;
+    *src_out = tmp;
+    if (dbg) cudaEventRecord(c.ev[4], st);
+    // ---- joint histogram of (A1, A2) on the partitioned array = the 65 536 segment sizes ----
+    Hist2Params hp;
+    hp.src = static_cast<const uint32_t*>(tmp);
+    hp.n = n;
+    hp.l1 = digit_params(lo, A1);
+    hp.l2 = digit_params(lo, A2);
+    hp.joint = d_joint;
+    const int hgrid = int(std::min<uint64_t>(uint64_t(c.sm_count) * 8, (n + H2_CHUNK - 1) / H2_CHUNK));
+    rc = words == 1 ? launch_hist2_w<1>(lo.is_float, hgrid, st, hp) : launch_hist2_w<2>(lo.is_float, hgrid, st, hp);
+    if (rc) return rc;
+    *launches += 1;
+    CUDA_TRY(cudaMemcpyAsync(c.h_joint, d_joint, size_t(RADIX) * RADIX * 8, cudaMemcpyDeviceToHost, st));
+    if (dbg) cudaEventRecord(c.ev[5], st);
+    CUDA_TRY(cudaStreamSynchronize(st));
+    // ---- segment offsets; give up (LSD from `tmp`) if a segment does not fit one SM ----
+    uint64_t run = 0, max_seg = 0, nonempty = 0;
+    for (int b1 = 0; b1 < RADIX; ++b1) {
+        uint64_t in_bucket = 0;
+        for (int b2 = 0; b2 < RADIX; ++b2) {
+            const uint64_t cnt = c.h_joint[b1 * RADIX + b2];
+            c.h_joint[b1 * RADIX + b2] = run;
+            run += cnt;
+            in_bucket += cnt;
+            max_seg = std::max(max_seg, cnt);
+            nonempty += cnt ? 1 : 0;
+        }
+        if (in_bucket != h1[b1]) {
+            g_last_cuda_error = "hybrid: joint histogram disagrees with K1";
+            return B200_ERR_CUDA;
+        }
+    }
+    c.h_joint[RADIX * RADIX] = run;
+    if (run != n) {
+        g_last_cuda_error = "hybrid: joint histogram does not sum to n";
+        return B200_ERR_CUDA;
+    }
+    if (max_seg > uint64_t(LS_CAP)) return B200_OK;  // *done stays false, records are in tmp
+    CUDA_TRY(cudaMemcpyAsync(d_seg, c.h_joint, size_t(RADIX * RADIX + 1) * 8, cudaMemcpyHostToDevice, st));
+    // ---- MSD pass 2: tmp -> data on level A2, every A1 bucket partitioned on its own (segmented K2 launch) ----
+    uint32_t h_tile_start[RADIX + 1];
+    uint64_t h_rec_start[RADIX + 1];
+    {
+        uint64_t t = 0, rsum = 0;
+        for (int b1 = 0; b1 < RADIX; ++b1) {
+            h_tile_start[b1] = uint32_t(t);
+            h_rec_start[b1] = rsum;
+            t += (h1[b1] + pp.tile - 1) / pp.tile;
+            rsum += h1[b1];
+        }
+        h_tile_start[RADIX] = uint32_t(t);
+        h_rec_start[RADIX] = rsum;
+        if (t > lb_rows) {
+            g_last_cuda_error = "hybrid: look-back rows exhausted";
+            return B200_ERR_CUDA;
+        }
+    }
+    uint32_t* d_tile_start = reinterpret_cast<uint32_t*>(c.d_hyb + HYB_TILESTART_OFF);
+    uint64_t* d_rec_start = reinterpret_cast<uint64_t*>(c.d_hyb + HYB_RECSTART_OFF);
+    CUDA_TRY(cudaMemcpyAsync(d_tile_start, h_tile_start, sizeof(h_tile_start), cudaMemcpyHostToDevice, st));
+    CUDA_TRY(cudaMemcpyAsync(d_rec_start, h_rec_start, sizeof(h_rec_start), cudaMemcpyHostToDevice, st));
+    CUDA_TRY(cudaMemsetAsync(c.d_lookback, 0, size_t(h_tile_start[RADIX]) * RADIX * 8, st));
+    PassPlan p2 = pp;
+    p2.num_tiles = h_tile_start[RADIX];
+    {
+        int occ = 0;
+        CUDA_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, pp.pl.kernel, pp.pl.threads, pp.pl.smem));
+        p2.grid = int(std::min<uint64_t>(p2.num_tiles, uint64_t(c.sm_count) * std::max(occ, 1)));
+    }
+    const int k = 1;
+    rc = launch_pass(c, st, p2, lo, tmp, data, n, A2, d_seg, d_tk + 1, 1, nullptr, nullptr, nullptr, nullptr, 0, nullptr,
+                     d_tile_start, d_rec_start, d_seg);
+    if (rc) return rc;
+    *launches += 1;
+    if (dbg) cudaEventRecord(c.ev[6], st);
+    // ---- K3: every segment sorted in shared memory, in place in `data` ----
+    LocalSortParams lp;
+    memset(&lp, 0, sizeof(lp));
+    lp.data = static_cast<uint32_t*>(data);
+    lp.seg_off = d_seg;
+    lp.nseg = RADIX * RADIX;
+    lp.ticket = d_tk;
+    lp.nlev = uint32_t(active.size() - 2);
+    if (lp.nlev > uint32_t(LS_MAXLEV)) return B200_ERR_BAD_DESC;
+    for (uint32_t i = 0; i < lp.nlev; ++i) lp.lv[i] = digit_params(lo, active[i]);
+    // fast levels: as many of the top local levels as make runs of equal prefixes rare
+    const double avg = double(n) / double(std::max<uint64_t>(1, nonempty));
+    uint32_t nfast = avg <= 64.0 ? 1 : 2;
+    if (max_seg > 4096 * 4) nfast = 2;
+    if (nfast >= lp.nlev) nfast = 0;  // nothing would be left for the fix-up: plain LSD over all local levels
+    const char* force_slow = getenv("B200SORT_HYBRID_NFAST");
+    if (force_slow) nfast = uint32_t(atoi(force_slow)) < lp.nlev ? uint32_t(atoi(force_slow)) : 0;
+    lp.nfast = nfast;
+    lp.fix_shift = nfast ? 8 * active[lp.nlev - nfast] : 0;
+    lp.key = key;
+    lp.slow_segments = d_tk + 300;
+    const int lgrid = int(std::min<uint64_t>(uint64_t(c.sm_count), nonempty ? nonempty : 1));
+    rc = words == 1 ? launch_local_sort_w<1>(lo.is_float, lgrid, st, lp) : launch_local_sort_w<2>(lo.is_float, lgrid, st, lp);
+    if (rc) return rc;
+    *launches += 1;
+    if (slow_segments) {
+        CUDA_TRY(cudaMemcpyAsync(slow_segments, d_tk + 300, 4, cudaMemcpyDeviceToHost, st));
+    }
+    if (dbg) {
+        cudaEventRecord(c.ev[7], st);
+        cudaEventSynchronize(c.ev[7]);
+        float a = 0, b = 0, d = 0, e = 0;
+        cudaEventElapsedTime(&a, c.ev[3], c.ev[4]);
+        cudaEventElapsedTime(&b, c.ev[4], c.ev[5]);
+        cudaEventElapsedTime(&d, c.ev[5], c.ev[6]);
+        cudaEventElapsedTime(&e, c.ev[6], c.ev[7]);
+        fprintf(stderr, "[b200sort] hybrid: MSD pass 1 %.3f ms, joint hist + D2H %.3f ms, MSD pass 2 (%d launches) %.3f ms, K3 %.3f ms"
+                        " (max segment %llu, nfast %u of %u local levels)\n",
+                a, b, k, d, e, (unsigned long long)max_seg, nfast, lp.nlev);
+    }
+    *done = true;
+    *src_out = data;
+    return B200_OK;
 }
 
 // ---------------------------------------------------------------------------
@@ -478,6 +731,19 @@ int sort_device_impl(DeviceCtx& c, cudaStream_t st, void* data, void* tmp, uint6
     if (rc) return rc;
     void* src = data;
     void* dst = tmp;
+    // the Tuner's algorithm choice on the GPU: MSD x2 + on-chip segment sort for large inputs whose
+    // segments fit an SM, LSD passes otherwise (an explicit variant request always means LSD passes)
+    bool hybrid_done = false;
+    uint32_t hybrid_launches = 0, slow_segments = 0;
+    if (variant < 0) {
+        void* where = data;
+        rc = sort_hybrid(c, st, data, tmp, n, lo, active, d_base, d_ticket, &hybrid_done, &where, &hybrid_launches,
+                         &slow_segments);
+        if (rc) return rc;
+        if (!hybrid_done && where == tmp) std::swap(src, dst);  // MSD pass 1 ran: the records now live in tmp
+    }
+    const uint32_t n_active = uint32_t(active.size());
+    if (hybrid_done) active.clear();  // nothing left for the LSD loop
     if (!active.empty()) {
         const size_t lb_bytes = size_t(pp.num_tiles) * RADIX * 8;
         rc = ensure_bytes(reinterpret_cast<void**>(&c.d_lookback), &c.lookback_bytes, lb_bytes);
@@ -506,9 +772,12 @@ int sort_device_impl(DeviceCtx& c, cudaStream_t st, void* data, void* tmp, uint6
     if (result_ptr) *result_ptr = src;
     CUDA_TRY(cudaEventRecord(c.ev[2], st));
     CUDA_TRY(cudaStreamSynchronize(st));
+    if (hybrid_done) pass = n_active;  // levels the result is sorted on
     if (stats) {
         stats->levels_run = pass;
         stats->levels_skipped = lo.levels - pass;
+        stats->hybrid = hybrid_done ? 1u : 0u;
+        stats->slow_segments = slow_segments;
         stats->variant = uint32_t(pp.variant);
         stats->copy_back = copy_back;
         stats->algorithmic_bytes = n * lo.elem_size * (1ull + 2ull * pass) + (copy_back ? 2ull * n * lo.elem_size : 0);
@@ -516,7 +785,7 @@ int sort_device_impl(DeviceCtx& c, cudaStream_t st, void* data, void* tmp, uint6
         CUDA_TRY(cudaEventElapsedTime(&stats->ms_passes, c.ev[1], c.ev[2]));
         CUDA_TRY(cudaEventElapsedTime(&stats->ms_total, c.ev[0], c.ev[2]));
         stats->tiles_per_pass = pp.num_tiles;
-        stats->kernel_launches = 2 + pass;  // K1 + scan + one K2 per executed level
+        stats->kernel_launches = hybrid_done ? 2 + hybrid_launches : 2 + pass + hybrid_launches;  // K1 + scan + passes
     }
     return B200_OK;
 }
@@ -786,26 +1055,6 @@ int b200_partition_peers_device(const void* dev_src, void* const* dst_ptrs, size
 }
 
 // ---- full-resolution splitters (sample-sort style) for the sharded sort ----
-// Word indices / xor / mask of the 64-bit key prefix (top min(LEVELS, 8) levels).  Only word-path
-// records with a contiguous key are supported; the caller falls back to digit splitters otherwise.
-static int lower_prefix(const Lowered& lo, SplitParams* sp) {
-    memset(sp, 0, sizeof(*sp));
-    if (!lo.contiguous || lo.elem_size % 4 != 0 || lo.elem_size > 16 || lo.key_offset % 4 != 0) return B200_ERR_BAD_DESC;
-    if (lo.is_float && lo.levels != lo.key_width) return B200_ERR_BAD_DESC;
-    const uint32_t L = lo.levels, words = lo.elem_size / 4, kw0 = lo.key_offset / 4;
-    if (L > 16 || (L > 8 && (L - 8) % 4 != 0)) return B200_ERR_BAD_DESC;
-    const uint32_t first = L > 8 ? L - 8 : 0;  // lowest level inside the prefix
-    const uint32_t nl = L - first;              // 1..8 levels
-    sp->lo_word = kw0 + first / 4;
-    sp->hi_word = nl > 4 ? sp->lo_word + 1 : 0xffffffffu;
-    if (sp->lo_word >= words || (nl > 4 && sp->hi_word >= words)) return B200_ERR_BAD_DESC;
-    sp->mask = nl >= 8 ? ~0ull : ((1ull << (8 * nl)) - 1);
-    for (uint32_t i = 0; i < nl; ++i) sp->xorv |= uint64_t(lo.lv[first + i].xor_mask & 0xffu) << (8 * i);
-    sp->sign_word = kw0 + (L - 1) / 4;
-    sp->sign_shift = ((L - 1) % 4) * 8 + 7;
-    return B200_OK;
-}
-
 static int prefix_src(const void* dev_ptr, size_t n, const b200_key_desc* desc, Lowered* lo, PrefixSrc* ps) {
     int rc = lower_desc(desc, lo);
     if (rc) return rc;

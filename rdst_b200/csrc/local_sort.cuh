@@ -1,0 +1,292 @@
+// local_sort.cuh — K3, the shared-memory segment sort of the hybrid path.
+//
+// rdst's default route is MSB-first: split on the top byte, recurse into the 256 buckets, and
+// finish small buckets with an LSB sort that runs in cache (reference src/sorter.rs:24-171,
+// src/tuners/standard_tuner.rs:13-63, src/sorts/lsb_sort.rs:38-128).  The GPU analogue: after
+// two global MSD passes (K2 on the two most significant active levels) the array is 65 536
+// segments that each fit in one SM's shared memory (<= 16 384 records); one CTA then sorts a
+// segment completely on chip — read once, written once — instead of six more passes through HBM.
+//
+// Per segment: records live in registers (32 per thread, 512 threads); every local level is one
+// stable counting-sort step exactly like K2's tile step (half-warp OR-matching ranks, digit scan,
+// scatter into the staging buffer) followed by a read-back.  Fast path: only the top `nfast` local
+// levels are radix-sorted; what is left are short runs of records that agree on those levels, and
+// the thread at the head of each run insertion-sorts it by the whole key (stable).  Runs longer
+// than MAXRUN (duplicate-heavy or adversarial data) switch the segment to the slow path: a full
+// LSD over all local levels.  Both paths give the unique stable order, so the result is
+// bit-identical to the pure LSD engine.
+#pragma once
+#include "pass_or.cuh"
+
+namespace b200 {
+
+constexpr int LS_THREADS = 512, LS_ITEMS = 32, LS_CAP = LS_THREADS * LS_ITEMS;  // 16 384 records
+constexpr int LS_GROUPS = LS_THREADS / 16, LS_MAXRUN = 24, LS_MAXLEV = 8;
+
+struct LocalSortParams {
+    uint32_t* data;            // sorted in place, segment by segment
+    const uint64_t* seg_off;   // [nseg + 1] record offsets of the segments
+    uint32_t nseg;
+    uint32_t* ticket;          // zeroed before the launch
+    uint32_t nlev;             // local radix levels, least significant first
+    uint32_t nfast;            // fast path sorts only the top nfast of them (0 or nlev: always all)
+    uint32_t fix_shift;        // bits of the key image below the lowest fast level
+    DigitParams lv[LS_MAXLEV];
+    SplitParams key;           // 64-bit order-preserving image of the whole key (LEVELS <= 8)
+    uint32_t* slow_segments;   // telemetry: segments that fell back to the full LSD
+};
+
+template <int WORDS>
+struct LocalSmem {
+    static constexpr size_t OUT_BYTES = size_t(LS_CAP) * WORDS * 4;
+    static constexpr size_t SLOT_BYTES = size_t(LS_GROUPS) * RADIX * 4;
+    static constexpr size_t PART_BYTES = size_t(LS_THREADS) * 4;
+    static constexpr size_t MISC_BYTES = 128;
+    static constexpr size_t TOTAL = OUT_BYTES + SLOT_BYTES + PART_BYTES + MISC_BYTES;
+};
+
+template <int WORDS, bool FLOATK>
+__global__ void __launch_bounds__(LS_THREADS, 1) local_sort_kernel(const LocalSortParams p) {
+    using SM = LocalSmem<WORDS>;
+    constexpr int ITEMS = LS_ITEMS, THREADS = LS_THREADS, GROUPS = LS_GROUPS;
+    constexpr int GPH = GROUPS / 2;  // two threads per digit in the digit phase
+    extern __shared__ __align__(128) uint8_t smem_raw[];
+    uint32_t* s_out = reinterpret_cast<uint32_t*>(smem_raw);
+    uint8_t* s_slot_raw = smem_raw + SM::OUT_BYTES;
+    uint32_t* s_part = reinterpret_cast<uint32_t*>(smem_raw + SM::OUT_BYTES + SM::SLOT_BYTES);
+    uint8_t* misc = smem_raw + SM::OUT_BYTES + SM::SLOT_BYTES + SM::PART_BYTES;
+    volatile uint32_t* s_seg = reinterpret_cast<volatile uint32_t*>(misc);       // [0] segment id, [1] slow-path flag
+    uint32_t* s_wtot = reinterpret_cast<uint32_t*>(misc + 32);                   // 8 digit-warp totals
+
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const uint32_t lane_bit = 1u << (lane & 15);
+    const uint32_t lt_mask = lane_bit - 1u;
+    const uint32_t slot_base = smem_u32(s_slot_raw);
+    const uint32_t my_slots = slot_base + uint32_t(tid >> 4) * RADIX * 4;
+    const uint32_t dg = tid & (RADIX - 1), h = tid / RADIX;
+
+    {
+        uint4* z = reinterpret_cast<uint4*>(s_slot_raw);
+        for (int i = tid; i < int(SM::SLOT_BYTES / 16); i += THREADS) z[i] = make_uint4(0, 0, 0, 0);
+    }
+
+    while (true) {
+        __syncthreads();  // previous segment's write-out done; slots clean
+        if (tid == 0) {
+            s_seg[0] = atomicAdd(p.ticket, 1u);
+            s_seg[1] = 0;
+        }
+        __syncthreads();
+        const uint32_t seg = s_seg[0];
+        if (seg >= p.nseg) break;
+        const uint64_t base = p.seg_off[seg];
+        const uint32_t cnt = uint32_t(p.seg_off[seg + 1] - base);
+        if (cnt <= 1) continue;
+        uint32_t* g = p.data + base * WORDS;
+        // records per thread actually used: element (group, j, lane16) = group*16*IT + j*16 + lane16,
+        // so that every half-warp owns a contiguous run and (group, j, lane) order is memory order
+        const uint32_t IT = (cnt + THREADS - 1) / THREADS;
+        const uint32_t e0 = uint32_t(tid >> 4) * 16u * IT + (lane & 15);
+
+        Rec<WORDS> r[ITEMS];
+#pragma unroll
+        for (int j = 0; j < ITEMS; ++j) {
+            const uint32_t e = e0 + j * 16;
+            if (uint32_t(j) < IT && e < cnt) {
+                r[j] = load_rec<WORDS>(g, e);
+            } else {
+#pragma unroll
+                for (int k = 0; k < WORDS; ++k) r[j].w[k] = 0;
+            }
+        }
+
+        bool fast = p.nfast > 0 && p.nfast < p.nlev;
+        uint32_t li = fast ? p.nlev - p.nfast : 0;
+        while (true) {  // one trip on the fast path; a second, over all levels, if a run was too long
+            for (; li < p.nlev; ++li) {
+                const DigitParams dp = p.lv[li];
+                // ---- rank inside the half-warp by OR-matching (as K2) ----
+                uint32_t rk[ITEMS / 2];
+#pragma unroll
+                for (int q = 0; q < ITEMS / 2; ++q) rk[q] = 0;
+#pragma unroll
+                for (int j = 0; j < ITEMS; ++j) {
+                    if (uint32_t(j) < IT) {
+                        const uint32_t e = e0 + j * 16;
+                        uint32_t d = 255u;  // padding sorts behind every record
+                        if (e < cnt) d = rec_digit<WORDS, FLOATK>(dp, r[j]);
+                        const uint32_t sa = my_slots + d * 4;
+                        slot_or(sa, lane_bit);
+                        __syncwarp();
+                        const uint32_t v = lds_u32(sa);
+                        __syncwarp();
+                        const uint32_t m = v & 0xffffu, c = v >> 16;
+                        const uint32_t lt = m & lt_mask;
+                        if (lt == 0) sts_u32(sa, (c + __popc(m)) << 16);
+                        __syncwarp();
+                        rk[j / 2] |= (c + __popc(lt)) << ((j & 1) * 16);
+                    }
+                }
+                __syncthreads();
+                // ---- two threads per digit: counts of my 16 groups -> positions in the sorted segment ----
+                uint32_t gc[GPH], part = 0, sum = 0, before = 0, incl = 0;
+                {
+                    const uint32_t ca = slot_base + (h * GPH * RADIX + dg) * 4;
+#pragma unroll
+                    for (int w = 0; w < GPH; ++w) {
+                        gc[w] = lds_u32(ca + w * RADIX * 4) >> 16;
+                        part += gc[w];
+                    }
+                    s_part[tid] = part;
+                }
+                __syncthreads();
+                {
+                    const uint32_t x0 = s_part[dg], x1 = s_part[RADIX + dg];
+                    sum = x0 + x1;
+                    before = h ? x0 : 0u;
+                    incl = sum;
+#pragma unroll
+                    for (int o = 1; o < 32; o <<= 1) {
+                        const uint32_t y = __shfl_up_sync(0xffffffffu, incl, o);
+                        if (lane >= o) incl += y;
+                    }
+                    if (h == 0 && lane == 31) s_wtot[warp] = incl;
+                }
+                __syncthreads();
+                {
+                    uint32_t wbase = 0;
+#pragma unroll
+                    for (int w = 0; w < RADIX / 32; ++w)
+                        if (uint32_t(w) < dg / 32) wbase += s_wtot[w];
+                    const uint32_t ca = slot_base + (h * GPH * RADIX + dg) * 4;
+                    uint32_t run = wbase + incl - sum + before;
+#pragma unroll
+                    for (int w = 0; w < GPH; ++w) {
+                        sts_u32(ca + w * RADIX * 4, run << 16);
+                        run += gc[w];
+                    }
+                }
+                __syncthreads();
+                // ---- scatter into the staging buffer in sorted order ----
+#pragma unroll
+                for (int j = 0; j < ITEMS; ++j) {
+                    if (uint32_t(j) < IT) {
+                        const uint32_t e = e0 + j * 16;
+                        uint32_t d = 255u;
+                        if (e < cnt) d = rec_digit<WORDS, FLOATK>(dp, r[j]);
+                        const uint32_t pos = (lds_u32(my_slots + d * 4) >> 16) + ((rk[j / 2] >> ((j & 1) * 16)) & 0xffffu);
+                        store_rec<WORDS>(s_out, pos, r[j]);
+                    }
+                }
+                __syncwarp();
+                {
+                    uint4* z = reinterpret_cast<uint4*>(s_slot_raw + size_t(warp) * 2 * RADIX * 4);
+#pragma unroll
+                    for (int i = lane; i < 2 * RADIX * 4 / 16; i += 32) z[i] = make_uint4(0, 0, 0, 0);
+                }
+                __syncthreads();
+                if (li + 1 < p.nlev) {
+                    // read back in element order for the next level
+#pragma unroll
+                    for (int j = 0; j < ITEMS; ++j) {
+                        const uint32_t e = e0 + j * 16;
+                        if (uint32_t(j) < IT && e < cnt) r[j] = load_rec<WORDS>(s_out, e);
+                    }
+                    __syncthreads();  // everyone has its records before the next scatter overwrites them
+                }
+            }
+            if (!fast) break;
+            // ---- fix-up: runs of records equal on the fast levels, ordered by the rest of the key ----
+            const uint32_t sh = p.fix_shift;
+            for (uint32_t i = tid; i < cnt; i += THREADS) {
+                const uint64_t ki = rec_prefix<WORDS, FLOATK>(p.key, load_rec<WORDS>(s_out, i)) >> sh;
+                const bool same_prev = i > 0 && (rec_prefix<WORDS, FLOATK>(p.key, load_rec<WORDS>(s_out, i - 1)) >> sh) == ki;
+                if (same_prev || i + 1 >= cnt) continue;
+                if ((rec_prefix<WORDS, FLOATK>(p.key, load_rec<WORDS>(s_out, i + 1)) >> sh) != ki) continue;
+                // i heads a run of at least two records: find its end
+                uint32_t q = i + 2;
+                while (q < cnt && q - i <= uint32_t(LS_MAXRUN) &&
+                       (rec_prefix<WORDS, FLOATK>(p.key, load_rec<WORDS>(s_out, q)) >> sh) == ki)
+                    ++q;
+                if (q - i > uint32_t(LS_MAXRUN)) {
+                    s_seg[1] = 1;  // too long for an insertion sort: the whole segment takes the slow path
+                    continue;
+                }
+                for (uint32_t a = i + 1; a < q; ++a) {  // stable insertion sort by the whole key image
+                    const Rec<WORDS> x = load_rec<WORDS>(s_out, a);
+                    const uint64_t kx = rec_prefix<WORDS, FLOATK>(p.key, x);
+                    uint32_t b = a;
+                    while (b > i) {
+                        const Rec<WORDS> y = load_rec<WORDS>(s_out, b - 1);
+                        if (rec_prefix<WORDS, FLOATK>(p.key, y) <= kx) break;
+                        store_rec<WORDS>(s_out, b, y);
+                        --b;
+                    }
+                    if (b != a) store_rec<WORDS>(s_out, b, x);
+                }
+            }
+            __syncthreads();
+            if (s_seg[1] == 0) break;
+            // slow path: the staging buffer holds a stable rearrangement of the segment; start over with
+            // a full LSD over every local level
+            if (tid == 0 && p.slow_segments) atomicAdd(p.slow_segments, 1u);
+#pragma unroll
+            for (int j = 0; j < ITEMS; ++j) {
+                const uint32_t e = e0 + j * 16;
+                if (uint32_t(j) < IT && e < cnt) r[j] = load_rec<WORDS>(s_out, e);
+            }
+            __syncthreads();
+            fast = false;
+            li = 0;
+        }
+        // ---- write-out: the sorted segment goes back where it came from, coalesced ----
+        for (uint32_t i = tid; i < cnt; i += THREADS) store_rec<WORDS>(g, uint64_t(i), load_rec<WORDS>(s_out, i));
+    }
+}
+
+}  // namespace b200
+
+namespace b200 {
+
+// Joint histogram of two levels for an array already partitioned (stably) on the first of them:
+// joint[d1][d2] = records with digit d1 on level A1 and d2 on level A2, i.e. the sizes of the
+// 65 536 segments the second MSD pass produces.  A CTA works on contiguous chunks; a chunk of an
+// array sorted by d1 spans few d1 values, so counts go to a small shared table first.
+constexpr int H2_THREADS = 256, H2_CHUNK = 16384, H2_SPAN = 4;
+struct Hist2Params {
+    const uint32_t* src;
+    uint64_t n;
+    DigitParams l1, l2;
+    unsigned long long* joint;  // [256][256], zeroed before the launch
+};
+
+template <int WORDS, bool FLOATK>
+__global__ void __launch_bounds__(H2_THREADS) hist2_kernel(const Hist2Params p) {
+    __shared__ uint32_t sh[H2_SPAN * RADIX];
+    const uint64_t chunks = (p.n + H2_CHUNK - 1) / H2_CHUNK;
+    for (uint64_t ch = blockIdx.x; ch < chunks; ch += gridDim.x) {
+        for (int i = threadIdx.x; i < H2_SPAN * RADIX; i += H2_THREADS) sh[i] = 0;
+        const uint64_t lo = ch * H2_CHUNK;
+        const uint64_t hi = lo + H2_CHUNK < p.n ? lo + H2_CHUNK : p.n;
+        const uint32_t dfirst = rec_digit<WORDS, FLOATK>(p.l1, load_rec<WORDS>(p.src + lo * WORDS, 0));
+        __syncthreads();
+        for (uint64_t i = lo + threadIdx.x; i < hi; i += H2_THREADS) {
+            const Rec<WORDS> r = load_rec<WORDS>(p.src + i * WORDS, 0);
+            const uint32_t d1 = rec_digit<WORDS, FLOATK>(p.l1, r), d2 = rec_digit<WORDS, FLOATK>(p.l2, r);
+            const uint32_t rel = d1 - dfirst;
+            if (rel < uint32_t(H2_SPAN))
+                atomicAdd(&sh[rel * RADIX + d2], 1u);
+            else
+                atomicAdd(p.joint + size_t(d1) * RADIX + d2, 1ull);
+        }
+        __syncthreads();
+        for (int i = threadIdx.x; i < H2_SPAN * RADIX; i += H2_THREADS) {
+            const uint32_t c = sh[i];
+            const uint32_t d1 = dfirst + i / RADIX;
+            if (c && d1 < uint32_t(RADIX)) atomicAdd(p.joint + size_t(d1) * RADIX + (i % RADIX), (unsigned long long)c);
+        }
+        __syncthreads();
+    }
+}
+
+}  // namespace b200

@@ -62,19 +62,32 @@ __global__ void __launch_bounds__(THREADS, MINB) lsd_pass_or16_kernel(const Pass
         for (int i = tid; i < int(SM::SLOT_BYTES / 16); i += THREADS) z[i] = make_uint4(0, 0, 0, 0);
     }
 
-    auto tile_valid = [&](uint32_t t) -> uint32_t {
-        const uint64_t rem = p.n - uint64_t(t) * TILE;
+    // segmented mode: (bucket, first tile of the bucket, first record, records) of a tile
+    const bool seg = !REMAP && p.seg_tile_start != nullptr;
+    auto seg_find = [&](uint32_t t) -> uint32_t {  // bucket b with seg_tile_start[b] <= t < seg_tile_start[b + 1]
+        uint32_t lo = 0, hi = RADIX;               // invariant: start[lo] <= t < start[hi]
+        while (hi - lo > 1) {
+            const uint32_t mid = (lo + hi) >> 1;
+            if (__ldg(p.seg_tile_start + mid) <= t) lo = mid; else hi = mid;
+        }
+        return lo;
+    };
+    uint32_t cur_b = 0, cur_t0 = 0;  // bucket of the current tile and its first tile
+    auto tile_valid_at = [&](uint32_t t, uint32_t b, uint32_t t0) -> uint32_t {
+        const uint64_t nrec = seg ? __ldg(p.seg_rec_start + b + 1) - __ldg(p.seg_rec_start + b) : p.n;
+        const uint64_t rem = nrec - uint64_t(t - t0) * TILE;
         return rem < uint64_t(TILE) ? uint32_t(rem) : uint32_t(TILE);
     };
     // element (half-warp h, j, lane16) = h*16*ITEMS + j*16 + lane16: every half-warp owns a
     // contiguous run of the tile, so (h, j, lane16) order is memory order
     const uint32_t e0 = uint32_t(tid >> 4) * 16u * ITEMS + (lane & 15);
     Rec<WORDS> r[ITEMS];
-    auto load_tile = [&](uint32_t t) {
+    auto load_tile = [&](uint32_t t, uint32_t b, uint32_t t0) {
         if (t >= p.num_tiles) return;
-        const uint32_t v = tile_valid(t);
+        const uint32_t v = tile_valid_at(t, b, t0);
         const bool f = v == uint32_t(TILE);
-        const uint32_t* g = p.src + uint64_t(t) * TILE * WORDS;
+        const uint64_t first = (seg ? __ldg(p.seg_rec_start + b) : 0ull) + uint64_t(t - t0) * TILE;
+        const uint32_t* g = p.src + first * WORDS;
 #pragma unroll
         for (int j = 0; j < ITEMS; ++j) {
             const uint32_t e = e0 + j * 16;
@@ -90,14 +103,25 @@ __global__ void __launch_bounds__(THREADS, MINB) lsd_pass_or16_kernel(const Pass
     // Tiles are claimed in ticket order, one ahead: while a tile is processed the next one
     // is already claimed, and its records are fetched as soon as the registers are free
     // (right after the scatter), so the loads fly during the look-back and the write-out.
-    if (tid == 0) s_tile[0] = atomicAdd(p.ticket, 1u);
+    if (tid == 0) {
+        const uint32_t t = atomicAdd(p.ticket, 1u);
+        s_tile[0] = t;
+        s_tile[2] = (seg && t < p.num_tiles) ? seg_find(t) : 0u;
+    }
     __syncthreads();  // first tile id visible; slots are clean
     uint32_t tile = s_tile[0];
-    load_tile(tile);
+    cur_b = s_tile[2];
+    cur_t0 = seg ? __ldg(p.seg_tile_start + cur_b) : 0u;
+    load_tile(tile, cur_b, cur_t0);
 
     while (tile < p.num_tiles) {
-        if (tid == 0) s_tile[1] = atomicAdd(p.ticket, 1u);  // read by everyone after barrier (B)
-        const uint32_t valid = tile_valid(tile);
+        if (tid == 0) {  // read by everyone after barrier (B)
+            const uint32_t t = atomicAdd(p.ticket, 1u);
+            s_tile[1] = t;
+            s_tile[3] = (seg && t < p.num_tiles) ? seg_find(t) : 0u;
+        }
+        const uint32_t valid = tile_valid_at(tile, cur_b, cur_t0);
+        const bool first_tile = tile == cur_t0;  // head of its look-back chain
         const bool full = valid == uint32_t(TILE);
 
         // ---- rank inside the warp by OR-matching; stable: lanes in order, rounds in order ----
@@ -209,7 +233,7 @@ __global__ void __launch_bounds__(THREADS, MINB) lsd_pass_or16_kernel(const Pass
             cnt = sum;
             if (dg == RADIX - 1) cnt -= uint32_t(TILE) - valid;
             if (h == 0)
-                lb_store(&p.lookback[uint64_t(tile) * RADIX + dg], lb_pack(tile == 0 ? LB_PREFIX : LB_AGG, p.tag, cnt));
+                lb_store(&p.lookback[uint64_t(tile) * RADIX + dg], lb_pack(first_tile ? LB_PREFIX : LB_AGG, p.tag, cnt));
             incl = sum;
 #pragma unroll
             for (int o = 1; o < 32; o <<= 1) {
@@ -251,7 +275,9 @@ __global__ void __launch_bounds__(THREADS, MINB) lsd_pass_or16_kernel(const Pass
             store_rec<WORDS>(s_out, pos, r[j]);
         }
         const uint32_t next_tile = s_tile[1];
-        load_tile(next_tile);  // registers are free again: fetch the next tile now
+        const uint32_t next_b = s_tile[3];
+        const uint32_t next_t0 = seg ? __ldg(p.seg_tile_start + next_b) : 0u;
+        load_tile(next_tile, next_b, next_t0);  // registers are free again: fetch the next tile now
         __syncwarp();
         // this warp's slots are only read by this warp: reset them for the next tile now
         {
@@ -263,7 +289,7 @@ __global__ void __launch_bounds__(THREADS, MINB) lsd_pass_or16_kernel(const Pass
         // ---- decoupled look-back, one thread per digit, LB_BATCH predecessors per round trip ----
         if (tid < RADIX) {
             uint64_t excl = 0;
-            if (tile > 0) {
+            if (!first_tile) {
                 int64_t t = int64_t(tile) - 1;
                 bool done = false;
                 while (!done) {
@@ -293,7 +319,8 @@ __global__ void __launch_bounds__(THREADS, MINB) lsd_pass_or16_kernel(const Pass
                 s_gofs[tid] = p.bucket_base[tid] + excl - local_off;
                 s_gptr[tid] = p.dst_tab[tid];
             } else {
-                const uint64_t go = p.bucket_base[tid] + excl - local_off;
+                const uint64_t bb = seg ? __ldg(p.seg_bases + size_t(cur_b) * RADIX + tid) : p.bucket_base[tid];
+                const uint64_t go = bb + excl - local_off;
                 s_gofs[tid] = go;
                 s_gofs32[tid] = uint32_t(go);
                 if (REMAP) s_gptr[tid] = reinterpret_cast<uint64_t>(p.dst);
@@ -345,6 +372,8 @@ __global__ void __launch_bounds__(THREADS, MINB) lsd_pass_or16_kernel(const Pass
         }
         // barriers (B)..(C) of the next iteration order this write-out before the next scatter
         tile = next_tile;
+        cur_b = next_b;
+        cur_t0 = next_t0;
     }
 }
 

@@ -518,3 +518,86 @@ def test_config4_struct_100m_stable_property():
     assert bool((idx[1:][same] > idx[:-1][same]).all())
     assert int(idx.to(torch.int64).sum()) == n * (n - 1) // 2
     _abi.lib().b200_release_scratch(-1)
+
+
+# ---------------------------------------------------------------------------------------------
+# Hybrid path (two MSD passes + K3 shared-memory segment sort): must give the oracle's answer
+# bit for bit on every input the LSD path handles.  B200SORT_HYBRID=1 forces it at small sizes.
+# ---------------------------------------------------------------------------------------------
+def _hybrid_cases():
+    rng = np.random.default_rng(977)
+    n = 1_500_007
+    yield "u64_uniform", "u8", rng.integers(0, 2**64, n, dtype="u8"), True
+    yield "i64_uniform", "i8", rng.integers(-2**63, 2**63 - 1, n, dtype="i8"), True
+    yield "f64_normal", "f8", rng.standard_normal(n), None  # few sign/exponent values: segments may be too large
+    yield "f64_bits", "f8", rand_bits(rng, "f8", n), True
+    yield "u32_uniform", "u4", rng.integers(0, 2**32, n, dtype="u4"), True
+    yield "f32_bits", "f4", rand_bits(rng, "f4", n), True
+    yield "i32_uniform", "i4", rng.integers(-2**31, 2**31 - 1, n, dtype="i4"), True
+    # few distinct values: long runs of equal fast-level prefixes -> slow path inside K3
+    yield "u64_dups", "u8", rng.integers(0, 3000, n, dtype="u8") * np.uint64(0x0001000100010001), True
+    # segments of ~6 k records (16 x 16 top-byte values): the big-segment regime of the 1 B-key run
+    top = (rng.integers(0, 16, n, dtype="u8") << np.uint64(56)) | (rng.integers(0, 16, n, dtype="u8") << np.uint64(48))
+    yield "u64_big_segments", "u8", top | rng.integers(0, 2**48, n, dtype="u8"), True
+    yield "u64_big_segments_dups", "u8", top | (rng.integers(0, 50, n, dtype="u8") << np.uint64(20)), True
+    # 4 x 4 top-byte values: segments of ~94 k records do not fit an SM -> falls back to LSD from the scratch buffer
+    top4 = (rng.integers(0, 4, n, dtype="u8") << np.uint64(56)) | (rng.integers(0, 4, n, dtype="u8") << np.uint64(48))
+    yield "u64_segments_too_large", "u8", top4 | rng.integers(0, 2**48, n, dtype="u8"), False
+    # trivial levels in the middle and on top (level skip inside the hybrid plan)
+    yield "u64_masked", "u8", rng.integers(0, 2**64, n, dtype="u8") & np.uint64(0x00FFFF00FFFF00FF), True
+    z = np.minimum(rng.zipf(1.1, n), 2**32).astype("u8")
+    yield "u64_zipf_hashed", "u8", (z * np.uint64(0x9E3779B97F4A7C15)) ^ (z >> np.uint64(7)), None
+    yield "u64_sorted", "u8", np.sort(rng.integers(0, 2**64, n, dtype="u8")), True
+    yield "u64_reverse", "u8", np.sort(rng.integers(0, 2**64, n, dtype="u8"))[::-1].copy(), True
+    yield "u64_tiny", "u8", rng.integers(0, 2**64, 1000, dtype="u8"), True
+
+
+@pytest.mark.parametrize("name,dt,a,expect_hybrid", list(_hybrid_cases()), ids=[c[0] for c in _hybrid_cases()])
+def test_hybrid_path_matches_oracle(monkeypatch, name, dt, a, expect_hybrid):
+    torch = torch_mod()
+    monkeypatch.setenv("B200SORT_HYBRID", "1")
+    key = RadixKey.for_dtype(dt)
+    exp = o.sorted_copy(a, key)
+    t = torch.from_numpy(np.ascontiguousarray(a).view(np.uint8).reshape(-1).copy()).cuda()
+    b = radix_sort_builder(t, key)
+    b.sort()
+    torch.cuda.synchronize()
+    assert t.cpu().numpy().tobytes() == exp.tobytes(), name
+    if expect_hybrid is not None:
+        assert bool(b.stats["hybrid"]) == expect_hybrid, (name, b.stats)
+    if name == "u64_dups":
+        assert b.stats["slow_segments"] > 0
+    # the host entry point takes the same route
+    h = a.copy()
+    radix_sort_unstable(h)
+    assert h.tobytes() == exp.tobytes(), name
+    # and both fast-level settings of K3 agree (nfast = 1 leaves more to the insertion fix-up)
+    monkeypatch.setenv("B200SORT_HYBRID_NFAST", "1")
+    t2 = torch.from_numpy(np.ascontiguousarray(a).view(np.uint8).reshape(-1).copy()).cuda()
+    radix_sort_builder(t2, key).sort()
+    torch.cuda.synchronize()
+    assert t2.cpu().numpy().tobytes() == exp.tobytes(), name + " nfast=1"
+
+
+def test_hybrid_is_stable_for_key_plus_payload_of_one_word():
+    """8-byte records {u32 key, u32 payload}: K3's fix-up and slow path must keep input order among equal keys."""
+    import os
+
+    torch = torch_mod()
+    rec = np.dtype([("key", "<u4"), ("idx", "<u4")])
+    rng = np.random.default_rng(31)
+    a = np.zeros(1_200_000, dtype=rec)
+    a["key"] = rng.integers(0, 1 << 31, len(a)) & 0xFFFF0FFF
+    a["key"][::300] = 12345  # 4000 equal keys: one long run (slow path), still one segment
+    a["idx"] = np.arange(len(a))
+    key = RadixKey.field(rec, "key", 4)
+    os.environ["B200SORT_HYBRID"] = "1"
+    try:
+        t = torch.from_numpy(a.view(np.uint8).copy()).cuda()
+        b = radix_sort_builder(t, key).with_stable(True)
+        b.sort()
+        torch.cuda.synchronize()
+    finally:
+        del os.environ["B200SORT_HYBRID"]
+    assert b.stats["hybrid"] == 1
+    assert t.cpu().numpy().tobytes() == o.stable_sorted(a, key).tobytes()
