@@ -384,25 +384,49 @@ def run_b200(args):
     ms_passes = float(st_local.get("ms_passes", 0.0))
     n_sorted = int(last.get("n_recv", n)) if world > 1 else n
     roof = None
+    traffic_db = {}
+    try:  # dram bytes per launch from the committed ncu --set full captures
+        traffic_db = json.load(open(os.path.join(ROOT, "profiles", "k2_traffic.json")))
+    except Exception:
+        pass
     if passes and ms_passes > 0:
-        per_launch_bytes = 2 * n_sorted * es
-        ach = per_launch_bytes * passes / (ms_passes * 1e-3) / 1e9
-        roof = {"bound": "hbm", "kernel": "K2 LSD pass (lsd_pass_or16_kernel, variant " + str(st_local.get("variant")) + ")", "achieved": ach, "peak": peak, "unit": "GB/s",
-                "frac": ach / peak, "traffic": None, "peak_source": peak_src,
-                "algorithmic_bytes_per_launch": per_launch_bytes, "launches_per_step": passes,
-                "avg_launch_ms": ms_passes / passes,
-                "how": "CUDA events recorded by the library on the launch stream around the K2 passes of the last step"}
-        try:  # dram bytes per launch from the committed ncu --set full capture of this workload
-            tr = json.load(open(os.path.join(ROOT, "profiles", "k2_traffic.json"))).get(args.workload)
-            if tr and tr["records"] == n_sorted:
-                roof["traffic"] = tr["traffic_bytes_per_launch"]
-                roof["traffic_source"] = "profiles/k2_traffic.json (ncu dram__bytes_read.sum + dram__bytes_write.sum, one launch)"
-        except Exception:
-            pass
-        whole = n_sorted * es * (1 + 2 * passes) / ((st_local["ms_hist"] + ms_passes) * 1e-3) / 1e9
-        roof["whole_sort"] = {"algorithmic_bytes": n_sorted * es * (1 + 2 * passes), "achieved": whole,
-                              "frac": whole / peak, "frac_of_8TBs_nominal": whole / 8000.0,
-                              "ms_hist": st_local["ms_hist"], "ms_passes": ms_passes}
+        hybrid = bool(st_local.get("hybrid"))
+        whole_bytes = n_sorted * es * (1 + 2 * passes)
+        whole = whole_bytes / ((st_local["ms_hist"] + ms_passes) * 1e-3) / 1e9
+        if hybrid:
+            # dominant kernel = K3: it does the work of `local_levels` LSD passes on chip
+            nl = int(st_local["local_levels"])
+            ms_k3 = float(st_local["ms_local"])
+            ms_k2 = (ms_passes - ms_k3 - float(st_local["ms_joint"])) / 2.0
+            per_launch_bytes = 2 * n_sorted * es * nl
+            ach = per_launch_bytes / (ms_k3 * 1e-3) / 1e9
+            roof = {"bound": "hbm", "kernel": f"K3 local_sort_kernel: shared-memory segment sort covering {nl} of the {passes} levels "
+                                              "(hybrid path: 2 MSD K2 passes + K3)",
+                    "achieved": ach, "peak": peak, "unit": "GB/s", "frac": ach / peak, "traffic": None, "peak_source": peak_src,
+                    "algorithmic_bytes_per_launch": per_launch_bytes, "launches_per_step": 1, "avg_launch_ms": ms_k3,
+                    "how": "algorithmic bytes = 2*n*S per level K3 sorts (SURVEY 8d) / the library's CUDA-event time of K3 in the last "
+                           "step; K3 reads and writes every record once (see traffic), the levels run in shared memory",
+                    "k2_msd_pass": {"kernel": "lsd_pass_or16_kernel, variant " + str(st_local.get("variant")),
+                                    "algorithmic_bytes_per_launch": 2 * n_sorted * es, "launches_per_step": 2, "avg_launch_ms": ms_k2,
+                                    "achieved": 2 * n_sorted * es / (ms_k2 * 1e-3) / 1e9,
+                                    "frac": 2 * n_sorted * es / (ms_k2 * 1e-3) / 1e9 / peak},
+                    "ms_joint_histogram": float(st_local["ms_joint"]), "slow_segments": int(st_local.get("slow_segments", 0))}
+            tr = traffic_db.get(args.workload + ":k3")
+        else:
+            per_launch_bytes = 2 * n_sorted * es
+            ach = per_launch_bytes * passes / (ms_passes * 1e-3) / 1e9
+            roof = {"bound": "hbm", "kernel": "K2 LSD pass (lsd_pass_or16_kernel, variant " + str(st_local.get("variant")) + ")",
+                    "achieved": ach, "peak": peak, "unit": "GB/s", "frac": ach / peak, "traffic": None, "peak_source": peak_src,
+                    "algorithmic_bytes_per_launch": per_launch_bytes, "launches_per_step": passes,
+                    "avg_launch_ms": ms_passes / passes,
+                    "how": "CUDA events recorded by the library on the launch stream around the K2 passes of the last step"}
+            tr = traffic_db.get(args.workload)
+        if tr and tr.get("records") == n_sorted:
+            roof["traffic"] = tr["traffic_bytes_per_launch"]
+            roof["traffic_source"] = "profiles/k2_traffic.json (ncu dram__bytes_read.sum + dram__bytes_write.sum, one launch)"
+        roof["whole_sort"] = {"algorithmic_bytes": whole_bytes, "achieved": whole, "frac": whole / peak,
+                              "frac_of_8TBs_nominal": whole / 8000.0, "ms_hist": st_local["ms_hist"], "ms_passes": ms_passes,
+                              "path": "hybrid (K1, K2 x2, joint histogram, K3)" if hybrid else "LSD (K1, K2 per level)"}
     cb = None
     if world == 1 and not args.no_cpu:
         cb = cpu_baseline(dtype, gen, args.cpu_steps, 1, min(args.cpu_sample, n))

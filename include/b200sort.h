@@ -105,6 +105,9 @@ typedef struct {
     uint32_t kernel_launches;  /* kernels of this library launched by the call */
     uint32_t hybrid;           /* 1 = MSD x2 + shared-memory segment sort (K3) ran instead of LSD passes */
     uint32_t slow_segments;    /* hybrid: segments whose fix-up fell back to a full local LSD */
+    uint32_t local_levels;     /* hybrid: levels K3 sorted on chip (levels_run - 2) */
+    float ms_joint;            /* hybrid: joint histogram of the two MSD levels + its read-back */
+    float ms_local;            /* hybrid: K3 (shared-memory segment sort), CUDA events */
 } b200_stats;
 
 /*

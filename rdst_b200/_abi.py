@@ -69,6 +69,9 @@ class Stats(C.Structure):
         ("kernel_launches", C.c_uint32),
         ("hybrid", C.c_uint32),
         ("slow_segments", C.c_uint32),
+        ("local_levels", C.c_uint32),
+        ("ms_joint", C.c_float),
+        ("ms_local", C.c_float),
     ]
 
     def as_dict(self):
