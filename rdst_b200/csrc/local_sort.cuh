@@ -55,7 +55,7 @@ __global__ void __launch_bounds__(LS_THREADS, 1) local_sort_kernel(const LocalSo
     uint8_t* s_slot_raw = smem_raw + SM::OUT_BYTES;
     uint32_t* s_part = reinterpret_cast<uint32_t*>(smem_raw + SM::OUT_BYTES + SM::SLOT_BYTES);
     uint8_t* misc = smem_raw + SM::OUT_BYTES + SM::SLOT_BYTES + SM::PART_BYTES;
-    volatile uint32_t* s_seg = reinterpret_cast<volatile uint32_t*>(misc);       // [0] segment id, [1] slow-path flag
+    volatile uint32_t* s_seg = reinterpret_cast<volatile uint32_t*>(misc);       // [0] segment id, [1] slow-path flag, [2] run heads found
     uint32_t* s_wtot = reinterpret_cast<uint32_t*>(misc + 32);                   // 8 digit-warp totals
 
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
@@ -75,6 +75,7 @@ __global__ void __launch_bounds__(LS_THREADS, 1) local_sort_kernel(const LocalSo
         if (tid == 0) {
             s_seg[0] = atomicAdd(p.ticket, 1u);
             s_seg[1] = 0;
+            s_seg[2] = 0;
         }
         __syncthreads();
         const uint32_t seg = s_seg[0];
@@ -197,13 +198,27 @@ __global__ void __launch_bounds__(LS_THREADS, 1) local_sort_kernel(const LocalSo
             }
             if (!fast) break;
             // ---- fix-up: runs of records equal on the fast levels, ordered by the rest of the key ----
+            // Phase 1: find the run heads (record i differs from i-1 and equals i+1 on the fast levels);
+            // neighbours' prefixes come from the adjacent lanes.  The heads are compacted into a list (it
+            // borrows the slot tables, which are idle and zero here) so that phase 2 keeps every thread busy.
             const uint32_t sh = p.fix_shift;
-            for (uint32_t i = tid; i < cnt; i += THREADS) {
+            uint16_t* s_heads = reinterpret_cast<uint16_t*>(s_slot_raw);  // up to cnt / 2 entries of 2 bytes
+            for (uint32_t i0 = 0; i0 < cnt; i0 += THREADS) {
+                const uint32_t i = i0 + tid;
+                const bool in = i < cnt;
+                const uint64_t ki = in ? rec_prefix<WORDS, FLOATK>(p.key, load_rec<WORDS>(s_out, i)) >> sh : 0ull;
+                uint64_t kp = __shfl_up_sync(0xffffffffu, ki, 1), kn = __shfl_down_sync(0xffffffffu, ki, 1);
+                if (lane == 0 && in && i > 0) kp = rec_prefix<WORDS, FLOATK>(p.key, load_rec<WORDS>(s_out, i - 1)) >> sh;
+                if (lane == 31 && i + 1 < cnt) kn = rec_prefix<WORDS, FLOATK>(p.key, load_rec<WORDS>(s_out, i + 1)) >> sh;
+                const bool head = in && i + 1 < cnt && kn == ki && (i == 0 || kp != ki);
+                if (head) s_heads[atomicAdd(const_cast<uint32_t*>(&s_seg[2]), 1u)] = uint16_t(i);
+            }
+            __syncthreads();
+            // Phase 2: one run per thread: find its end, insertion-sort it by the whole key image (stable)
+            const uint32_t nheads = s_seg[2];
+            for (uint32_t hidx = tid; hidx < nheads; hidx += THREADS) {
+                const uint32_t i = s_heads[hidx];
                 const uint64_t ki = rec_prefix<WORDS, FLOATK>(p.key, load_rec<WORDS>(s_out, i)) >> sh;
-                const bool same_prev = i > 0 && (rec_prefix<WORDS, FLOATK>(p.key, load_rec<WORDS>(s_out, i - 1)) >> sh) == ki;
-                if (same_prev || i + 1 >= cnt) continue;
-                if ((rec_prefix<WORDS, FLOATK>(p.key, load_rec<WORDS>(s_out, i + 1)) >> sh) != ki) continue;
-                // i heads a run of at least two records: find its end
                 uint32_t q = i + 2;
                 while (q < cnt && q - i <= uint32_t(LS_MAXRUN) &&
                        (rec_prefix<WORDS, FLOATK>(p.key, load_rec<WORDS>(s_out, q)) >> sh) == ki)
@@ -212,7 +227,7 @@ __global__ void __launch_bounds__(LS_THREADS, 1) local_sort_kernel(const LocalSo
                     s_seg[1] = 1;  // too long for an insertion sort: the whole segment takes the slow path
                     continue;
                 }
-                for (uint32_t a = i + 1; a < q; ++a) {  // stable insertion sort by the whole key image
+                for (uint32_t a = i + 1; a < q; ++a) {
                     const Rec<WORDS> x = load_rec<WORDS>(s_out, a);
                     const uint64_t kx = rec_prefix<WORDS, FLOATK>(p.key, x);
                     uint32_t b = a;
@@ -225,6 +240,10 @@ __global__ void __launch_bounds__(LS_THREADS, 1) local_sort_kernel(const LocalSo
                     if (b != a) store_rec<WORDS>(s_out, b, x);
                 }
             }
+            __syncthreads();
+            // give the slot tables back clean
+            for (uint32_t w = tid; w < (nheads + 1) / 2; w += THREADS) reinterpret_cast<uint32_t*>(s_slot_raw)[w] = 0;
+            if (tid == 0) s_seg[2] = 0;
             __syncthreads();
             if (s_seg[1] == 0) break;
             // slow path: the staging buffer holds a stable rearrangement of the segment; start over with
