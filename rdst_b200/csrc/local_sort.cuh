@@ -55,7 +55,7 @@ __global__ void __launch_bounds__(LS_THREADS, 1) local_sort_kernel(const LocalSo
     uint8_t* s_slot_raw = smem_raw + SM::OUT_BYTES;
     uint32_t* s_part = reinterpret_cast<uint32_t*>(smem_raw + SM::OUT_BYTES + SM::SLOT_BYTES);
     uint8_t* misc = smem_raw + SM::OUT_BYTES + SM::SLOT_BYTES + SM::PART_BYTES;
-    volatile uint32_t* s_seg = reinterpret_cast<volatile uint32_t*>(misc);       // [0] segment id, [1] slow-path flag, [2] run heads found
+    volatile uint32_t* s_seg = reinterpret_cast<volatile uint32_t*>(misc);       // [0] segment id, [1] slow-path flag, [2] run heads found, [3] next segment id
     uint32_t* s_wtot = reinterpret_cast<uint32_t*>(misc + 32);                   // 8 digit-warp totals
 
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
@@ -70,26 +70,22 @@ __global__ void __launch_bounds__(LS_THREADS, 1) local_sort_kernel(const LocalSo
         for (int i = tid; i < int(SM::SLOT_BYTES / 16); i += THREADS) z[i] = make_uint4(0, 0, 0, 0);
     }
 
-    while (true) {
-        __syncthreads();  // previous segment's write-out done; slots clean
-        if (tid == 0) {
-            s_seg[0] = atomicAdd(p.ticket, 1u);
-            s_seg[1] = 0;
-            s_seg[2] = 0;
-        }
-        __syncthreads();
-        const uint32_t seg = s_seg[0];
-        if (seg >= p.nseg) break;
-        const uint64_t base = p.seg_off[seg];
-        const uint32_t cnt = uint32_t(p.seg_off[seg + 1] - base);
-        if (cnt <= 1) continue;
-        uint32_t* g = p.data + base * WORDS;
+    // Segments are claimed one ahead, and the next segment's records are fetched into the registers as
+    // soon as the current one sits sorted in the staging buffer, so the loads fly during the write-out.
+    uint32_t cnt = 0, IT = 0, e0 = 0;
+    uint32_t* g = nullptr;
+    Rec<WORDS> r[ITEMS];
+    auto fetch = [&](uint32_t sg) {  // header + records of segment sg (nothing for cnt <= 1)
+        cnt = 0;
+        if (sg >= p.nseg) return;
+        const uint64_t base = p.seg_off[sg];
+        cnt = uint32_t(p.seg_off[sg + 1] - base);
+        g = p.data + base * WORDS;
         // records per thread actually used: element (group, j, lane16) = group*16*IT + j*16 + lane16,
         // so that every half-warp owns a contiguous run and (group, j, lane) order is memory order
-        const uint32_t IT = (cnt + THREADS - 1) / THREADS;
-        const uint32_t e0 = uint32_t(tid >> 4) * 16u * IT + (lane & 15);
-
-        Rec<WORDS> r[ITEMS];
+        IT = (cnt + THREADS - 1) / THREADS;
+        e0 = uint32_t(tid >> 4) * 16u * IT + (lane & 15);
+        if (cnt <= 1) return;
 #pragma unroll
         for (int j = 0; j < ITEMS; ++j) {
             const uint32_t e = e0 + j * 16;
@@ -100,6 +96,27 @@ __global__ void __launch_bounds__(LS_THREADS, 1) local_sort_kernel(const LocalSo
                 for (int k = 0; k < WORDS; ++k) r[j].w[k] = 0;
             }
         }
+    };
+    if (tid == 0) s_seg[0] = atomicAdd(p.ticket, 1u);
+    __syncthreads();
+    uint32_t seg = s_seg[0];
+    fetch(seg);
+    while (seg < p.nseg) {
+        if (tid == 0) {
+            s_seg[3] = atomicAdd(p.ticket, 1u);  // the segment after this one
+            s_seg[1] = 0;
+            s_seg[2] = 0;
+        }
+        __syncthreads();  // previous segment's write-out done; slots clean; next id visible
+        const uint32_t next_seg = s_seg[3];
+        if (cnt <= 1) {  // nothing to sort
+            seg = next_seg;
+            fetch(seg);
+            __syncthreads();  // everyone has read the next id before thread 0 claims another one
+            continue;
+        }
+        const uint32_t cur_cnt = cnt;
+        uint32_t* const cur_g = g;
 
         bool fast = p.nfast > 0 && p.nfast < p.nlev;
         uint32_t li = fast ? p.nlev - p.nfast : 0;
@@ -258,8 +275,11 @@ __global__ void __launch_bounds__(LS_THREADS, 1) local_sort_kernel(const LocalSo
             fast = false;
             li = 0;
         }
-        // ---- write-out: the sorted segment goes back where it came from, coalesced ----
-        for (uint32_t i = tid; i < cnt; i += THREADS) store_rec<WORDS>(g, uint64_t(i), load_rec<WORDS>(s_out, i));
+        // ---- prefetch the next segment, then write-out: the sorted segment goes back where it came from ----
+        seg = next_seg;
+        fetch(seg);
+        for (uint32_t i = tid; i < cur_cnt; i += THREADS)
+            store_rec<WORDS>(cur_g, uint64_t(i), load_rec<WORDS>(s_out, i));
     }
 }
 
@@ -271,7 +291,7 @@ namespace b200 {
 // joint[d1][d2] = records with digit d1 on level A1 and d2 on level A2, i.e. the sizes of the
 // 65 536 segments the second MSD pass produces.  A CTA works on contiguous chunks; a chunk of an
 // array sorted by d1 spans few d1 values, so counts go to a small shared table first.
-constexpr int H2_THREADS = 256, H2_CHUNK = 16384, H2_SPAN = 4;
+constexpr int H2_THREADS = 256, H2_CHUNK = 65536, H2_SPAN = 4;
 struct Hist2Params {
     const uint32_t* src;
     uint64_t n;
