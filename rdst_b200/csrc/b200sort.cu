@@ -237,12 +237,12 @@ bool word_path_ok(const Lowered& lo, const void* a, const void* b) {
     return pa % 16 == 0 && pb % 16 == 0;
 }
 
-PassLaunch get_pass_launch(uint32_t words, bool floatk, bool remap, int variant, bool hot) {
+PassLaunch get_pass_launch(uint32_t words, bool floatk, bool remap, int variant, bool hot, bool seg = false) {
     switch (words) {
-        case 1: return get_pass_launch_w1(floatk, remap, variant, hot);
-        case 2: return get_pass_launch_w2(floatk, remap, variant, hot);
-        case 3: return get_pass_launch_w3(floatk, remap, variant, hot);
-        case 4: return get_pass_launch_w4(floatk, remap, variant, hot);
+        case 1: return get_pass_launch_w1(floatk, remap, variant, hot, seg);
+        case 2: return get_pass_launch_w2(floatk, remap, variant, hot, seg);
+        case 3: return get_pass_launch_w3(floatk, remap, variant, hot, seg);
+        case 4: return get_pass_launch_w4(floatk, remap, variant, hot, seg);
     }
     return PassLaunch{};
 }
@@ -536,7 +536,7 @@ int sort_hybrid(DeviceCtx& c, cudaStream_t st, void* data, void* tmp, uint64_t n
         // (K3 handles one segment per SM at a time: segments below a few thousand records leave it idle)
         // and from six active levels on: with four, K3's two local levels cost more than the two K2 passes
         // they replace (500 M f32: 11.4 ms hybrid against 8.2 ms LSD)
-        if (active.size() < 6 || n < (256ull << 20)) return B200_OK;
+        if (active.size() < 5 || n < (256ull << 20)) return B200_OK;
         uint64_t m1 = 0, m2 = 0;
         for (int b = 0; b < RADIX; ++b) m1 = std::max(m1, h1[b]), m2 = std::max(m2, h2[b]);
         if (double(m1) * double(m2) / double(n) > 0.97 * LS_CAP) return B200_OK;
@@ -632,9 +632,15 @@ int sort_hybrid(DeviceCtx& c, cudaStream_t st, void* data, void* tmp, uint64_t n
     CUDA_TRY(cudaMemsetAsync(c.d_lookback, 0, size_t(h_tile_start[RADIX]) * RADIX * 8, st));
     PassPlan p2 = pp;
     p2.num_tiles = h_tile_start[RADIX];
+    p2.pl = get_pass_launch(words, lo.is_float, false, pp.variant, false, true);
+    if (!p2.pl.kernel || !p2.pl.seg || p2.pl.tile != int(pp.tile)) {
+        g_last_cuda_error = "hybrid: no segmented instantiation of the pass kernel for this variant";
+        return B200_ERR_CUDA;
+    }
+    CUDA_TRY(cudaFuncSetAttribute(p2.pl.kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, int(p2.pl.smem)));
     {
         int occ = 0;
-        CUDA_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, pp.pl.kernel, pp.pl.threads, pp.pl.smem));
+        CUDA_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, p2.pl.kernel, p2.pl.threads, p2.pl.smem));
         p2.grid = int(std::min<uint64_t>(p2.num_tiles, uint64_t(c.sm_count) * std::max(occ, 1)));
     }
     const int k = 1;

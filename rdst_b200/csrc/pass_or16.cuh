@@ -23,7 +23,7 @@ struct Or16Smem {
     static constexpr size_t TOTAL = OUT_BYTES + SLOT_BYTES + GOFS_BYTES + MISC_BYTES + PART_BYTES;
 };
 
-template <int WORDS, int THREADS, int ITEMS, bool FLOATK, bool REMAP, int MINB, int SUB = 1, bool HOT = false>
+template <int WORDS, int THREADS, int ITEMS, bool FLOATK, bool REMAP, int MINB, int SUB = 1, bool HOT = false, bool SEG = false>
 __global__ void __launch_bounds__(THREADS, MINB) lsd_pass_or16_kernel(const PassParams p) {
     static_assert(SUB == 1, "one slot table per half-warp");
     constexpr int JH = ITEMS / SUB;  // rounds per sub-table
@@ -63,7 +63,7 @@ __global__ void __launch_bounds__(THREADS, MINB) lsd_pass_or16_kernel(const Pass
     }
 
     // segmented mode: (bucket, first tile of the bucket, first record, records) of a tile
-    const bool seg = !REMAP && p.seg_tile_start != nullptr;
+    constexpr bool seg = SEG && !REMAP;  // a separate instantiation: the plain pass stays lean
     auto seg_find = [&](uint32_t t) -> uint32_t {  // bucket b with seg_tile_start[b] <= t < seg_tile_start[b + 1]
         uint32_t lo = 0, hi = RADIX;               // invariant: start[lo] <= t < start[hi]
         while (hi - lo > 1) {

@@ -1,6 +1,6 @@
 #include "pass_inst.cuh"
 namespace b200 {
-PassLaunch get_pass_launch_w4(bool floatk, bool remap, int variant, bool hot) {
-    return pick_launch_w<4>(floatk, remap, variant, hot);
+PassLaunch get_pass_launch_w4(bool floatk, bool remap, int variant, bool hot, bool seg) {
+    return pick_launch_w<4>(floatk, remap, variant, hot, seg);
 }
 }  // namespace b200
