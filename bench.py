@@ -39,6 +39,8 @@ WORKLOADS = {
     "u64_1b_uniform": ("u8", 1_000_000_000, "uniform", "BASELINE configs[1]: u64 keys, 1B uniform random, LSD 8 levels"),
     "u32_100m_uniform": ("u4", 100_000_000, "uniform", "BASELINE configs[0]: u32, 100M uniform random keys"),
     "u64_1b_40bit": ("u8", 1_000_000_000, "low40", "configs[1] variant: keys < 2^40, 3 trivial levels skipped"),
+    "u64_1b_61bit": ("u8", 1_000_000_000, "low61",
+                     "configs[1] variant: keys < 2^61 (what one rank of an 8-GPU sharded sort holds): MSD digits are bit windows"),
     "f32_500m": ("f4", 500_000_000, "uniform", "BASELINE configs[2]: f32 random bit patterns, 500M"),
     "i64_500m": ("i8", 500_000_000, "uniform", "BASELINE configs[2]: i64, 500M incl. negatives"),
     "u64_1b_lowcard": ("u8", 1_000_000_000, "lowcard", "skew stress: every key byte is 0 or 1 (two buckets per level)"),
@@ -60,6 +62,8 @@ def gen_host(dtype, n, gen, seed):
     a = rng.integers(0, 2**64, n, dtype=np.uint64) if dt.itemsize == 8 else rng.integers(0, 2**32, n, dtype=np.uint32)
     if gen == "low40":
         a &= np.uint64((1 << 40) - 1)
+    if gen == "low61":
+        a &= np.uint64((1 << 61) - 1)
     if gen == "lowcard":
         a &= np.uint64(0x0101010101010101)
     if dt.kind == "f":  # NaN/Inf-free random bit patterns (BASELINE configs[2])
@@ -84,6 +88,8 @@ def gen_device(torch, dtype, n, gen, seed):
         t = torch.randint(-2**63, 2**63 - 1, (n,), dtype=torch.int64, device="cuda", generator=g)
         if gen == "low40":
             t &= (1 << 40) - 1
+        if gen == "low61":
+            t &= (1 << 61) - 1
         if gen == "lowcard":
             t &= 0x0101010101010101
         return t

@@ -113,6 +113,8 @@ DigitParams digit_params(const Lowered& lo, uint32_t level) {
     dp.xor_mask = lo.lv[level].xor_mask;
     dp.sign_word = lo.sign_byte / 4;
     dp.sign_shift = (lo.sign_byte % 4) * 8 + 7;
+    dp.word2 = dp.word;
+    dp.mask = 0xffu;
     return dp;
 }
 
@@ -315,7 +317,7 @@ int launch_pass(DeviceCtx& c, cudaStream_t st, const PassPlan& pp, const Lowered
                 const uint8_t* d_remap, const uint64_t* d_dst_tab = nullptr, const SplitParams* sp = nullptr,
                 const uint32_t* hot = nullptr, uint32_t match_bits = 0, uint64_t* lookback = nullptr,
                 const uint32_t* seg_tile_start = nullptr, const uint64_t* seg_rec_start = nullptr,
-                const uint64_t* seg_bases = nullptr) {
+                const uint64_t* seg_bases = nullptr, const DigitParams* window = nullptr) {
     if (pp.word_path) {
         PassParams p;
         memset(&p.sp, 0, sizeof(p.sp));
@@ -323,7 +325,7 @@ int launch_pass(DeviceCtx& c, cudaStream_t st, const PassPlan& pp, const Lowered
         p.src = static_cast<const uint32_t*>(src);
         p.dst = static_cast<uint32_t*>(dst);
         p.n = n;
-        p.dp = digit_params(lo, level);
+        p.dp = window ? *window : digit_params(lo, level);
         p.bucket_base = d_base;
         p.lookback = lookback ? lookback : c.d_lookback;
         p.ticket = d_ticket;
@@ -480,7 +482,23 @@ constexpr size_t HYB_SEG_OFF = size_t(RADIX) * RADIX * 8;
 constexpr size_t HYB_TICKET_OFF = HYB_SEG_OFF + (size_t(RADIX) * RADIX + 1) * 8 + 8;
 constexpr size_t HYB_TILESTART_OFF = HYB_TICKET_OFF + 4096;  // [257] u32
 constexpr size_t HYB_RECSTART_OFF = HYB_TILESTART_OFF + 2048;  // [257] u64
-constexpr size_t HYB_BYTES = HYB_RECSTART_OFF + 4096;
+constexpr size_t HYB_WHIST_OFF = HYB_RECSTART_OFF + 4096;     // [2][256] u64 window histograms
+constexpr size_t HYB_P1_TILESTART_OFF = HYB_WHIST_OFF + 4096;  // pass 1 as one trivial segment: [257] u32
+constexpr size_t HYB_P1_RECSTART_OFF = HYB_P1_TILESTART_OFF + 2048;  // [257] u64
+constexpr size_t HYB_P1_BASES_OFF = HYB_P1_RECSTART_OFF + 4096;      // [256] u64
+constexpr size_t HYB_BYTES = HYB_P1_BASES_OFF + 2048;
+
+// bits [bit_lo, bit_lo + width) of the 64-bit key image (lower_prefix) as a digit
+DigitParams window_params(const Lowered& lo, const SplitParams& key, uint32_t bit_lo, uint32_t width) {
+    DigitParams dp = digit_params(lo, 0);  // sign word / shift
+    const bool in_hi = bit_lo >= 32;
+    dp.word = in_hi ? key.hi_word : key.lo_word;
+    dp.shift = bit_lo % 32;
+    dp.word2 = (!in_hi && dp.shift + width > 32) ? key.hi_word : dp.word;
+    dp.mask = (1u << width) - 1u;
+    dp.xor_mask = uint32_t(key.xorv >> bit_lo) & dp.mask;
+    return dp;
+}
 
 int hybrid_mode() {  // 0 = never, 1 = whenever the key shape allows (tests), 2 = auto (default)
     const char* env = getenv("B200SORT_HYBRID");
@@ -512,12 +530,23 @@ int launch_hist2_w(bool floatk, int grid, cudaStream_t st, const Hist2Params& hp
     return B200_OK;
 }
 
+template <int WORDS>
+int launch_hist_win_w(bool floatk, int grid, cudaStream_t st, const HistWinParams& hp) {
+    if (floatk)
+        hist_win_kernel<WORDS, true><<<grid, H2_THREADS, 0, st>>>(hp);
+    else
+        hist_win_kernel<WORDS, false><<<grid, H2_THREADS, 0, st>>>(hp);
+    CUDA_TRY(cudaGetLastError());
+    return B200_OK;
+}
+
 // Returns B200_OK with *done = true when the array was sorted here (result in `data`);
 // *done = false means "not eligible / segments too large": the caller runs the LSD passes.
 // *src_out tells the caller where the (possibly re-partitioned) records are.
 int sort_hybrid(DeviceCtx& c, cudaStream_t st, void* data, void* tmp, uint64_t n, const Lowered& lo,
                 const std::vector<uint32_t>& active, const unsigned long long* d_base, uint32_t* d_ticket, bool* done,
-                void** src_out, uint32_t* launches, uint32_t* slow_segments) {
+                void** src_out, uint32_t* launches, uint32_t* slow_segments, uint32_t* local_levels,
+                bool copy_back_counts) {
     *done = false;
     *src_out = data;
     const int mode = hybrid_mode();
@@ -527,29 +556,110 @@ int sort_hybrid(DeviceCtx& c, cudaStream_t st, void* data, void* tmp, uint64_t n
     if (!word_path_ok(lo, data, tmp) || n >= (1ull << 32)) return B200_OK;
     SplitParams key;
     if (lower_prefix(lo, &key) != B200_OK) return B200_OK;
-    const uint32_t A1 = active[active.size() - 1], A2 = active[active.size() - 2];
-    const uint64_t* h1 = c.h_hist + size_t(A1) * RADIX;
-    const uint64_t* h2 = c.h_hist + size_t(A2) * RADIX;
-    if (mode == 2) {
-        // worth it from four active levels and ~16 M records on; and only when the segments can be
-        // expected to fit one SM (independence estimate; the exact check follows the joint histogram)
-        // (K3 handles one segment per SM at a time: segments below a few thousand records leave it idle)
-        // and from six active levels on: with four, K3's two local levels cost more than the two K2 passes
-        // they replace (500 M f32: 11.4 ms hybrid against 8.2 ms LSD)
-        if (active.size() < 5 || n < (256ull << 20)) return B200_OK;
-        uint64_t m1 = 0, m2 = 0;
-        for (int b = 0; b < RADIX; ++b) m1 = std::max(m1, h1[b]), m2 = std::max(m2, h2[b]);
-        if (double(m1) * double(m2) / double(n) > 0.97 * LS_CAP) return B200_OK;
+    // worth it from 256 M records and the cost of ~5.5 LSD passes on: the hybrid costs about as much as
+    // 5.1 passes whatever the key width (1 B u64: 25.9 ms against 1.4 + 4.77 ms per level, and an odd
+    // number of LSD passes ends with a 2.5 ms copy back); K3 handles one segment per SM at a time,
+    // so segments below a few thousand records leave it idle
+    const double lsd_cost = double(active.size()) + ((active.size() & 1) && copy_back_counts ? 0.5 : 0.0);
+    if (mode == 2 && (lsd_cost < 5.5 || n < (256ull << 20))) return B200_OK;
+
+    // ---- the digits: bit windows over the varying bits of the key image ----
+    // K1's per-level histograms tell which bits of the 64-bit key image vary at all.  The two MSD
+    // digits are the top 8 varying bits and the next 8 below them wherever they start (keys that
+    // do not fill their type — or one rank's range of a sharded sort — still split 65 536 ways);
+    // the local levels are the byte-aligned windows of what is left below.
+    uint64_t vary = 0;
+    for (uint32_t l = 0; l < lo.levels; ++l) {
+        const uint64_t* h = c.h_hist + size_t(l) * RADIX;
+        for (uint32_t bit = 0; bit < 8; ++bit) {
+            uint64_t ones = 0;
+            for (uint32_t d = 0; d < uint32_t(RADIX); ++d)
+                if (d >> bit & 1u) ones += h[d];
+            if (ones != 0 && ones != n) vary |= 1ull << (8 * l + bit);
+        }
     }
+    if (!vary) return B200_OK;
+    const int T1 = 63 - __builtin_clzll(vary);
+    if (T1 < 8) return B200_OK;
+    const uint32_t w1_lo = uint32_t(T1 - 7);
+    const uint64_t below1 = vary & ((1ull << w1_lo) - 1);
+    if (!below1) return B200_OK;
+    const int T2 = 63 - __builtin_clzll(below1);
+    const uint32_t w2_lo = T2 >= 7 ? uint32_t(T2 - 7) : 0u, w2_width = uint32_t(T2) + 1 - w2_lo;
+    const DigitParams W1 = window_params(lo, key, w1_lo, 8), W2 = window_params(lo, key, w2_lo, w2_width);
+    // local windows, anchored below the second digit so that the top ones are full bytes (K3's fast
+    // path radix-sorts only the top two and wants them to separate the records); least significant first
+    DigitParams local[LS_MAXLEV];
+    uint32_t local_lo[LS_MAXLEV], nlocal = 0;
+    {
+        uint32_t los[8], widths[8], cnt = 0;
+        for (uint32_t hi = w2_lo; hi > 0;) {
+            const uint32_t width = std::min<uint32_t>(8, hi);
+            hi -= width;
+            if ((vary >> hi) & ((1ull << width) - 1)) los[cnt] = hi, widths[cnt++] = width;  // constant bits: an exact no-op
+        }
+        for (uint32_t i = 0; i < cnt; ++i) {
+            local[i] = window_params(lo, key, los[cnt - 1 - i], widths[cnt - 1 - i]);
+            local_lo[i] = los[cnt - 1 - i];
+        }
+        nlocal = cnt;
+    }
+    if (nlocal == 0 || nlocal > uint32_t(LS_MAXLEV)) return B200_OK;
+    {   // the kernels take the upper bits of a window that crosses words from the record's last word
+        auto crossing_ok = [&](const DigitParams& w) { return w.word2 == w.word || w.word2 == words - 1; };
+        bool ok = crossing_ok(W1) && crossing_ok(W2);
+        for (uint32_t i = 0; i < nlocal; ++i) ok = ok && crossing_ok(local[i]);
+        if (!ok) return B200_OK;
+    }
+    // byte-aligned windows are levels: K1 already has their histograms and bucket bases
+    const bool aligned = w1_lo % 8 == 0 && w2_lo % 8 == 0 && w2_width == 8;
+    const uint32_t A1 = w1_lo / 8, A2 = w2_lo / 8;
+
     int rc = ensure_bytes(reinterpret_cast<void**>(&c.d_hyb), &c.hyb_bytes, HYB_BYTES);
     if (rc) return rc;
     unsigned long long* d_joint = reinterpret_cast<unsigned long long*>(c.d_hyb + HYB_JOINT_OFF);
     uint64_t* d_seg = reinterpret_cast<uint64_t*>(c.d_hyb + HYB_SEG_OFF);
     uint32_t* d_tk = reinterpret_cast<uint32_t*>(c.d_hyb + HYB_TICKET_OFF);
+    unsigned long long* d_whist = reinterpret_cast<unsigned long long*>(c.d_hyb + HYB_WHIST_OFF);
 
     static const bool dbg = getenv("B200SORT_DEBUG_TIMING") != nullptr;
     if (dbg) cudaEventRecord(c.ev[3], st);
-    // ---- MSD pass 1: data -> tmp on level A1 (plain K2 pass) ----
+    uint64_t hw[2 * RADIX];  // histograms of the two MSD digits
+    if (aligned) {
+        memcpy(hw, c.h_hist + size_t(A1) * RADIX, RADIX * 8);
+        memcpy(hw + RADIX, c.h_hist + size_t(A2) * RADIX, RADIX * 8);
+    } else {
+        HistWinParams hp;
+        hp.src = static_cast<const uint32_t*>(data);
+        hp.n = n;
+        hp.l1 = W1;
+        hp.l2 = W2;
+        hp.hist = d_whist;
+        CUDA_TRY(cudaMemsetAsync(d_whist, 0, 2 * RADIX * 8, st));
+        const int grid = int(std::min<uint64_t>(uint64_t(c.sm_count) * 8, (n + H2_THREADS * 4 - 1) / (H2_THREADS * 4)));
+        rc = words == 1 ? launch_hist_win_w<1>(lo.is_float, grid, st, hp) : launch_hist_win_w<2>(lo.is_float, grid, st, hp);
+        if (rc) return rc;
+        *launches += 1;
+        CUDA_TRY(cudaMemcpyAsync(c.h_joint, d_whist, 2 * RADIX * 8, cudaMemcpyDeviceToHost, st));
+        CUDA_TRY(cudaStreamSynchronize(st));
+        memcpy(hw, c.h_joint, 2 * RADIX * 8);
+        uint64_t s1 = 0, s2 = 0;
+        for (int b = 0; b < RADIX; ++b) s1 += hw[b], s2 += hw[RADIX + b];
+        if (s1 != n || s2 != n) {
+            g_last_cuda_error = "hybrid: window histograms do not sum to n";
+            return B200_ERR_CUDA;
+        }
+    }
+    const uint64_t* h1 = hw;
+    if (mode == 2) {
+        // only when the segments can be expected to fit one SM (independence estimate; the exact
+        // check follows the joint histogram)
+        uint64_t m1 = 0, m2 = 0;
+        for (int b = 0; b < RADIX; ++b) m1 = std::max(m1, hw[b]), m2 = std::max(m2, hw[RADIX + b]);
+        if (double(m1) * double(m2) / double(n) > 0.97 * LS_CAP) return B200_OK;
+    }
+
+    // ---- MSD pass 1: data -> tmp on the first digit ----
     PassPlan pp{};
     rc = plan_pass(c, lo, n, data, tmp, false, -1, &pp);
     if (rc) return rc;
@@ -563,18 +673,49 @@ int sort_hybrid(DeviceCtx& c, cudaStream_t st, void* data, void* tmp, uint64_t n
     CUDA_TRY(cudaMemsetAsync(d_ticket, 0, 1024, st));
     CUDA_TRY(cudaMemsetAsync(c.d_hyb, 0, HYB_SEG_OFF, st));
     CUDA_TRY(cudaMemsetAsync(d_tk, 0, 4096, st));
-    rc = launch_pass(c, st, pp, lo, data, tmp, n, A1, reinterpret_cast<const uint64_t*>(d_base + size_t(A1) * RADIX),
-                     d_ticket, 1, nullptr);
+    // the segmented instantiation of the pass kernel (it is also the one that reads bit windows)
+    PassPlan ps = pp;
+    ps.pl = get_pass_launch(words, lo.is_float, false, pp.variant, false, true);
+    if (!ps.pl.kernel || !ps.pl.seg || ps.pl.tile != int(pp.tile)) {
+        g_last_cuda_error = "hybrid: no segmented instantiation of the pass kernel for this variant";
+        return B200_ERR_CUDA;
+    }
+    CUDA_TRY(cudaFuncSetAttribute(ps.pl.kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, int(ps.pl.smem)));
+    int occ_seg = 0;
+    CUDA_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ_seg, ps.pl.kernel, ps.pl.threads, ps.pl.smem));
+    occ_seg = std::max(occ_seg, 1);
+    if (aligned) {
+        rc = launch_pass(c, st, pp, lo, data, tmp, n, A1, reinterpret_cast<const uint64_t*>(d_base + size_t(A1) * RADIX),
+                         d_ticket, 1, nullptr);
+    } else {
+        // the whole array as one segment (bucket 0) of the segmented kernel
+        uint32_t h_ts[RADIX + 1];
+        uint64_t h_rs[RADIX + 1], h_b1[RADIX];
+        h_ts[0] = 0, h_rs[0] = 0;
+        for (int b = 1; b <= RADIX; ++b) h_ts[b] = uint32_t(tiles1), h_rs[b] = n;
+        uint64_t run = 0;
+        for (int b = 0; b < RADIX; ++b) h_b1[b] = run, run += hw[b];
+        uint32_t* d_ts = reinterpret_cast<uint32_t*>(c.d_hyb + HYB_P1_TILESTART_OFF);
+        uint64_t* d_rs = reinterpret_cast<uint64_t*>(c.d_hyb + HYB_P1_RECSTART_OFF);
+        uint64_t* d_b1 = reinterpret_cast<uint64_t*>(c.d_hyb + HYB_P1_BASES_OFF);
+        CUDA_TRY(cudaMemcpyAsync(d_ts, h_ts, sizeof(h_ts), cudaMemcpyHostToDevice, st));
+        CUDA_TRY(cudaMemcpyAsync(d_rs, h_rs, sizeof(h_rs), cudaMemcpyHostToDevice, st));
+        CUDA_TRY(cudaMemcpyAsync(d_b1, h_b1, sizeof(h_b1), cudaMemcpyHostToDevice, st));
+        PassPlan p1 = ps;
+        p1.grid = int(std::min<uint64_t>(tiles1, uint64_t(c.sm_count) * occ_seg));
+        rc = launch_pass(c, st, p1, lo, data, tmp, n, 0, d_b1, d_ticket, 1, nullptr, nullptr, nullptr, nullptr, 0, nullptr,
+                         d_ts, d_rs, d_b1, &W1);
+    }
     if (rc) return rc;
     *launches += 1;
     *src_out = tmp;
     cudaEventRecord(c.ev[4], st);
-    // ---- joint histogram of (A1, A2) on the partitioned array = the 65 536 segment sizes ----
+    // ---- joint histogram of the two digits on the partitioned array = the 65 536 segment sizes ----
     Hist2Params hp;
     hp.src = static_cast<const uint32_t*>(tmp);
     hp.n = n;
-    hp.l1 = digit_params(lo, A1);
-    hp.l2 = digit_params(lo, A2);
+    hp.l1 = W1;
+    hp.l2 = W2;
     hp.joint = d_joint;
     const int hgrid = int(std::min<uint64_t>(uint64_t(c.sm_count) * 8, (n + H2_CHUNK - 1) / H2_CHUNK));
     rc = words == 1 ? launch_hist2_w<1>(lo.is_float, hgrid, st, hp) : launch_hist2_w<2>(lo.is_float, hgrid, st, hp);
@@ -607,7 +748,7 @@ int sort_hybrid(DeviceCtx& c, cudaStream_t st, void* data, void* tmp, uint64_t n
     }
     if (max_seg > uint64_t(LS_CAP)) return B200_OK;  // *done stays false, records are in tmp
     CUDA_TRY(cudaMemcpyAsync(d_seg, c.h_joint, size_t(RADIX * RADIX + 1) * 8, cudaMemcpyHostToDevice, st));
-    // ---- MSD pass 2: tmp -> data on level A2, every A1 bucket partitioned on its own (segmented K2 launch) ----
+    // ---- MSD pass 2: tmp -> data on the second digit, every bucket of the first partitioned on its own ----
     uint32_t h_tile_start[RADIX + 1];
     uint64_t h_rec_start[RADIX + 1];
     {
@@ -630,22 +771,12 @@ int sort_hybrid(DeviceCtx& c, cudaStream_t st, void* data, void* tmp, uint64_t n
     CUDA_TRY(cudaMemcpyAsync(d_tile_start, h_tile_start, sizeof(h_tile_start), cudaMemcpyHostToDevice, st));
     CUDA_TRY(cudaMemcpyAsync(d_rec_start, h_rec_start, sizeof(h_rec_start), cudaMemcpyHostToDevice, st));
     CUDA_TRY(cudaMemsetAsync(c.d_lookback, 0, size_t(h_tile_start[RADIX]) * RADIX * 8, st));
-    PassPlan p2 = pp;
+    PassPlan p2 = ps;
     p2.num_tiles = h_tile_start[RADIX];
-    p2.pl = get_pass_launch(words, lo.is_float, false, pp.variant, false, true);
-    if (!p2.pl.kernel || !p2.pl.seg || p2.pl.tile != int(pp.tile)) {
-        g_last_cuda_error = "hybrid: no segmented instantiation of the pass kernel for this variant";
-        return B200_ERR_CUDA;
-    }
-    CUDA_TRY(cudaFuncSetAttribute(p2.pl.kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, int(p2.pl.smem)));
-    {
-        int occ = 0;
-        CUDA_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, p2.pl.kernel, p2.pl.threads, p2.pl.smem));
-        p2.grid = int(std::min<uint64_t>(p2.num_tiles, uint64_t(c.sm_count) * std::max(occ, 1)));
-    }
+    p2.grid = int(std::min<uint64_t>(p2.num_tiles, uint64_t(c.sm_count) * occ_seg));
     const int k = 1;
-    rc = launch_pass(c, st, p2, lo, tmp, data, n, A2, d_seg, d_tk + 1, 1, nullptr, nullptr, nullptr, nullptr, 0, nullptr,
-                     d_tile_start, d_rec_start, d_seg);
+    rc = launch_pass(c, st, p2, lo, tmp, data, n, 0, d_seg, d_tk + 1, 1, nullptr, nullptr, nullptr, nullptr, 0, nullptr,
+                     d_tile_start, d_rec_start, d_seg, &W2);
     if (rc) return rc;
     *launches += 1;
     cudaEventRecord(c.ev[6], st);
@@ -656,9 +787,8 @@ int sort_hybrid(DeviceCtx& c, cudaStream_t st, void* data, void* tmp, uint64_t n
     lp.seg_off = d_seg;
     lp.nseg = RADIX * RADIX;
     lp.ticket = d_tk;
-    lp.nlev = uint32_t(active.size() - 2);
-    if (lp.nlev > uint32_t(LS_MAXLEV)) return B200_ERR_BAD_DESC;
-    for (uint32_t i = 0; i < lp.nlev; ++i) lp.lv[i] = digit_params(lo, active[i]);
+    lp.nlev = nlocal;
+    for (uint32_t i = 0; i < lp.nlev; ++i) lp.lv[i] = local[i];
     // fast levels: as many of the top local levels as make runs of equal prefixes rare
     const double avg = double(n) / double(std::max<uint64_t>(1, nonempty));
     uint32_t nfast = avg <= 64.0 ? 1 : 2;
@@ -667,7 +797,7 @@ int sort_hybrid(DeviceCtx& c, cudaStream_t st, void* data, void* tmp, uint64_t n
     const char* force_slow = getenv("B200SORT_HYBRID_NFAST");
     if (force_slow) nfast = uint32_t(atoi(force_slow)) < lp.nlev ? uint32_t(atoi(force_slow)) : 0;
     lp.nfast = nfast;
-    lp.fix_shift = nfast ? 8 * active[lp.nlev - nfast] : 0;
+    lp.fix_shift = nfast ? local_lo[lp.nlev - nfast] : 0;
     lp.key = key;
     lp.slow_segments = d_tk + 300;
     const int lgrid = int(std::min<uint64_t>(uint64_t(c.sm_count), nonempty ? nonempty : 1));
@@ -686,11 +816,13 @@ int sort_hybrid(DeviceCtx& c, cudaStream_t st, void* data, void* tmp, uint64_t n
         cudaEventElapsedTime(&d, c.ev[5], c.ev[6]);
         cudaEventElapsedTime(&e, c.ev[6], c.ev[7]);
         fprintf(stderr, "[b200sort] hybrid: MSD pass 1 %.3f ms, joint hist + D2H %.3f ms, MSD pass 2 (%d launches) %.3f ms, K3 %.3f ms"
-                        " (max segment %llu, nfast %u of %u local levels)\n",
-                a, b, k, d, e, (unsigned long long)max_seg, nfast, lp.nlev);
+                        " (max segment %llu, nfast %u of %u local levels; digits: bits %u..%u, %u..%u%s)\n",
+                a, b, k, d, e, (unsigned long long)max_seg, nfast, lp.nlev, w1_lo, w1_lo + 7, w2_lo, w2_lo + w2_width - 1,
+                aligned ? "" : ", window histogram pass");
     }
     *done = true;
     *src_out = data;
+    if (local_levels) *local_levels = nlocal;
     return B200_OK;
 }
 
@@ -742,11 +874,11 @@ int sort_device_impl(DeviceCtx& c, cudaStream_t st, void* data, void* tmp, uint6
     // the Tuner's algorithm choice on the GPU: MSD x2 + on-chip segment sort for large inputs whose
     // segments fit an SM, LSD passes otherwise (an explicit variant request always means LSD passes)
     bool hybrid_done = false;
-    uint32_t hybrid_launches = 0, slow_segments = 0;
+    uint32_t hybrid_launches = 0, slow_segments = 0, local_levels = 0;
     if (variant < 0) {
         void* where = data;
         rc = sort_hybrid(c, st, data, tmp, n, lo, active, d_base, d_ticket, &hybrid_done, &where, &hybrid_launches,
-                         &slow_segments);
+                         &slow_segments, &local_levels, !result_anywhere);
         if (rc) return rc;
         if (!hybrid_done && where == tmp) std::swap(src, dst);  // MSD pass 1 ran: the records now live in tmp
     }
@@ -786,7 +918,7 @@ int sort_device_impl(DeviceCtx& c, cudaStream_t st, void* data, void* tmp, uint6
         stats->levels_skipped = lo.levels - pass;
         stats->hybrid = hybrid_done ? 1u : 0u;
         stats->slow_segments = slow_segments;
-        stats->local_levels = hybrid_done ? n_active - 2 : 0;
+        stats->local_levels = hybrid_done ? local_levels : 0;
         stats->ms_joint = stats->ms_local = 0.0f;
         if (hybrid_done) {
             CUDA_TRY(cudaEventElapsedTime(&stats->ms_joint, c.ev[4], c.ev[5]));

@@ -28,6 +28,10 @@ struct DigitParams {
     uint32_t xor_mask;   // per level
     uint32_t sign_word;  // FLOAT keys: word holding the sign bit
     uint32_t sign_shift; // FLOAT keys: bit position of the sign inside that word
+    // bit windows (hybrid path only; the byte-aligned kernels ignore these): the digit is
+    // bits [shift, shift + width) of the 64-bit pair (record word `word2` : record word `word`)
+    uint32_t word2;      // word holding the bits above bit 31 of the pair (== word when the window does not cross)
+    uint32_t mask;       // (1 << width) - 1; xor_mask lies inside it
 };
 
 template <bool FLOATK>
@@ -37,6 +41,18 @@ __device__ __forceinline__ uint32_t digit_from_words(const DigitParams& dp, uint
     if (FLOATK) {
         uint32_t neg = (sign_word_val >> dp.sign_shift) & 1u;
         return b ^ (neg ? 0xffu : dp.xor_mask);
+    }
+    return b ^ dp.xor_mask;
+}
+
+// Window digit: up to 8 bits at any bit position of the key image, possibly across two record words.
+template <bool FLOATK>
+__device__ __forceinline__ uint32_t window_from_words(const DigitParams& dp, uint32_t key_word, uint32_t key_word2,
+                                                      uint32_t sign_word_val) {
+    const uint32_t b = __funnelshift_r(key_word, key_word2, dp.shift) & dp.mask;
+    if (FLOATK) {
+        const uint32_t neg = (sign_word_val >> dp.sign_shift) & 1u;
+        return b ^ (neg ? dp.mask : dp.xor_mask);
     }
     return b ^ dp.xor_mask;
 }

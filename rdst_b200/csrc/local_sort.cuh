@@ -132,7 +132,7 @@ __global__ void __launch_bounds__(LS_THREADS, 1) local_sort_kernel(const LocalSo
                     if (uint32_t(j) < IT) {
                         const uint32_t e = e0 + j * 16;
                         uint32_t d = 255u;  // padding sorts behind every record
-                        if (e < cnt) d = rec_digit<WORDS, FLOATK>(dp, r[j]);
+                        if (e < cnt) d = rec_digit_w<WORDS, FLOATK, true>(dp, r[j]);
                         const uint32_t sa = my_slots + d * 4;
                         slot_or(sa, lane_bit);
                         __syncwarp();
@@ -191,7 +191,7 @@ __global__ void __launch_bounds__(LS_THREADS, 1) local_sort_kernel(const LocalSo
                     if (uint32_t(j) < IT) {
                         const uint32_t e = e0 + j * 16;
                         uint32_t d = 255u;
-                        if (e < cnt) d = rec_digit<WORDS, FLOATK>(dp, r[j]);
+                        if (e < cnt) d = rec_digit_w<WORDS, FLOATK, true>(dp, r[j]);
                         const uint32_t pos = (lds_u32(my_slots + d * 4) >> 16) + ((rk[j / 2] >> ((j & 1) * 16)) & 0xffffu);
                         store_rec<WORDS>(s_out, pos, r[j]);
                     }
@@ -299,6 +299,51 @@ struct Hist2Params {
     unsigned long long* joint;  // [256][256], zeroed before the launch
 };
 
+// Histograms of two bit windows over the whole array in one read (the two MSD digits when the key's
+// varying bits do not end on a byte boundary, so K1's per-level histograms do not describe them).
+// Per-warp private tables; a skewed window serialises on its hot bins (correct, slower).
+struct HistWinParams {
+    const uint32_t* src;
+    uint64_t n;
+    DigitParams l1, l2;
+    unsigned long long* hist;  // [2][256], zeroed before the launch
+};
+
+template <int WORDS, bool FLOATK>
+__global__ void __launch_bounds__(H2_THREADS) hist_win_kernel(const HistWinParams p) {
+    constexpr int WARPS = H2_THREADS / 32;
+    __shared__ uint32_t sh[2 * WARPS * RADIX];
+    for (int i = threadIdx.x; i < 2 * WARPS * RADIX; i += H2_THREADS) sh[i] = 0;
+    __syncthreads();
+    uint32_t* mine1 = sh + (threadIdx.x / 32) * RADIX;
+    uint32_t* mine2 = mine1 + WARPS * RADIX;
+    const uint64_t stride = uint64_t(gridDim.x) * H2_THREADS;
+    uint64_t i = uint64_t(blockIdx.x) * H2_THREADS + threadIdx.x;
+    for (; i + 3 * stride < p.n; i += 4 * stride) {
+        Rec<WORDS> r[4];
+#pragma unroll
+        for (int k = 0; k < 4; ++k) r[k] = load_rec<WORDS>(p.src + (i + k * stride) * WORDS, 0);
+#pragma unroll
+        for (int k = 0; k < 4; ++k) {
+            atomicAdd(&mine1[rec_digit_w<WORDS, FLOATK, true>(p.l1, r[k])], 1u);
+            atomicAdd(&mine2[rec_digit_w<WORDS, FLOATK, true>(p.l2, r[k])], 1u);
+        }
+    }
+    for (; i < p.n; i += stride) {
+        const Rec<WORDS> r = load_rec<WORDS>(p.src + i * WORDS, 0);
+        atomicAdd(&mine1[rec_digit_w<WORDS, FLOATK, true>(p.l1, r)], 1u);
+        atomicAdd(&mine2[rec_digit_w<WORDS, FLOATK, true>(p.l2, r)], 1u);
+    }
+    __syncthreads();
+    for (int d = threadIdx.x; d < 2 * RADIX; d += H2_THREADS) {
+        const uint32_t* t = sh + (d / RADIX) * WARPS * RADIX + (d % RADIX);
+        unsigned long long c = 0;
+#pragma unroll
+        for (int w = 0; w < WARPS; ++w) c += t[w * RADIX];
+        if (c) atomicAdd(p.hist + d, c);
+    }
+}
+
 template <int WORDS, bool FLOATK>
 __global__ void __launch_bounds__(H2_THREADS) hist2_kernel(const Hist2Params p) {
     __shared__ uint32_t sh[H2_SPAN * RADIX];
@@ -307,11 +352,11 @@ __global__ void __launch_bounds__(H2_THREADS) hist2_kernel(const Hist2Params p) 
         for (int i = threadIdx.x; i < H2_SPAN * RADIX; i += H2_THREADS) sh[i] = 0;
         const uint64_t lo = ch * H2_CHUNK;
         const uint64_t hi = lo + H2_CHUNK < p.n ? lo + H2_CHUNK : p.n;
-        const uint32_t dfirst = rec_digit<WORDS, FLOATK>(p.l1, load_rec<WORDS>(p.src + lo * WORDS, 0));
+        const uint32_t dfirst = rec_digit_w<WORDS, FLOATK, true>(p.l1, load_rec<WORDS>(p.src + lo * WORDS, 0));
         __syncthreads();
         for (uint64_t i = lo + threadIdx.x; i < hi; i += H2_THREADS) {
             const Rec<WORDS> r = load_rec<WORDS>(p.src + i * WORDS, 0);
-            const uint32_t d1 = rec_digit<WORDS, FLOATK>(p.l1, r), d2 = rec_digit<WORDS, FLOATK>(p.l2, r);
+            const uint32_t d1 = rec_digit_w<WORDS, FLOATK, true>(p.l1, r), d2 = rec_digit_w<WORDS, FLOATK, true>(p.l2, r);
             const uint32_t rel = d1 - dfirst;
             if (rel < uint32_t(H2_SPAN))
                 atomicAdd(&sh[rel * RADIX + d2], 1u);

@@ -113,6 +113,21 @@ __device__ __forceinline__ uint32_t rec_digit(const DigitParams& dp, const Rec<W
     return digit_from_words<FLOATK>(dp, kw, sw);
 }
 
+// WIN = true: bit-window digit (hybrid path), false: byte-aligned level
+template <int WORDS, bool FLOATK, bool WIN>
+__device__ __forceinline__ uint32_t rec_digit_w(const DigitParams& dp, const Rec<WORDS>& r) {
+    if constexpr (WIN) {
+        // a window that crosses a word boundary has its upper bits in the record's last word (the host
+        // checks dp.word2 == WORDS - 1); one that does not never looks at the second operand
+        const uint32_t kw = pick_word<WORDS>(r, dp.word);
+        const uint32_t kw2 = r.w[WORDS - 1];
+        const uint32_t sw = FLOATK ? pick_word<WORDS>(r, dp.sign_word) : 0u;
+        return window_from_words<FLOATK>(dp, kw, kw2, sw);
+    } else {
+        return rec_digit<WORDS, FLOATK>(dp, r);
+    }
+}
+
 template <int WORDS, bool FLOATK>
 __device__ __forceinline__ uint64_t rec_prefix(const SplitParams& sp, const Rec<WORDS>& r) {
     const uint32_t lo = pick_word<WORDS>(r, sp.lo_word);

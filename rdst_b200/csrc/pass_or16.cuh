@@ -150,7 +150,7 @@ __global__ void __launch_bounds__(THREADS, MINB) lsd_pass_or16_kernel(const Pass
             const uint32_t e = e0 + j * 16;
             uint32_t d = 255u;  // padding sorts to the very end of the tile
             if (full || e < valid) {
-                d = pass_bucket<WORDS, FLOATK, REMAP>(p, dp, r[j]);
+                d = seg ? rec_digit_w<WORDS, FLOATK, seg>(dp, r[j]) : pass_bucket<WORDS, FLOATK, REMAP>(p, dp, r[j]);
             }
             if (REMAP) dcache[j / 4] |= d << ((j % 4) * 8);  // the part id is costly to recompute
             const uint32_t sa = my_slots + d * 4;
@@ -269,7 +269,7 @@ __global__ void __launch_bounds__(THREADS, MINB) lsd_pass_or16_kernel(const Pass
             if (REMAP) {
                 d = (dcache[j / 4] >> ((j % 4) * 8)) & 0xffu;
             } else if (full || e < valid) {
-                d = rec_digit<WORDS, FLOATK>(dp, r[j]);
+                d = rec_digit_w<WORDS, FLOATK, seg>(dp, r[j]);
             }
             const uint32_t pos = (lds_u32(my_slots + (j / JH) * RADIX * 4 + d * 4) >> 16) + ((rk[j / RPR] >> ((j % RPR) * RBITS)) & RMASK);
             store_rec<WORDS>(s_out, pos, r[j]);
@@ -336,7 +336,7 @@ __global__ void __launch_bounds__(THREADS, MINB) lsd_pass_or16_kernel(const Pass
                 for (int k = 0; k < ITEMS; ++k) {
                     const uint32_t i = tid + k * THREADS;
                     const Rec<WORDS> x = load_rec<WORDS>(s_out, i);
-                    const uint32_t d = rec_digit<WORDS, FLOATK>(dp, x);
+                    const uint32_t d = rec_digit_w<WORDS, FLOATK, seg>(dp, x);
                     store_rec<WORDS>(p.dst, uint64_t(s_gofs32[d] + i), x);
                 }
             } else if (full) {
@@ -344,13 +344,13 @@ __global__ void __launch_bounds__(THREADS, MINB) lsd_pass_or16_kernel(const Pass
                 for (int k = 0; k < ITEMS; ++k) {
                     const uint32_t i = tid + k * THREADS;
                     const Rec<WORDS> x = load_rec<WORDS>(s_out, i);
-                    const uint32_t d = pass_bucket<WORDS, FLOATK, REMAP>(p, dp, x);
+                    const uint32_t d = seg ? rec_digit_w<WORDS, FLOATK, seg>(dp, x) : pass_bucket<WORDS, FLOATK, REMAP>(p, dp, x);
                     store_rec<WORDS>(REMAP ? reinterpret_cast<uint32_t*>(s_gptr[d]) : p.dst, s_gofs[d] + i, x);
                 }
             } else {
                 for (uint32_t i = tid; i < valid; i += THREADS) {
                     const Rec<WORDS> x = load_rec<WORDS>(s_out, i);
-                    const uint32_t d = pass_bucket<WORDS, FLOATK, REMAP>(p, dp, x);
+                    const uint32_t d = seg ? rec_digit_w<WORDS, FLOATK, seg>(dp, x) : pass_bucket<WORDS, FLOATK, REMAP>(p, dp, x);
                     store_rec<WORDS>(REMAP ? reinterpret_cast<uint32_t*>(s_gptr[d]) : p.dst, s_gofs[d] + i, x);
                 }
             }

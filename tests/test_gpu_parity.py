@@ -536,13 +536,24 @@ def _hybrid_cases():
     yield "i32_uniform", "i4", rng.integers(-2**31, 2**31 - 1, n, dtype="i4"), True
     # few distinct values: long runs of equal fast-level prefixes -> slow path inside K3
     yield "u64_dups", "u8", rng.integers(0, 3000, n, dtype="u8") * np.uint64(0x0001000100010001), True
-    # segments of ~6 k records (16 x 16 top-byte values): the big-segment regime of the 1 B-key run
-    top = (rng.integers(0, 16, n, dtype="u8") << np.uint64(56)) | (rng.integers(0, 16, n, dtype="u8") << np.uint64(48))
-    yield "u64_big_segments", "u8", top | rng.integers(0, 2**48, n, dtype="u8"), True
+    # segments of ~6 k records (16 x 16 values in the two MSD digits): the big-segment regime of the 1 B-key run
+    top = (rng.integers(0, 16, n, dtype="u8") << np.uint64(60)) | (rng.integers(0, 16, n, dtype="u8") << np.uint64(52))
+    yield "u64_big_segments", "u8", top | rng.integers(0, 2**44, n, dtype="u8"), True
     yield "u64_big_segments_dups", "u8", top | (rng.integers(0, 50, n, dtype="u8") << np.uint64(20)), True
-    # 4 x 4 top-byte values: segments of ~94 k records do not fit an SM -> falls back to LSD from the scratch buffer
-    top4 = (rng.integers(0, 4, n, dtype="u8") << np.uint64(56)) | (rng.integers(0, 4, n, dtype="u8") << np.uint64(48))
-    yield "u64_segments_too_large", "u8", top4 | rng.integers(0, 2**48, n, dtype="u8"), False
+    # 4 x 4 values in the two MSD digits: segments of ~94 k records do not fit an SM -> falls back to LSD from the scratch buffer
+    top4 = (rng.integers(0, 4, n, dtype="u8") << np.uint64(62)) | (rng.integers(0, 4, n, dtype="u8") << np.uint64(54))
+    yield "u64_segments_too_large", "u8", top4 | rng.integers(0, 2**46, n, dtype="u8"), False
+    # keys that do not fill their type: the MSD digits are bit windows below the top varying bit
+    yield "u64_61_bits", "u8", rng.integers(0, 2**61, n, dtype="u8"), True
+    yield "u64_45_bits", "u8", rng.integers(0, 2**45, n, dtype="u8"), True
+    yield "u64_36_bits_window_across_words", "u8", rng.integers(0, 2**36, n, dtype="u8"), True
+    yield "u64_rank_range", "u8", rng.integers(3 << 58, 5 << 58, n, dtype="u8"), True
+    yield "i64_narrow", "i8", rng.integers(-2**40, 2**40, n, dtype="i8"), None
+    yield "i64_positive_50_bits", "i8", rng.integers(0, 2**50, n, dtype="i8"), True
+    yield "u32_27_bits", "u4", rng.integers(0, 2**27, n, dtype="u4"), True
+    yield "f32_one_to_two", "f4", (rng.random(n, dtype="f4") + np.float32(1.0)), True
+    yield "f64_unit_interval", "f8", rng.random(n), None
+    yield "f64_negative_bits", "f8", -np.abs(rand_bits(rng, "f8", n)), None
     # trivial levels in the middle and on top (level skip inside the hybrid plan)
     yield "u64_masked", "u8", rng.integers(0, 2**64, n, dtype="u8") & np.uint64(0x00FFFF00FFFF00FF), True
     z = np.minimum(rng.zipf(1.1, n), 2**32).astype("u8")
