@@ -450,7 +450,8 @@ static void pick_hot_buckets(const uint64_t* hist, uint64_t n, uint32_t hot[2]) 
     static const bool off = getenv("B200SORT_NO_HOT") != nullptr;
     hot[0] = hot[1] = 0xffffffffu;
     if (off) return;
-    uint64_t best0 = n / 8, best1 = n / 8;
+    static const uint64_t div = getenv("B200SORT_HOT_DIV") ? std::max(2, atoi(getenv("B200SORT_HOT_DIV"))) : 8;
+    uint64_t best0 = n / div, best1 = n / div;
     for (uint32_t b = 0; b < uint32_t(RADIX); ++b) {
         const uint64_t cnt = hist[b];
         if (cnt > best0) {

@@ -27,7 +27,9 @@ __global__ void __launch_bounds__(1024) probe(uint32_t* out, long long* cycles, 
     for (int i = 0; i < ITERS; ++i) {
         x = lcg(x);
         uint32_t d = skew == 0 ? (x >> 24) : skew == 1 ? 7u : skew == 2 ? ((x >> 24) & (x >> 16) & (x >> 8) & 0xffu)
-                                                                  : ((x & 0x100u) ? 7u : (x >> 24));
+                     : skew == 3 ? ((x & 0x100u) ? 7u : (x >> 24))
+                     // skew 4: Zipf-like, one digit holds 1/8 of the records, another 1/16, the rest uniform
+                     : ((x & 0x700u) == 0 ? 7u : (x & 0xf00u) == 0x100u ? 9u : (x >> 24));
         if (MODE == 0) acc += __match_any_sync(0xffffffffu, d);
         if (MODE == 1) acc += match_digit<false>(d);
         if (MODE == 2) atomicAdd(&my[d], 1u);                 // warp-private, no return
@@ -39,6 +41,16 @@ __global__ void __launch_bounds__(1024) probe(uint32_t* out, long long* cycles, 
             uint32_t* slot = sh + ((threadIdx.x >> 4) & 31) * 256 + d;
             const uint32_t bit = 1u << (threadIdx.x & 15);
             atomicOr(slot, bit); __syncwarp();
+            const uint32_t v = *(volatile uint32_t*)slot; __syncwarp();
+            const uint32_t m = v & 0xffffu, c = v >> 16, lt = m & (bit - 1u);
+            if (lt == 0) *(volatile uint32_t*)slot = (c + __popc(m)) << 16;
+            __syncwarp(); acc += c + __popc(lt);
+        }
+        if (MODE == 11) atomicAdd(&my[d], 1u << (threadIdx.x & 31));  // RED.ADD of distinct bits == OR
+        if (MODE == 12) {  // the half-warp rank step with ADD instead of OR
+            uint32_t* slot = sh + ((threadIdx.x >> 4) & 31) * 256 + d;
+            const uint32_t bit = 1u << (threadIdx.x & 15);
+            atomicAdd(slot, bit); __syncwarp();
             const uint32_t v = *(volatile uint32_t*)slot; __syncwarp();
             const uint32_t m = v & 0xffffu, c = v >> 16, lt = m & (bit - 1u);
             if (lt == 0) *(volatile uint32_t*)slot = (c + __popc(m)) << 16;
@@ -90,11 +102,14 @@ int main() {
     printf("device %s, %d SMs, clock %d kHz\n", prop.name, sms, prop.clockRate);
     uint32_t* d_out; long long* d_cyc;
     CK(cudaMalloc(&d_out, size_t(sms) * 2 * 1024 * 4)); CK(cudaMalloc(&d_cyc, sms * 2 * 8));
-    for (int skew = 0; skew < 4; ++skew) {
+    for (int skew = 0; skew < 5; ++skew) {
         run_probe<2>("ATOMS.ADD warp-private no-ret", sms, d_out, d_cyc, skew);
         run_probe<9>("RED.OR warp-private", sms, d_out, d_cyc, skew);
+        run_probe<11>("RED.ADD lane bit warp-private", sms, d_out, d_cyc, skew);
         run_probe<10>("half-warp OR rank step", sms, d_out, d_cyc, skew);
+        run_probe<12>("half-warp ADD rank step", sms, d_out, d_cyc, skew);
     }
+    if (getenv("MICROBENCH_ATOMICS_ONLY")) return 0;
     for (int skew = 0; skew < 2; ++skew) {
         run_probe<6>("loop overhead", sms, d_out, d_cyc, skew);
         run_probe<0>("MATCH.ANY", sms, d_out, d_cyc, skew);
