@@ -801,6 +801,8 @@ int sort_hybrid(DeviceCtx& c, cudaStream_t st, void* data, void* tmp, uint64_t n
     lp.fix_shift = nfast ? local_lo[lp.nlev - nfast] : 0;
     lp.key = key;
     lp.slow_segments = d_tk + 300;
+    static const bool k3prof = getenv("B200SORT_K3_PROFILE") != nullptr;
+    lp.prof = k3prof ? reinterpret_cast<unsigned long long*>(d_tk + 320) : nullptr;
     const int lgrid = int(std::min<uint64_t>(uint64_t(c.sm_count), nonempty ? nonempty : 1));
     rc = words == 1 ? launch_local_sort_w<1>(lo.is_float, lgrid, st, lp) : launch_local_sort_w<2>(lo.is_float, lgrid, st, lp);
     if (rc) return rc;
@@ -820,6 +822,17 @@ int sort_hybrid(DeviceCtx& c, cudaStream_t st, void* data, void* tmp, uint64_t n
                         " (max segment %llu, nfast %u of %u local levels; digits: bits %u..%u, %u..%u%s)\n",
                 a, b, k, d, e, (unsigned long long)max_seg, nfast, lp.nlev, w1_lo, w1_lo + 7, w2_lo, w2_lo + w2_width - 1,
                 aligned ? "" : ", window histogram pass");
+    }
+    if (k3prof) {
+        unsigned long long h[8];
+        cudaMemcpyAsync(h, d_tk + 320, sizeof(h), cudaMemcpyDeviceToHost, st);
+        cudaStreamSynchronize(st);
+        double tot = 0;
+        for (int i = 0; i < 8; ++i) tot += double(h[i]);
+        fprintf(stderr, "[b200sort] K3 cycles of thread 0, share per phase: wait/claim %.1f%% rank %.1f%% digit scan %.1f%% scatter %.1f%% "
+                        "read-back %.1f%% fix-up heads %.1f%% fix-up runs %.1f%% prefetch+write-out %.1f%% (%.0f cycles per segment)\n",
+                100 * h[0] / tot, 100 * h[1] / tot, 100 * h[2] / tot, 100 * h[3] / tot, 100 * h[4] / tot, 100 * h[5] / tot,
+                100 * h[6] / tot, 100 * h[7] / tot, tot / double(std::max<uint64_t>(1, nonempty)));
     }
     *done = true;
     *src_out = data;

@@ -34,6 +34,7 @@ struct LocalSortParams {
     DigitParams lv[LS_MAXLEV];
     SplitParams key;           // 64-bit order-preserving image of the whole key (LEVELS <= 8)
     uint32_t* slow_segments;   // telemetry: segments that fell back to the full LSD
+    unsigned long long* prof;  // optional [8] cycle counters per phase (thread 0 of every CTA), nullptr = off
 };
 
 template <int WORDS>
@@ -97,6 +98,14 @@ __global__ void __launch_bounds__(LS_THREADS, 1) local_sort_kernel(const LocalSo
             }
         }
     };
+    long long t_last = p.prof ? clock64() : 0;
+    auto tick = [&](int k) {
+        if (p.prof && tid == 0) {
+            const long long t = clock64();
+            atomicAdd(p.prof + k, (unsigned long long)(t - t_last));
+            t_last = t;
+        }
+    };
     if (tid == 0) s_seg[0] = atomicAdd(p.ticket, 1u);
     __syncthreads();
     uint32_t seg = s_seg[0];
@@ -108,6 +117,7 @@ __global__ void __launch_bounds__(LS_THREADS, 1) local_sort_kernel(const LocalSo
             s_seg[2] = 0;
         }
         __syncthreads();  // previous segment's write-out done; slots clean; next id visible
+        tick(0);
         const uint32_t next_seg = s_seg[3];
         if (cnt <= 1) {  // nothing to sort
             seg = next_seg;
@@ -146,6 +156,7 @@ __global__ void __launch_bounds__(LS_THREADS, 1) local_sort_kernel(const LocalSo
                     }
                 }
                 __syncthreads();
+                tick(1);
                 // ---- two threads per digit: counts of my 16 groups -> positions in the sorted segment ----
                 uint32_t gc[GPH], part = 0, sum = 0, before = 0, incl = 0;
                 {
@@ -185,6 +196,7 @@ __global__ void __launch_bounds__(LS_THREADS, 1) local_sort_kernel(const LocalSo
                     }
                 }
                 __syncthreads();
+                tick(2);
                 // ---- scatter into the staging buffer in sorted order ----
 #pragma unroll
                 for (int j = 0; j < ITEMS; ++j) {
@@ -203,6 +215,7 @@ __global__ void __launch_bounds__(LS_THREADS, 1) local_sort_kernel(const LocalSo
                     for (int i = lane; i < 2 * RADIX * 4 / 16; i += 32) z[i] = make_uint4(0, 0, 0, 0);
                 }
                 __syncthreads();
+                tick(3);
                 if (li + 1 < p.nlev) {
                     // read back in element order for the next level
 #pragma unroll
@@ -211,35 +224,64 @@ __global__ void __launch_bounds__(LS_THREADS, 1) local_sort_kernel(const LocalSo
                         if (uint32_t(j) < IT && e < cnt) r[j] = load_rec<WORDS>(s_out, e);
                     }
                     __syncthreads();  // everyone has its records before the next scatter overwrites them
+                    tick(4);
                 }
             }
             if (!fast) break;
             // ---- fix-up: runs of records equal on the fast levels, ordered by the rest of the key ----
-            // Phase 1: find the run heads (record i differs from i-1 and equals i+1 on the fast levels);
-            // neighbours' prefixes come from the adjacent lanes.  The heads are compacted into a list (it
-            // borrows the slot tables, which are idle and zero here) so that phase 2 keeps every thread busy.
-            const uint32_t sh = p.fix_shift;
-            uint16_t* s_heads = reinterpret_cast<uint16_t*>(s_slot_raw);  // up to cnt / 2 entries of 2 bytes
-            for (uint32_t i0 = 0; i0 < cnt; i0 += THREADS) {
-                const uint32_t i = i0 + tid;
-                const bool in = i < cnt;
-                const uint64_t ki = in ? rec_prefix<WORDS, FLOATK>(p.key, load_rec<WORDS>(s_out, i)) >> sh : 0ull;
-                uint64_t kp = __shfl_up_sync(0xffffffffu, ki, 1), kn = __shfl_down_sync(0xffffffffu, ki, 1);
-                if (lane == 0 && in && i > 0) kp = rec_prefix<WORDS, FLOATK>(p.key, load_rec<WORDS>(s_out, i - 1)) >> sh;
-                if (lane == 31 && i + 1 < cnt) kn = rec_prefix<WORDS, FLOATK>(p.key, load_rec<WORDS>(s_out, i + 1)) >> sh;
-                const bool head = in && i + 1 < cnt && kn == ki && (i == 0 || kp != ki);
-                if (head) s_heads[atomicAdd(const_cast<uint32_t*>(&s_seg[2]), 1u)] = uint16_t(i);
+            // Phase 1: find the run heads (record i differs from i-1 and equals i+1 on the fast levels).
+            // Every warp scans one contiguous chunk, so eq(i) = "record i equals record i + 1 on the fast
+            // levels" comes from two conflict-free loads and eq(i - 1) from the warp's ballot (bit 31 of
+            // the previous round carries over).  The heads go into the warp's own list (it borrows the slot
+            // tables, idle and zero here; no shared counter: same-address shared atomics with a return
+            // value serialise at ~36 cycles each and made this phase a third of the kernel).
+            // Phase 2: the same warp, one run per thread: find its end, insertion-sort it by the whole key
+            // image (stable).  A run may reach into the next warp's chunk while that warp is still
+            // scanning: its records all agree on the fast levels, so the scan reads the same eq() either way.
+            // "equal on the fast levels" on the raw record words: the key image is the raw key xor a
+            // constant (or, for floats, a constant chosen by the sign bit, which is above the fast levels),
+            // so two records agree on image bits >= fix_shift iff their raw words agree under these masks
+            uint32_t eqm_w[WORDS];
+            {
+                const uint64_t m = (p.key.mask >> p.fix_shift) << p.fix_shift;
+#pragma unroll
+                for (int k = 0; k < WORDS; ++k)
+                    eqm_w[k] = uint32_t(k) == p.key.lo_word ? uint32_t(m) : (uint32_t(k) == p.key.hi_word ? uint32_t(m >> 32) : 0u);
             }
-            __syncthreads();
-            // Phase 2: one run per thread: find its end, insertion-sort it by the whole key image (stable)
-            const uint32_t nheads = s_seg[2];
-            for (uint32_t hidx = tid; hidx < nheads; hidx += THREADS) {
-                const uint32_t i = s_heads[hidx];
-                const uint64_t ki = rec_prefix<WORDS, FLOATK>(p.key, load_rec<WORDS>(s_out, i)) >> sh;
+            auto same_fast = [&](const Rec<WORDS>& a, const Rec<WORDS>& b) {
+                uint32_t diff = 0;
+#pragma unroll
+                for (int k = 0; k < WORDS; ++k) diff |= (a.w[k] ^ b.w[k]) & eqm_w[k];
+                return diff == 0;
+            };
+            constexpr uint32_t HEADS_PER_WARP = LS_CAP / (THREADS / 32) / 2;  // a chunk of c records has <= c / 2 heads
+            uint16_t* my_heads = reinterpret_cast<uint16_t*>(s_slot_raw) + uint32_t(warp) * HEADS_PER_WARP;
+            uint32_t nheads = 0;  // warp-uniform
+            {
+                auto same_at = [&](uint32_t i) { return same_fast(load_rec<WORDS>(s_out, i), load_rec<WORDS>(s_out, i + 1)); };
+                const uint32_t per = ((cnt + THREADS - 1) / THREADS) * 32;
+                const uint32_t wlo = uint32_t(warp) * per, whi = wlo + per < cnt ? wlo + per : cnt;
+                uint32_t carry = 0;
+                if (wlo > 0 && wlo < cnt) carry = same_at(wlo - 1) ? 1u : 0u;
+#pragma unroll 2
+                for (uint32_t i0 = wlo; i0 < whi; i0 += 32) {
+                    const uint32_t i = i0 + lane;
+                    bool eq = false;
+                    if (i + 1 < cnt) eq = same_at(i);
+                    const uint32_t eqm = __ballot_sync(0xffffffffu, eq && i < whi);
+                    const uint32_t headm = eqm & ~((eqm << 1) | carry);
+                    carry = eqm >> 31;
+                    if ((headm >> lane) & 1u) my_heads[nheads + __popc(headm & lanemask_lt())] = uint16_t(i);
+                    nheads += __popc(headm);
+                }
+            }
+            __syncwarp();
+            tick(5);
+            for (uint32_t hidx = lane; hidx < nheads; hidx += 32) {
+                const uint32_t i = my_heads[hidx];
+                const Rec<WORDS> ri = load_rec<WORDS>(s_out, i);
                 uint32_t q = i + 2;
-                while (q < cnt && q - i <= uint32_t(LS_MAXRUN) &&
-                       (rec_prefix<WORDS, FLOATK>(p.key, load_rec<WORDS>(s_out, q)) >> sh) == ki)
-                    ++q;
+                while (q < cnt && q - i <= uint32_t(LS_MAXRUN) && same_fast(ri, load_rec<WORDS>(s_out, q))) ++q;
                 if (q - i > uint32_t(LS_MAXRUN)) {
                     s_seg[1] = 1;  // too long for an insertion sort: the whole segment takes the slow path
                     continue;
@@ -257,11 +299,11 @@ __global__ void __launch_bounds__(LS_THREADS, 1) local_sort_kernel(const LocalSo
                     if (b != a) store_rec<WORDS>(s_out, b, x);
                 }
             }
-            __syncthreads();
+            __syncwarp();
             // give the slot tables back clean
-            for (uint32_t w = tid; w < (nheads + 1) / 2; w += THREADS) reinterpret_cast<uint32_t*>(s_slot_raw)[w] = 0;
-            if (tid == 0) s_seg[2] = 0;
+            for (uint32_t w = lane; w < (nheads + 1) / 2; w += 32) reinterpret_cast<uint32_t*>(my_heads)[w] = 0;
             __syncthreads();
+            tick(6);
             if (s_seg[1] == 0) break;
             // slow path: the staging buffer holds a stable rearrangement of the segment; start over with
             // a full LSD over every local level
@@ -280,6 +322,7 @@ __global__ void __launch_bounds__(LS_THREADS, 1) local_sort_kernel(const LocalSo
         fetch(seg);
         for (uint32_t i = tid; i < cur_cnt; i += THREADS)
             store_rec<WORDS>(cur_g, uint64_t(i), load_rec<WORDS>(s_out, i));
+        tick(7);
     }
 }
 
