@@ -557,12 +557,13 @@ int sort_hybrid(DeviceCtx& c, cudaStream_t st, void* data, void* tmp, uint64_t n
     if (!word_path_ok(lo, data, tmp) || n >= (1ull << 32)) return B200_OK;
     SplitParams key;
     if (lower_prefix(lo, &key) != B200_OK) return B200_OK;
-    // worth it from 256 M records and the cost of ~5.5 LSD passes on: the hybrid costs about as much as
-    // 5.1 passes whatever the key width (1 B u64: 25.9 ms against 1.4 + 4.77 ms per level, and an odd
-    // number of LSD passes ends with a 2.5 ms copy back); K3 handles one segment per SM at a time,
-    // so segments below a few thousand records leave it idle
-    const double lsd_cost = double(active.size()) + ((active.size() & 1) && copy_back_counts ? 0.5 : 0.0);
-    if (mode == 2 && (lsd_cost < 5.5 || n < (256ull << 20))) return B200_OK;
+    // worth it from 256 M records and five active levels on: the hybrid costs about as much as 4.5 LSD
+    // passes whatever the key width (1 B u64: 22.7 ms against 1.4 + 4.77 ms per level, and an odd number
+    // of LSD passes ends with a 2.5 ms copy back); K3 handles one segment per SM at a time, so segments
+    // below a few thousand records leave it idle, and with four active levels K3's two local levels cost
+    // more than the two K2 passes they replace
+    (void)copy_back_counts;
+    if (mode == 2 && (active.size() < 5 || n < (256ull << 20))) return B200_OK;
 
     // ---- the digits: bit windows over the varying bits of the key image ----
     // K1's per-level histograms tell which bits of the 64-bit key image vary at all.  The two MSD

@@ -263,21 +263,49 @@ __global__ void __launch_bounds__(LS_THREADS, 1) local_sort_kernel(const LocalSo
                 const uint32_t wlo = uint32_t(warp) * per, whi = wlo + per < cnt ? wlo + per : cnt;
                 uint32_t carry = 0;
                 if (wlo > 0 && wlo < cnt) carry = same_at(wlo - 1) ? 1u : 0u;
-#pragma unroll 2
-                for (uint32_t i0 = wlo; i0 < whi; i0 += 32) {
-                    const uint32_t i = i0 + lane;
-                    bool eq = false;
-                    if (i + 1 < cnt) eq = same_at(i);
-                    const uint32_t eqm = __ballot_sync(0xffffffffu, eq && i < whi);
-                    const uint32_t headm = eqm & ~((eqm << 1) | carry);
-                    carry = eqm >> 31;
-                    if ((headm >> lane) & 1u) my_heads[nheads + __popc(headm & lanemask_lt())] = uint16_t(i);
-                    nheads += __popc(headm);
+                for (uint32_t i0 = wlo; i0 < whi; i0 += 128) {
+                    // four rounds at a time, loads first: the list stores below order against shared loads
+                    uint32_t eqm[4];
+#pragma unroll
+                    for (int u = 0; u < 4; ++u) {
+                        const uint32_t i = i0 + u * 32 + lane;
+                        bool eq = false;
+                        if (i + 1 < cnt && i < whi) eq = same_at(i);
+                        eqm[u] = __ballot_sync(0xffffffffu, eq);
+                    }
+#pragma unroll
+                    for (int u = 0; u < 4; ++u) {
+                        const uint32_t headm = eqm[u] & ~((eqm[u] << 1) | carry);
+                        carry = eqm[u] >> 31;
+                        if ((headm >> lane) & 1u)
+                            my_heads[nheads + __popc(headm & lanemask_lt())] = uint16_t(i0 + u * 32 + lane);
+                        nheads += __popc(headm);
+                    }
                 }
             }
             __syncwarp();
             tick(5);
-            for (uint32_t hidx = lane; hidx < nheads; hidx += 32) {
+            // nine runs in ten are two records long: three independent loads and at most one swap, all lanes
+            // together; the heads of longer runs are compacted to the front of the list for a second sweep
+            uint32_t nlong = 0;  // warp-uniform
+            for (uint32_t hbase = 0; hbase < nheads; hbase += 32) {
+                const bool act = hbase + lane < nheads;
+                const uint32_t i = act ? my_heads[hbase + lane] : 0u;
+                bool more = false;
+                if (act) {
+                    const Rec<WORDS> ri = load_rec<WORDS>(s_out, i), r1 = load_rec<WORDS>(s_out, i + 1);
+                    more = i + 2 < cnt && same_fast(ri, load_rec<WORDS>(s_out, i + 2));
+                    if (!more && rec_prefix<WORDS, FLOATK>(p.key, r1) < rec_prefix<WORDS, FLOATK>(p.key, ri)) {
+                        store_rec<WORDS>(s_out, i, r1);
+                        store_rec<WORDS>(s_out, i + 1, ri);
+                    }
+                }
+                const uint32_t lm = __ballot_sync(0xffffffffu, more);  // (every lane has read its entry by now)
+                if (more) my_heads[nlong + __popc(lm & lanemask_lt())] = uint16_t(i);
+                nlong += __popc(lm);
+            }
+            __syncwarp();
+            for (uint32_t hidx = lane; hidx < nlong; hidx += 32) {
                 const uint32_t i = my_heads[hidx];
                 const Rec<WORDS> ri = load_rec<WORDS>(s_out, i);
                 uint32_t q = i + 2;
