@@ -280,7 +280,7 @@ def run_b200(args):
     if world > 1:
         slack = 1.0 + args.recv_slack
         cap = int(nbytes * slack) // es * es
-        if args.exchange == "peer":
+        if args.exchange in ("peer", "ce"):
             from rdst_b200.dist import PeerBuffers
 
             scratch["peers"] = PeerBuffers(cap)
@@ -288,6 +288,10 @@ def run_b200(args):
             scratch["part"] = torch.empty(nbytes, dtype=torch.uint8, device="cuda")
             scratch["recv"] = torch.empty(cap, dtype=torch.uint8, device="cuda")
         scratch["tmp"] = torch.empty(cap, dtype=torch.uint8, device="cuda")
+        if args.exchange == "ce":
+            # the send regions live in the local sort's scratch buffer: it is idle until the exchange is over
+            scratch["part"] = scratch["tmp"]
+            scratch["ce_chunks"] = args.ce_chunks
 
     def barrier():
         if world > 1:
@@ -461,12 +465,12 @@ def run_b200(args):
     }
     if world > 1:
         line["exchange"] = {"mode": args.exchange}
-        line["exchange"].update({k: last.get(k) for k in ("level", "n_recv", "sent_bytes", "phase_ms", "splitter_mode", "splitter_plan_ms")})
+        line["exchange"].update({k: last.get(k) for k in ("level", "n_recv", "sent_bytes", "phase_ms", "splitter_mode", "splitter_plan_ms", "exchange_path")})
         line["exchange"]["max_n_recv_over_ranks"] = max_n_recv
         line["exchange"]["imbalance"] = max_n_recv / float(n)
         pm = last.get("phase_ms") or {}
         if pm.get("all_to_all"):
-            t_x = pm["all_to_all"] + (pm["partition"] if args.exchange == "peer" else 0.0)
+            t_x = pm["all_to_all"] + (pm["partition"] if args.exchange in ("peer", "ce") else 0.0)
             line["exchange"]["exchange_ms"] = t_x
             line["exchange"]["all_to_all_GBps_per_direction"] = last["sent_bytes"] / (t_x * 1e-3) / 1e9
             line["exchange"]["nvlink_peak_GBps"] = 900.0
@@ -488,8 +492,10 @@ def main():
     ap.add_argument("--cpu-steps", type=int, default=3)
     ap.add_argument("--e2e-steps", type=int, default=3)
     ap.add_argument("--recv-slack", type=float, default=0.3)
-    ap.add_argument("--exchange", default="peer", choices=["peer", "nccl"],
-                    help="N>1: fused partition + peer stores over NVLink (CUDA IPC), or partition + NCCL all-to-all")
+    ap.add_argument("--exchange", default="peer", choices=["peer", "ce", "nccl"],
+                    help="N>1: fused partition + peer stores over NVLink (CUDA IPC); ce: chunked partition pipelined with "
+                         "copy-engine pushes into the same IPC buffers; nccl: partition + NCCL all-to-all")
+    ap.add_argument("--ce-chunks", type=int, default=8)
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-cpu", action="store_true")
     args = ap.parse_args()

@@ -317,6 +317,50 @@ def _device_view(torch, ptr, nbytes):
     return torch.as_tensor(h, device="cuda")
 
 
+def _pipelined_exchange(eng, key, local, scratch, peers, bounds, hist_c, level, split, world, rank, starts, send_counts):
+    """Partition + exchange as a two-stage pipeline: the shard is partitioned chunk by chunk into
+    local send regions (K2 on the SMs, HBM speed) while the copy engines push the previous chunk's
+    regions into the owners' receive buffers over NVLink.  The fused kernel stores straight into the
+    peers, but an SM whose store queue is full of NVLink writes also stalls its ranking warps
+    (measured: 13.5 ms at N=8 = partition + drain, not max(partition, drain)); the copy engines need
+    no SM at all.  Destination layout is the fused path's: by source rank, then in input order."""
+    torch = eng.torch
+    es = key.elem_size
+    part = scratch["part"]
+    streams = scratch.setdefault("_ce_streams", [torch.cuda.Stream() for _ in range(2)])
+    main = torch.cuda.current_stream()
+    sent = np.zeros(world, dtype=np.int64)  # records of this rank already placed per destination
+    views = scratch.setdefault("_peer_views", {})
+    for g in range(world):
+        if g not in views:
+            views[g] = peers.local if g == rank else _device_view(torch, peers.ptrs[g], peers.capacity)
+    part_of = part_of_digit(split, world)
+    for c in range(len(bounds) - 1):
+        lo, hi = bounds[c], bounds[c + 1]
+        # the chunk's records per destination, from its own histogram; this rank's own records go
+        # straight into its receive buffer, the others into send regions packed at the chunk's place
+        pc_plan = np.bincount(part_of, weights=hist_c[c][level].astype(np.float64), minlength=world).astype(np.int64)
+        off = lo + np.concatenate([[0], np.cumsum(pc_plan)[:-1]])
+        dst = [part.data_ptr() + int(off[g]) * es for g in range(world)]
+        dst[rank] = peers.local_ptr + (int(starts[rank]) + int(sent[rank])) * es
+        # returns when the chunk's send regions are complete (the entry point synchronises the stream)
+        pc = eng.partition_peers(local[lo * es: hi * es], dst, hi - lo, level, hist_c[c][level], split, world)
+        assert np.array_equal(pc, pc_plan), "partition counts disagree with the chunk histogram"
+        sent[rank] += int(pc[rank])
+        for k in range(world - 1):
+            g = (rank + 1 + k) % world  # at any moment every destination hears from one source
+            cnt = int(pc[g])
+            if cnt == 0:
+                continue
+            d0 = (int(starts[g]) + int(sent[g])) * es
+            with torch.cuda.stream(streams[k % len(streams)]):
+                views[g][d0: d0 + cnt * es].copy_(part[int(off[g]) * es: (int(off[g]) + cnt) * es], non_blocking=True)
+            sent[g] += cnt
+    assert np.array_equal(sent, send_counts), "partition counts disagree with the gathered histograms"
+    for st in streams:
+        main.wait_stream(st)
+
+
 # --------------------------------------------------------------------------- the sort
 MAX_SPLITTERS = 15        # include/b200sort.h: nsplit <= 15
 SAMPLES_PER_RANK = 8192   # key prefixes each rank contributes to the splitter choice
@@ -342,8 +386,20 @@ def sharded_sort(local, n_local: int, key: RadixKey, engine=None, group=None, re
     if timings is not None and hasattr(eng, "torch"):
         ev = [eng.torch.cuda.Event(enable_timing=True) for _ in range(5)]
         ev[0].record()
-    # 1. K1 on the local shard, all levels in one read
-    hist = eng.histogram(local, n_local)
+    # 1. K1 on the local shard, all levels in one read (chunk by chunk for the pipelined exchange,
+    #    which needs every chunk's own histogram of the partition level)
+    ce_chunks = int(scratch.get("ce_chunks", 0)) if scratch else 0
+    pipelined = (ce_chunks > 1 and scratch.get("peers") is not None and scratch.get("part") is not None
+                 and hasattr(eng, "torch") and n_local >= ce_chunks * 4096 and key.elem_size % 4 == 0
+                 and key.elem_size <= 16)
+    bounds = hist_c = None
+    if pipelined:
+        bounds = [(n_local * c) // ce_chunks for c in range(ce_chunks + 1)]
+        es = key.elem_size
+        hist_c = [eng.histogram(local[bounds[c] * es: bounds[c + 1] * es], bounds[c + 1] - bounds[c]) for c in range(ce_chunks)]
+        hist = np.sum(hist_c, axis=0).astype(np.uint64)
+    else:
+        hist = eng.histogram(local, n_local)
     # 2. global histogram + every rank's rows: one small all-gather ([P, L, 256] i64)
     mine = eng.to_comm(hist.astype(np.int64))
     gathered = [mine.new_empty(mine.shape) for _ in range(world)]
@@ -415,7 +471,10 @@ def sharded_sort(local, n_local: int, key: RadixKey, engine=None, group=None, re
         starts = np.concatenate([np.zeros((1, world), dtype=np.int64), np.cumsum(m, axis=0)])[rank]  # [g]
         dst = [peers.ptrs[g] + int(starts[g]) * key.elem_size for g in range(world)]
         peers.fence()  # every rank is done with the previous contents of its receive buffer
-        if splitters is not None:
+        if pipelined and splitters is None:
+            _pipelined_exchange(eng, key, local, scratch, peers, bounds, hist_c, level, split, world, rank, starts,
+                                send_counts)
+        elif splitters is not None:
             eng.partition_splitters(local, None, dst, n_local, splitters, incl_mask_for_rank(t_thr, rank), send_counts)
         else:
             pc = eng.partition_peers(local, dst, n_local, level, hist[level], split, world)
@@ -443,6 +502,8 @@ def sharded_sort(local, n_local: int, key: RadixKey, engine=None, group=None, re
     if timings is not None:
         timings.update({"level": level, "split": split.tolist(), "n_recv": n_recv, "local": st,
                         "splitter_mode": "prefix" if splitters is not None else "digit", "splitter_plan_ms": plan_t,
+                        "exchange_path": "pipelined" if (pipelined and splitters is None and peers is not None) else
+                        ("fused" if peers is not None else "all_to_all"),
                         "sent_bytes": int((send_counts.sum() - send_counts[rank]) * key.elem_size)})
         if ev:
             ev[4].record()

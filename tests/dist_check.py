@@ -50,14 +50,21 @@ def main():
     ok = True
     from rdst_b200.dist import PeerBuffers
 
-    peers = PeerBuffers(64 << 20) if os.environ.get("DIST_CHECK_MODE", "nccl") == "peer" else None
+    mode = os.environ.get("DIST_CHECK_MODE", "nccl")
+    peers = PeerBuffers(64 << 20) if mode in ("peer", "ce") else None
+    part = torch.empty(64 << 20, dtype=torch.uint8, device="cuda") if mode == "ce" else None
     for name, key, full in cases():
         es = key.elem_size
         n = len(full) // es
         lo, hi = rank * n // world, (rank + 1) * n // world
         shard = torch.from_numpy(full[lo * es: hi * es].copy()).cuda()
         tm = {}
-        out, n_out = sharded_sort(shard, hi - lo, key, scratch={"peers": peers} if peers else None, timings=tm)
+        scratch = None
+        if peers:
+            scratch = {"peers": peers}
+            if part is not None:  # chunked partition pipelined with copy-engine pushes (3 uneven chunks)
+                scratch.update({"part": part, "ce_chunks": 3})
+        out, n_out = sharded_sort(shard, hi - lo, key, scratch=scratch, timings=tm)
         torch.cuda.synchronize()
         mine = out[: n_out * es].cpu()
         sizes = [torch.zeros(1, dtype=torch.int64, device="cuda") for _ in range(world)]
@@ -72,7 +79,7 @@ def main():
             got = torch.cat(bufs).cpu().numpy().tobytes()
             exp = o.stable_sorted(full, key).tobytes()
             good = got == exp
-            print(f"[dist_check] {'peer' if peers else 'nccl'} {name}: {'ok' if good else 'MISMATCH'} splitters={tm.get('splitter_mode')} sizes={[s // es for s in sizes]}", flush=True)
+            print(f"[dist_check] {mode} {name} ({tm.get('exchange_path')}): {'ok' if good else 'MISMATCH'} splitters={tm.get('splitter_mode')} sizes={[s // es for s in sizes]}", flush=True)
             ok = ok and good
     dist.barrier()
     if peers:

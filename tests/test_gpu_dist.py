@@ -9,10 +9,11 @@ pytestmark = pytest.mark.gpu
 HERE = os.path.dirname(os.path.abspath(__file__))
 
 
-@pytest.mark.parametrize("mode", ["nccl", "peer"])
+@pytest.mark.parametrize("mode", ["nccl", "peer", "ce"])
 def test_sharded_sort_matches_oracle(mode):
     """nccl: partition + all_to_all_single; peer: fused partition kernel storing into the peers'
-    IPC-mapped receive buffers over NVLink."""
+    IPC-mapped receive buffers over NVLink; ce: chunked partition pipelined with copy-engine pushes
+    into the same buffers."""
     import torch
 
     n = torch.cuda.device_count()
