@@ -425,15 +425,23 @@ __global__ void __launch_bounds__(H2_THREADS) hist2_kernel(const Hist2Params p) 
         const uint64_t hi = lo + H2_CHUNK < p.n ? lo + H2_CHUNK : p.n;
         const uint32_t dfirst = rec_digit_w<WORDS, FLOATK, true>(p.l1, load_rec<WORDS>(p.src + lo * WORDS, 0));
         __syncthreads();
-        for (uint64_t i = lo + threadIdx.x; i < hi; i += H2_THREADS) {
-            const Rec<WORDS> r = load_rec<WORDS>(p.src + i * WORDS, 0);
+        auto count = [&](const Rec<WORDS>& r) {
             const uint32_t d1 = rec_digit_w<WORDS, FLOATK, true>(p.l1, r), d2 = rec_digit_w<WORDS, FLOATK, true>(p.l2, r);
             const uint32_t rel = d1 - dfirst;
             if (rel < uint32_t(H2_SPAN))
                 atomicAdd(&sh[rel * RADIX + d2], 1u);
             else
                 atomicAdd(p.joint + size_t(d1) * RADIX + d2, 1ull);
+        };
+        uint64_t i = lo + threadIdx.x;
+        for (; i + 3 * H2_THREADS < hi; i += 4 * H2_THREADS) {  // four loads in flight per thread
+            Rec<WORDS> r[4];
+#pragma unroll
+            for (int k = 0; k < 4; ++k) r[k] = load_rec<WORDS>(p.src + (i + k * H2_THREADS) * WORDS, 0);
+#pragma unroll
+            for (int k = 0; k < 4; ++k) count(r[k]);
         }
+        for (; i < hi; i += H2_THREADS) count(load_rec<WORDS>(p.src + i * WORDS, 0));
         __syncthreads();
         for (int i = threadIdx.x; i < H2_SPAN * RADIX; i += H2_THREADS) {
             const uint32_t c = sh[i];
