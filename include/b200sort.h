@@ -225,6 +225,26 @@ int b200_host_free(void* p);
 /* Release the cached per-device scratch pool. */
 int b200_release_scratch(int device);
 
+/*
+ * Planner introspection (host only, no GPU): the digits the hybrid route would sort on for an
+ * input with these per-level histograms (hist[LEVELS][256], what b200_histogram_device returns).
+ * The route is the GPU form of the reference's MSB-first recursion with an LSB finish
+ * (src/sorter.rs:24-171, src/tuners/standard_tuner.rs:13-63): two global MSD passes on
+ * digit[0] (most significant) and digit[1], then every segment is sorted on chip on the local
+ * windows (least significant first).  Digits are bit windows [lo, lo + width) of the 64-bit
+ * order-preserving key image (level l = bits 8l .. 8l+7), placed on the bits that vary.
+ * eligible = 0: the key shape or the data rule the route out (the LSD passes run).
+ */
+typedef struct b200_window_plan {
+    uint32_t eligible;
+    uint32_t aligned;        /* both MSD digits are whole levels (no window histogram pass) */
+    uint64_t vary;           /* bits of the key image that differ between some two records */
+    uint32_t digit_lo[2], digit_width[2];
+    uint32_t nlocal;
+    uint32_t local_lo[8], local_width[8];
+} b200_window_plan;
+int b200_hybrid_plan(const b200_key_desc* desc, const uint64_t* hist, size_t n, b200_window_plan* out);
+
 /* Tuner introspection: the Tuner now only picks a tile/occupancy variant. */
 int b200_variant_count(void);
 const char* b200_variant_name(int variant);

@@ -95,6 +95,21 @@ LIB_PATH = os.path.join(os.path.dirname(os.path.abspath(__file__)), "libb200sort
 _lib = None
 
 # name -> (restype, argtypes): every symbol include/b200sort.h declares
+class WindowPlan(C.Structure):
+    """b200_window_plan (include/b200sort.h): the digits the hybrid route would sort on."""
+
+    _fields_ = [
+        ("eligible", C.c_uint32),
+        ("aligned", C.c_uint32),
+        ("vary", C.c_uint64),
+        ("digit_lo", C.c_uint32 * 2),
+        ("digit_width", C.c_uint32 * 2),
+        ("nlocal", C.c_uint32),
+        ("local_lo", C.c_uint32 * 8),
+        ("local_width", C.c_uint32 * 8),
+    ]
+
+
 SYMBOLS = {
     "b200_sort_host": (C.c_int, [C.c_void_p, C.c_size_t, C.POINTER(KeyDesc), C.POINTER(SortOpts), C.POINTER(Stats)]),
     "b200_sort_device": (
@@ -162,6 +177,7 @@ SYMBOLS = {
     "b200_host_alloc": (C.c_int, [C.POINTER(C.c_void_p), C.c_size_t]),
     "b200_host_free": (C.c_int, [C.c_void_p]),
     "b200_release_scratch": (C.c_int, [C.c_int]),
+    "b200_hybrid_plan": (C.c_int, [C.POINTER(KeyDesc), C.POINTER(C.c_uint64), C.c_size_t, C.POINTER(WindowPlan)]),
     "b200_variant_count": (C.c_int, []),
     "b200_variant_name": (C.c_char_p, [C.c_int]),
     "b200_strerror": (C.c_char_p, [C.c_int]),

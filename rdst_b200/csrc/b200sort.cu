@@ -531,6 +531,52 @@ int launch_hist2_w(bool floatk, int grid, cudaStream_t st, const Hist2Params& hp
     return B200_OK;
 }
 
+// The digits of the hybrid path, from K1's per-level histograms (host only; b200_hybrid_plan exposes it).
+// D1 = the top 8 varying bits of the key image, D2 = the 8 bits below D1 starting at the next varying
+// bit, local windows = byte-wide windows of what is left, anchored under D2 (least significant first;
+// windows without a varying bit are dropped: sorting on constant bits is an exact no-op).
+struct WindowPlan {
+    uint64_t vary;            // bits of the key image that differ between some two records
+    uint32_t w1_lo, w2_lo, w2_width;
+    uint32_t nlocal, local_lo[LS_MAXLEV], local_width[LS_MAXLEV];
+    bool aligned;             // D1 and D2 are whole levels: K1 already has their histograms
+};
+bool plan_windows(const Lowered& lo, const uint64_t* hist, uint64_t n, WindowPlan* wp) {
+    memset(wp, 0, sizeof(*wp));
+    if (lo.levels > 8) return false;
+    uint64_t vary = 0;
+    for (uint32_t l = 0; l < lo.levels; ++l) {
+        const uint64_t* h = hist + size_t(l) * RADIX;
+        for (uint32_t bit = 0; bit < 8; ++bit) {
+            uint64_t ones = 0;
+            for (uint32_t d = 0; d < uint32_t(RADIX); ++d)
+                if (d >> bit & 1u) ones += h[d];
+            if (ones != 0 && ones != n) vary |= 1ull << (8 * l + bit);
+        }
+    }
+    wp->vary = vary;
+    if (!vary) return false;
+    const int T1 = 63 - __builtin_clzll(vary);
+    if (T1 < 8) return false;
+    wp->w1_lo = uint32_t(T1 - 7);
+    const uint64_t below1 = vary & ((1ull << wp->w1_lo) - 1);
+    if (!below1) return false;
+    const int T2 = 63 - __builtin_clzll(below1);
+    wp->w2_lo = T2 >= 7 ? uint32_t(T2 - 7) : 0u;
+    wp->w2_width = uint32_t(T2) + 1 - wp->w2_lo;
+    uint32_t los[8], widths[8], cnt = 0;
+    for (uint32_t hi = wp->w2_lo; hi > 0;) {
+        const uint32_t width = std::min<uint32_t>(8, hi);
+        hi -= width;
+        if ((vary >> hi) & ((1ull << width) - 1)) los[cnt] = hi, widths[cnt++] = width;
+    }
+    if (cnt == 0 || cnt > uint32_t(LS_MAXLEV)) return false;
+    for (uint32_t i = 0; i < cnt; ++i) wp->local_lo[i] = los[cnt - 1 - i], wp->local_width[i] = widths[cnt - 1 - i];
+    wp->nlocal = cnt;
+    wp->aligned = wp->w1_lo % 8 == 0 && wp->w2_lo % 8 == 0 && wp->w2_width == 8;
+    return true;
+}
+
 template <int WORDS>
 int launch_hist_win_w(bool floatk, int grid, cudaStream_t st, const HistWinParams& hp) {
     if (floatk)
@@ -565,48 +611,18 @@ int sort_hybrid(DeviceCtx& c, cudaStream_t st, void* data, void* tmp, uint64_t n
     (void)copy_back_counts;
     if (mode == 2 && (active.size() < 5 || n < (256ull << 20))) return B200_OK;
 
-    // ---- the digits: bit windows over the varying bits of the key image ----
-    // K1's per-level histograms tell which bits of the 64-bit key image vary at all.  The two MSD
-    // digits are the top 8 varying bits and the next 8 below them wherever they start (keys that
-    // do not fill their type — or one rank's range of a sharded sort — still split 65 536 ways);
-    // the local levels are the byte-aligned windows of what is left below.
-    uint64_t vary = 0;
-    for (uint32_t l = 0; l < lo.levels; ++l) {
-        const uint64_t* h = c.h_hist + size_t(l) * RADIX;
-        for (uint32_t bit = 0; bit < 8; ++bit) {
-            uint64_t ones = 0;
-            for (uint32_t d = 0; d < uint32_t(RADIX); ++d)
-                if (d >> bit & 1u) ones += h[d];
-            if (ones != 0 && ones != n) vary |= 1ull << (8 * l + bit);
-        }
-    }
-    if (!vary) return B200_OK;
-    const int T1 = 63 - __builtin_clzll(vary);
-    if (T1 < 8) return B200_OK;
-    const uint32_t w1_lo = uint32_t(T1 - 7);
-    const uint64_t below1 = vary & ((1ull << w1_lo) - 1);
-    if (!below1) return B200_OK;
-    const int T2 = 63 - __builtin_clzll(below1);
-    const uint32_t w2_lo = T2 >= 7 ? uint32_t(T2 - 7) : 0u, w2_width = uint32_t(T2) + 1 - w2_lo;
+    // ---- the digits: bit windows over the varying bits of the key image (plan_windows) ----
+    // keys that do not fill their type — or one rank's range of a sharded sort — still split 65 536 ways
+    WindowPlan wp;
+    if (!plan_windows(lo, c.h_hist, n, &wp)) return B200_OK;
+    const uint32_t w1_lo = wp.w1_lo, w2_lo = wp.w2_lo, w2_width = wp.w2_width, nlocal = wp.nlocal;
     const DigitParams W1 = window_params(lo, key, w1_lo, 8), W2 = window_params(lo, key, w2_lo, w2_width);
-    // local windows, anchored below the second digit so that the top ones are full bytes (K3's fast
-    // path radix-sorts only the top two and wants them to separate the records); least significant first
     DigitParams local[LS_MAXLEV];
-    uint32_t local_lo[LS_MAXLEV], nlocal = 0;
-    {
-        uint32_t los[8], widths[8], cnt = 0;
-        for (uint32_t hi = w2_lo; hi > 0;) {
-            const uint32_t width = std::min<uint32_t>(8, hi);
-            hi -= width;
-            if ((vary >> hi) & ((1ull << width) - 1)) los[cnt] = hi, widths[cnt++] = width;  // constant bits: an exact no-op
-        }
-        for (uint32_t i = 0; i < cnt; ++i) {
-            local[i] = window_params(lo, key, los[cnt - 1 - i], widths[cnt - 1 - i]);
-            local_lo[i] = los[cnt - 1 - i];
-        }
-        nlocal = cnt;
+    uint32_t local_lo[LS_MAXLEV];
+    for (uint32_t i = 0; i < nlocal; ++i) {
+        local[i] = window_params(lo, key, wp.local_lo[i], wp.local_width[i]);
+        local_lo[i] = wp.local_lo[i];
     }
-    if (nlocal == 0 || nlocal > uint32_t(LS_MAXLEV)) return B200_OK;
     {   // the kernels take the upper bits of a window that crosses words from the record's last word
         auto crossing_ok = [&](const DigitParams& w) { return w.word2 == w.word || w.word2 == words - 1; };
         bool ok = crossing_ok(W1) && crossing_ok(W2);
@@ -614,7 +630,7 @@ int sort_hybrid(DeviceCtx& c, cudaStream_t st, void* data, void* tmp, uint64_t n
         if (!ok) return B200_OK;
     }
     // byte-aligned windows are levels: K1 already has their histograms and bucket bases
-    const bool aligned = w1_lo % 8 == 0 && w2_lo % 8 == 0 && w2_width == 8;
+    const bool aligned = wp.aligned;
     const uint32_t A1 = w1_lo / 8, A2 = w2_lo / 8;
 
     int rc = ensure_bytes(reinterpret_cast<void**>(&c.d_hyb), &c.hyb_bytes, HYB_BYTES);
@@ -1432,6 +1448,27 @@ int b200_release_scratch(int device) {
         *ptrs[i] = nullptr;
         *sizes[i] = 0;
     }
+    return B200_OK;
+}
+
+int b200_hybrid_plan(const b200_key_desc* desc, const uint64_t* hist, size_t n, b200_window_plan* out) {
+    Lowered lo;
+    int rc = lower_desc(desc, &lo);
+    if (rc) return rc;
+    if (!hist || !out) return B200_ERR_BAD_ARG;
+    memset(out, 0, sizeof(*out));
+    SplitParams key;
+    const uint32_t words = lo.elem_size / 4;
+    if (lo.elem_size % 4 != 0 || (words != 1 && words != 2) || lo.levels > 8 || lower_prefix(lo, &key) != B200_OK) return B200_OK;
+    WindowPlan wp;
+    if (!plan_windows(lo, hist, n, &wp)) return B200_OK;
+    out->eligible = 1;
+    out->aligned = wp.aligned ? 1u : 0u;
+    out->vary = wp.vary;
+    out->digit_lo[0] = wp.w1_lo, out->digit_width[0] = 8;
+    out->digit_lo[1] = wp.w2_lo, out->digit_width[1] = wp.w2_width;
+    out->nlocal = wp.nlocal;
+    for (uint32_t i = 0; i < wp.nlocal; ++i) out->local_lo[i] = wp.local_lo[i], out->local_width[i] = wp.local_width[i];
     return B200_OK;
 }
 
