@@ -25,6 +25,7 @@
 #include "hist.cuh"
 #include "splitters.cuh"
 #include "local_sort.cuh"
+#include "sorted_check.cuh"
 #include "launch.h"
 #include "onesweep.cuh"
 #include "variants.h"
@@ -131,6 +132,7 @@ struct DeviceCtx {
     // small device block: hist [64][256] u64 | base [64][256] u64 | tickets [64] u32 | remap [256] u8 | part base
     uint8_t* d_small = nullptr;
     uint64_t* h_hist = nullptr;  // pinned [64][256]
+    uint32_t* h_flag = nullptr;  // pinned: K0's out-of-order flag
     void* d_tmp = nullptr;
     size_t tmp_bytes = 0;
     uint64_t* d_lookback = nullptr;
@@ -157,7 +159,8 @@ constexpr size_t SMALL_REMAP_OFF = SMALL_TICKET_OFF + 1024;
 constexpr size_t SMALL_PBASE_OFF = SMALL_REMAP_OFF + 256;
 constexpr size_t SMALL_DTAB_OFF = SMALL_PBASE_OFF + RADIX * 8;
 constexpr size_t SMALL_SPLIT_OFF = SMALL_DTAB_OFF + RADIX * 8;  // less[15] | equal[15] (u64), 256 bytes
-constexpr size_t SMALL_BYTES = SMALL_SPLIT_OFF + 256;
+constexpr size_t SMALL_FLAG_OFF = SMALL_SPLIT_OFF + 256;  // K0 (sorted check) flag
+constexpr size_t SMALL_BYTES = SMALL_FLAG_OFF + 256;
 
 constexpr int MAX_DEVICES = 64;
 DeviceCtx g_ctx[MAX_DEVICES];
@@ -195,6 +198,7 @@ int get_ctx(int device, DeviceCtx** out) {
         CUDA_TRY(cudaMalloc(&c.d_small, SMALL_BYTES));
         CUDA_TRY(cudaMallocHost(&c.h_hist, size_t(MAX_LEVELS) * RADIX * 8));
         CUDA_TRY(cudaMallocHost(&c.h_joint, size_t(RADIX * RADIX + 1) * 8));
+        CUDA_TRY(cudaMallocHost(&c.h_flag, 64));
         for (auto& a : c.aux) CUDA_TRY(cudaStreamCreateWithFlags(&a, cudaStreamNonBlocking));
         for (auto& ev : c.aux_ev) CUDA_TRY(cudaEventCreateWithFlags(&ev, cudaEventDisableTiming));
         c.ready = true;
@@ -858,6 +862,92 @@ int sort_hybrid(DeviceCtx& c, cudaStream_t st, void* data, void* tmp, uint64_t n
 }
 
 // ---------------------------------------------------------------------------
+// Small inputs: the whole array is one segment of K3.  rdst hands chunks of up to 128 records to a
+// comparison sort and runs everything else below its thresholds single-threaded in cache
+// (reference src/sorter.rs:33-45, src/sorts/comparative_sort.rs:29-119); on the GPU an array that
+// fits one SM's shared memory is sorted by ONE launch — no histogram, no read-back, no passes
+// through HBM, no scratch — which is what bounds the latency of small sorts.
+// ---------------------------------------------------------------------------
+bool small_sort_ok(const Lowered& lo, const void* data, uint64_t n, SplitParams* key) {
+    static const bool off = getenv("B200SORT_SMALL") && atoi(getenv("B200SORT_SMALL")) == 0;
+    if (off || hybrid_mode() == 0 || n > uint64_t(LS_CAP)) return false;
+    if (lo.elem_size != 4 && lo.elem_size != 8) return false;
+    if (lo.levels > uint32_t(LS_MAXLEV) || !word_path_ok(lo, data, data)) return false;
+    return lower_prefix(lo, key) == B200_OK;
+}
+
+int sort_small(DeviceCtx& c, cudaStream_t st, void* data, uint64_t n, const Lowered& lo, const SplitParams& key) {
+    int rc = ensure_bytes(reinterpret_cast<void**>(&c.d_hyb), &c.hyb_bytes, HYB_BYTES);
+    if (rc) return rc;
+    uint64_t* d_seg = reinterpret_cast<uint64_t*>(c.d_hyb + HYB_SEG_OFF);
+    uint32_t* d_tk = reinterpret_cast<uint32_t*>(c.d_hyb + HYB_TICKET_OFF);
+    c.h_joint[0] = 0;
+    c.h_joint[1] = n;
+    CUDA_TRY(cudaMemcpyAsync(d_seg, c.h_joint, 16, cudaMemcpyHostToDevice, st));
+    CUDA_TRY(cudaMemsetAsync(d_tk, 0, 4096, st));
+    LocalSortParams lp;
+    memset(&lp, 0, sizeof(lp));
+    lp.data = static_cast<uint32_t*>(data);
+    lp.seg_off = d_seg;
+    lp.nseg = 1;
+    lp.ticket = d_tk;
+    lp.nlev = lo.levels;
+    for (uint32_t l = 0; l < lo.levels; ++l) lp.lv[l] = window_params(lo, key, 8 * l, 8);
+    lp.nfast = 0;  // a plain stable LSD over every level, all in shared memory
+    lp.fix_shift = 0;
+    lp.key = key;
+    lp.slow_segments = d_tk + 300;
+    lp.prof = nullptr;
+    return lo.elem_size == 4 ? launch_local_sort_w<1>(lo.is_float, 1, st, lp) : launch_local_sort_w<2>(lo.is_float, 1, st, lp);
+}
+
+// ---------------------------------------------------------------------------
+// K0: is the input already in key order?  (rdst's already_sorted shortcut,
+// reference src/sort_utils.rs:125-136 and src/sorter.rs:59-65.)
+// ---------------------------------------------------------------------------
+int sorted_check_mode() {  // B200SORT_SORTED_CHECK=0 switches the early-out off
+    static const int mode = [] {
+        const char* env = getenv("B200SORT_SORTED_CHECK");
+        return env ? atoi(env) : 1;
+    }();
+    return mode;
+}
+
+// Enqueues K0 over records [0, n) and the read-back of its flag into c.h_flag (no synchronisation).
+int launch_sorted_check(DeviceCtx& c, cudaStream_t st, const Lowered& lo, const void* data, uint64_t n) {
+    uint32_t* d_flag = reinterpret_cast<uint32_t*>(c.d_small + SMALL_FLAG_OFF);
+    SortedCheckParams p;
+    memset(&p, 0, sizeof(p));
+    p.data = static_cast<const uint8_t*>(data);
+    p.n_pairs = n - 1;
+    p.flag = d_flag;
+    p.elem_size = lo.elem_size;
+    p.levels = lo.levels;
+    p.key_offset = lo.key_offset;
+    p.is_float = lo.is_float ? 1u : 0u;
+    p.sign_byte = lo.sign_byte;
+    for (uint32_t l = 0; l < lo.levels; ++l) p.lv[l] = lo.lv[l];
+    const uint32_t w = lo.key_width;
+    const bool word = lo.contiguous && (w == 1 || w == 2 || w == 4 || w == 8) && lo.levels <= w && lo.key_offset % w == 0 &&
+                      lo.elem_size % w == 0 && reinterpret_cast<uintptr_t>(data) % w == 0;
+    if (word) {
+        p.keep = lo.levels >= 8 ? ~0ull : ((1ull << (8 * lo.levels)) - 1ull);
+        for (uint32_t l = 0; l < lo.levels; ++l) p.flip |= uint64_t(lo.lv[l].xor_mask & 0xffu) << (8 * l);
+    }
+    CUDA_TRY(cudaMemsetAsync(d_flag, 0, 4, st));
+    const uint64_t per_cta = uint64_t(SC_THREADS) * SC_ITEMS;
+    const int grid = int(std::max<uint64_t>(1, std::min<uint64_t>(uint64_t(c.sm_count) * 8, (p.n_pairs + per_cta - 1) / per_cta)));
+    if (!word) sorted_check_kernel<0><<<grid, SC_THREADS, 0, st>>>(p);
+    else if (w == 8) sorted_check_kernel<8><<<grid, SC_THREADS, 0, st>>>(p);
+    else if (w == 4) sorted_check_kernel<4><<<grid, SC_THREADS, 0, st>>>(p);
+    else if (w == 2) sorted_check_kernel<2><<<grid, SC_THREADS, 0, st>>>(p);
+    else sorted_check_kernel<1><<<grid, SC_THREADS, 0, st>>>(p);
+    CUDA_TRY(cudaGetLastError());
+    CUDA_TRY(cudaMemcpyAsync(c.h_flag, d_flag, 4, cudaMemcpyDeviceToHost, st));
+    return B200_OK;
+}
+
+// ---------------------------------------------------------------------------
 // The sort proper, device resident.
 // ---------------------------------------------------------------------------
 int sort_device_impl(DeviceCtx& c, cudaStream_t st, void* data, void* tmp, uint64_t n, const Lowered& lo,
@@ -867,7 +957,59 @@ int sort_device_impl(DeviceCtx& c, cudaStream_t st, void* data, void* tmp, uint6
     uint32_t* d_ticket = reinterpret_cast<uint32_t*>(c.d_small + SMALL_TICKET_OFF);
 
     CUDA_TRY(cudaEventRecord(c.ev[0], st));
-    int rc = launch_histogram(c, st, lo, data, n, d_hist);
+    int rc = B200_OK;
+    SplitParams small_key;
+    if (variant < 0 && small_sort_ok(lo, data, n, &small_key)) {
+        rc = sort_small(c, st, data, n, lo, small_key);
+        if (rc) return rc;
+        CUDA_TRY(cudaEventRecord(c.ev[1], st));
+        CUDA_TRY(cudaEventRecord(c.ev[2], st));
+        CUDA_TRY(cudaStreamSynchronize(st));
+        if (result_ptr) *result_ptr = data;
+        if (stats) {
+            stats->levels_run = lo.levels;  // no histogram: every declared level is sorted on chip
+            stats->levels_skipped = 0;
+            stats->local_levels = lo.levels;
+            stats->algorithmic_bytes = n * lo.elem_size * (1ull + 2ull * lo.levels);
+            stats->kernel_launches = 1;
+            stats->tiles_per_pass = 1;
+            CUDA_TRY(cudaEventElapsedTime(&stats->ms_local, c.ev[0], c.ev[1]));
+            stats->ms_passes = stats->ms_total = stats->ms_local;
+        }
+        return B200_OK;
+    }
+    // K0, the already-sorted early-out.  Large inputs wait for its verdict before K1 (one extra
+    // synchronisation, microseconds against a sort of milliseconds; a presorted input then costs one
+    // read of the array); small inputs are latency bound, so K0 just rides in front of K1 and its flag
+    // comes back with the histograms.
+    constexpr uint64_t SORTED_SYNC_MIN = 4ull << 20;
+    const bool check = sorted_check_mode() != 0 && n >= 2;
+    auto sorted_return = [&](uint32_t launches) -> int {
+        CUDA_TRY(cudaEventRecord(c.ev[1], st));
+        CUDA_TRY(cudaEventRecord(c.ev[2], st));
+        CUDA_TRY(cudaStreamSynchronize(st));
+        if (result_ptr) *result_ptr = data;
+        if (stats) {
+            stats->levels_run = 0;
+            stats->levels_skipped = lo.levels;
+            stats->already_sorted = 1;
+            stats->algorithmic_bytes = n * lo.elem_size;
+            stats->kernel_launches = launches;
+            CUDA_TRY(cudaEventElapsedTime(&stats->ms_hist, c.ev[0], c.ev[1]));
+            stats->ms_total = stats->ms_hist;
+        }
+        return B200_OK;
+    };
+    if (check) {
+        *c.h_flag = 1;
+        rc = launch_sorted_check(c, st, lo, data, n);
+        if (rc) return rc;
+        if (n >= SORTED_SYNC_MIN) {
+            CUDA_TRY(cudaStreamSynchronize(st));
+            if (*c.h_flag == 0) return sorted_return(1);
+        }
+    }
+    rc = launch_histogram(c, st, lo, data, n, d_hist);
     if (rc) return rc;
     static const bool dbg = getenv("B200SORT_DEBUG_TIMING") != nullptr;
     if (dbg) cudaEventRecord(c.ev[8], st);
@@ -884,6 +1026,8 @@ int sort_device_impl(DeviceCtx& c, cudaStream_t st, void* data, void* tmp, uint6
         cudaEventElapsedTime(&d, c.ev[9], c.ev[1]);
         fprintf(stderr, "[b200sort] memset+K1 %.3f ms, scan %.3f ms, D2H hist %.3f ms\n", a, b, d);
     }
+
+    if (check && n < SORTED_SYNC_MIN && *c.h_flag == 0) return sorted_return(3);
 
     // levels with a single non-empty bucket are exact no-ops for a stable LSD sort
     std::vector<uint32_t> active;
@@ -962,7 +1106,7 @@ int sort_device_impl(DeviceCtx& c, cudaStream_t st, void* data, void* tmp, uint6
         CUDA_TRY(cudaEventElapsedTime(&stats->ms_passes, c.ev[1], c.ev[2]));
         CUDA_TRY(cudaEventElapsedTime(&stats->ms_total, c.ev[0], c.ev[2]));
         stats->tiles_per_pass = pp.num_tiles;
-        stats->kernel_launches = hybrid_done ? 2 + hybrid_launches : 2 + pass + hybrid_launches;  // K1 + scan + passes
+        stats->kernel_launches = (hybrid_done ? 2 + hybrid_launches : 2 + pass + hybrid_launches) + (check ? 1 : 0);  // (K0 +) K1 + scan + passes
     }
     return B200_OK;
 }
@@ -1041,7 +1185,7 @@ int b200_sort_host(void* host_ptr, size_t n, const b200_key_desc* desc, const b2
         c->bounce_bytes = CHUNK;
     }
 
-    CUDA_TRY(cudaEventRecord(c->ev[3], st));
+    CUDA_TRY(cudaEventRecord(c->ev[10], st));
     if (pinned) {
         CUDA_TRY(cudaMemcpyAsync(c->d_stage, host_ptr, bytes, cudaMemcpyHostToDevice, st));
     } else {
@@ -1060,13 +1204,15 @@ int b200_sort_host(void* host_ptr, size_t n, const b200_key_desc* desc, const b2
             k ^= 1;
         }
     }
-    CUDA_TRY(cudaEventRecord(c->ev[4], st));
+    CUDA_TRY(cudaEventRecord(c->ev[11], st));
     void* result = nullptr;
     b200_stats local{};
     rc = sort_device_impl(*c, st, c->d_stage, c->d_tmp, n, lo, opts ? opts->variant : -1, true, &result, &local);
     if (rc) return rc;
     CUDA_TRY(cudaEventRecord(c->ev[5], st));
-    if (pinned) {
+    if (local.already_sorted) {
+        // K0 found the input in key order: the caller's buffer already holds the result
+    } else if (pinned) {
         CUDA_TRY(cudaMemcpyAsync(host_ptr, result, bytes, cudaMemcpyDeviceToHost, st));
     } else {
         size_t off = 0;
@@ -1094,9 +1240,9 @@ int b200_sort_host(void* host_ptr, size_t n, const b200_key_desc* desc, const b2
     CUDA_TRY(cudaStreamSynchronize(st));
     if (stats) {
         *stats = local;
-        CUDA_TRY(cudaEventElapsedTime(&stats->ms_h2d, c->ev[3], c->ev[4]));
+        CUDA_TRY(cudaEventElapsedTime(&stats->ms_h2d, c->ev[10], c->ev[11]));
         CUDA_TRY(cudaEventElapsedTime(&stats->ms_d2h, c->ev[5], c->ev[6]));
-        CUDA_TRY(cudaEventElapsedTime(&stats->ms_total, c->ev[3], c->ev[6]));
+        CUDA_TRY(cudaEventElapsedTime(&stats->ms_total, c->ev[10], c->ev[6]));
     }
     return B200_OK;
 }

@@ -1,0 +1,110 @@
+// sorted_check.cuh — K0, the already-sorted early-out.
+//
+// rdst scans every chunk while its digits are still non-decreasing before it counts them
+// (reference src/sort_utils.rs:125-136) and skips the sort of a level whose digits already arrive
+// in order (src/sorter.rs:59-65); a fully presorted input therefore costs it counting passes only
+// (the `struct_sort` bench's "fully presorted" case, benches/struct_sort.rs:43-74).  The GPU
+// counterpart checks the whole key once: one read of the array (n*S bytes, HBM bound), and a
+// stable sort of an input that is already non-decreasing by its key is the identity, so the
+// engine returns without running K1/K2/K3.
+//
+// Every thread compares adjacent records i and i+1 by the order-preserving image of their keys.
+// The first violation raises a global flag; CTAs read the flag once per chunk and leave as soon as
+// it is up, so an unsorted input costs a few microseconds, not a pass.
+#pragma once
+#include "common.cuh"
+
+namespace b200 {
+
+constexpr int SC_THREADS = 256, SC_ITEMS = 4;
+
+struct SortedCheckParams {
+    const uint8_t* data;
+    uint64_t n_pairs;  // n - 1: pair i is (record i, record i + 1)
+    uint32_t* flag;    // zeroed before the launch; 1 = some pair is out of order
+    uint32_t elem_size;
+    uint32_t levels;
+    // word path: the key is an aligned little-endian word of W bytes at key_offset
+    uint32_t key_offset;
+    uint32_t is_float;
+    uint64_t flip;  // xor applied to the word (SINT: the sign bit; FLOAT non-negative: the sign bit)
+    uint64_t keep;  // the low `levels` bytes
+    // byte path: one digit per level, most significant level compared first
+    uint32_t sign_byte;
+    LevelLowering lv[MAX_LEVELS];
+};
+
+template <int W>
+__device__ __forceinline__ uint64_t sc_load_word(const uint8_t* p) {
+    if (W == 8) return *reinterpret_cast<const uint64_t*>(p);
+    if (W == 4) return *reinterpret_cast<const uint32_t*>(p);
+    if (W == 2) return *reinterpret_cast<const uint16_t*>(p);
+    return *p;
+}
+
+// Order-preserving unsigned image of the low `levels` bytes of the key word
+// (reference src/radix_key_impl.rs:3-46 unsigned, :87-160 signed, :162-185 floats).
+template <int W>
+__device__ __forceinline__ uint64_t sc_image(const SortedCheckParams& p, uint64_t i) {
+    uint64_t v = sc_load_word<W>(p.data + i * p.elem_size + p.key_offset);
+    if (p.is_float && ((v >> (8 * W - 1)) & 1ull))
+        v = ~v;
+    else
+        v ^= p.flip;
+    return v & p.keep;
+}
+
+// true when record a sorts strictly after record b (levels compared from the most significant down)
+__device__ __forceinline__ bool sc_greater_bytes(const SortedCheckParams& p, uint64_t ia, uint64_t ib) {
+    const uint8_t* a = p.data + ia * p.elem_size;
+    const uint8_t* b = p.data + ib * p.elem_size;
+    uint32_t na = 0, nb = 0;
+    if (p.is_float) {
+        na = (a[p.sign_byte] >> 7) ? 0xffu : 0u;
+        nb = (b[p.sign_byte] >> 7) ? 0xffu : 0u;
+    }
+    for (int l = int(p.levels) - 1; l >= 0; --l) {
+        const uint32_t off = p.lv[l].byte_offset, x = p.lv[l].xor_mask;
+        const uint32_t da = uint32_t(a[off]) ^ (na ? na : x);
+        const uint32_t db = uint32_t(b[off]) ^ (nb ? nb : x);
+        if (da != db) return da > db;
+    }
+    return false;
+}
+
+// W = key word bytes (1, 2, 4, 8) for the word path, 0 for the byte path
+template <int W>
+__global__ void __launch_bounds__(SC_THREADS) sorted_check_kernel(const SortedCheckParams p) {
+    constexpr uint64_t PER_ITER = uint64_t(SC_THREADS) * SC_ITEMS;
+    for (uint64_t base = uint64_t(blockIdx.x) * PER_ITER; base < p.n_pairs; base += uint64_t(gridDim.x) * PER_ITER) {
+        const uint32_t raised = *reinterpret_cast<volatile const uint32_t*>(p.flag);
+        bool bad = false;
+        if (W != 0) {
+            uint64_t a[SC_ITEMS], b[SC_ITEMS];
+#pragma unroll
+            for (int k = 0; k < SC_ITEMS; ++k) {
+                const uint64_t i = base + uint64_t(k) * SC_THREADS + threadIdx.x;
+                a[k] = b[k] = 0;
+                if (i < p.n_pairs) {
+                    a[k] = sc_image<(W ? W : 1)>(p, i);
+                    b[k] = sc_image<(W ? W : 1)>(p, i + 1);
+                }
+            }
+#pragma unroll
+            for (int k = 0; k < SC_ITEMS; ++k) bad |= a[k] > b[k];
+        } else {
+#pragma unroll 1
+            for (int k = 0; k < SC_ITEMS; ++k) {
+                const uint64_t i = base + uint64_t(k) * SC_THREADS + threadIdx.x;
+                if (i < p.n_pairs) bad |= sc_greater_bytes(p, i, i + 1);
+            }
+        }
+        if (bad) {
+            *reinterpret_cast<volatile uint32_t*>(p.flag) = 1u;
+            return;
+        }
+        if (raised) return;
+    }
+}
+
+}  // namespace b200
