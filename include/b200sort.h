@@ -101,7 +101,8 @@ typedef struct {
     float ms_h2d, ms_d2h;      /* host entry point only */
     float ms_total;            /* first launch to last completion */
     uint64_t tiles_per_pass;
-    uint32_t already_sorted;   /* reserved (rdst's already_sorted shortcut, src/sorter.rs:59-65) */
+    uint32_t already_sorted;   /* 1 = K0 found the input in key order and nothing else ran (rdst's
+                                  already_sorted shortcut, src/sort_utils.rs:125-136, src/sorter.rs:59-65) */
     uint32_t kernel_launches;  /* kernels of this library launched by the call */
     uint32_t hybrid;           /* 1 = MSD x2 + shared-memory segment sort (K3) ran instead of LSD passes */
     uint32_t slow_segments;    /* hybrid: segments whose fix-up fell back to a full local LSD */
