@@ -15,6 +15,7 @@
 #include <cuda_runtime.h>
 
 #include <algorithm>
+#include <chrono>
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
@@ -869,8 +870,8 @@ int sort_hybrid(DeviceCtx& c, cudaStream_t st, void* data, void* tmp, uint64_t n
 // through HBM, no scratch — which is what bounds the latency of small sorts.
 // ---------------------------------------------------------------------------
 bool small_sort_ok(const Lowered& lo, const void* data, uint64_t n, SplitParams* key) {
-    static const bool off = getenv("B200SORT_SMALL") && atoi(getenv("B200SORT_SMALL")) == 0;
-    if (off || hybrid_mode() == 0 || n > uint64_t(LS_CAP)) return false;
+    const char* env = getenv("B200SORT_SMALL");  // read per call: tests flip it
+    if ((env && atoi(env) == 0) || hybrid_mode() == 0 || n > uint64_t(LS_CAP)) return false;
     if (lo.elem_size != 4 && lo.elem_size != 8) return false;
     if (lo.levels > uint32_t(LS_MAXLEV) || !word_path_ok(lo, data, data)) return false;
     return lower_prefix(lo, key) == B200_OK;
@@ -906,11 +907,8 @@ int sort_small(DeviceCtx& c, cudaStream_t st, void* data, uint64_t n, const Lowe
 // reference src/sort_utils.rs:125-136 and src/sorter.rs:59-65.)
 // ---------------------------------------------------------------------------
 int sorted_check_mode() {  // B200SORT_SORTED_CHECK=0 switches the early-out off
-    static const int mode = [] {
-        const char* env = getenv("B200SORT_SORTED_CHECK");
-        return env ? atoi(env) : 1;
-    }();
-    return mode;
+    const char* env = getenv("B200SORT_SORTED_CHECK");  // read per call: tests flip it
+    return env ? atoi(env) : 1;
 }
 
 // Enqueues K0 over records [0, n) and the read-back of its flag into c.h_flag (no synchronisation).
@@ -937,7 +935,17 @@ int launch_sorted_check(DeviceCtx& c, cudaStream_t st, const Lowered& lo, const 
     CUDA_TRY(cudaMemsetAsync(d_flag, 0, 4, st));
     const uint64_t per_cta = uint64_t(SC_THREADS) * SC_ITEMS;
     const int grid = int(std::max<uint64_t>(1, std::min<uint64_t>(uint64_t(c.sm_count) * 8, (p.n_pairs + per_cta - 1) / per_cta)));
-    if (!word) sorted_check_kernel<0><<<grid, SC_THREADS, 0, st>>>(p);
+    // key-only arrays: the vectorised kernel (B200SORT_SORTED_CHECK=2 keeps the scalar one, for tests)
+    const bool vec = word && lo.elem_size == w && lo.key_offset == 0 && reinterpret_cast<uintptr_t>(data) % 16 == 0 &&
+                     sorted_check_mode() != 2;
+    if (vec) {
+        const uint64_t nvec = n * w / 16;
+        const int vgrid = int(std::max<uint64_t>(1, std::min<uint64_t>(uint64_t(c.sm_count) * 8, (nvec + per_cta - 1) / per_cta)));
+        if (w == 8) sorted_check_vec_kernel<8><<<vgrid, SC_THREADS, 0, st>>>(p, nvec);
+        else if (w == 4) sorted_check_vec_kernel<4><<<vgrid, SC_THREADS, 0, st>>>(p, nvec);
+        else if (w == 2) sorted_check_vec_kernel<2><<<vgrid, SC_THREADS, 0, st>>>(p, nvec);
+        else sorted_check_vec_kernel<1><<<vgrid, SC_THREADS, 0, st>>>(p, nvec);
+    } else if (!word) sorted_check_kernel<0><<<grid, SC_THREADS, 0, st>>>(p);
     else if (w == 8) sorted_check_kernel<8><<<grid, SC_THREADS, 0, st>>>(p);
     else if (w == 4) sorted_check_kernel<4><<<grid, SC_THREADS, 0, st>>>(p);
     else if (w == 2) sorted_check_kernel<2><<<grid, SC_THREADS, 0, st>>>(p);
@@ -1000,18 +1008,27 @@ int sort_device_impl(DeviceCtx& c, cudaStream_t st, void* data, void* tmp, uint6
         }
         return B200_OK;
     };
+    static const bool dbg = getenv("B200SORT_DEBUG_TIMING") != nullptr;
     if (check) {
         *c.h_flag = 1;
         rc = launch_sorted_check(c, st, lo, data, n);
         if (rc) return rc;
         if (n >= SORTED_SYNC_MIN) {
+            if (dbg) cudaEventRecord(c.ev[8], st);
+            const auto t0 = std::chrono::steady_clock::now();
             CUDA_TRY(cudaStreamSynchronize(st));
+            if (dbg) {
+                float k0 = 0;
+                cudaEventElapsedTime(&k0, c.ev[0], c.ev[8]);
+                const double wall = std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t0).count();
+                fprintf(stderr, "[b200sort] K0 (memset + kernel + flag D2H) %.3f ms on the device, host waited %.3f ms, sorted = %d\n",
+                        k0, wall, *c.h_flag == 0);
+            }
             if (*c.h_flag == 0) return sorted_return(1);
         }
     }
     rc = launch_histogram(c, st, lo, data, n, d_hist);
     if (rc) return rc;
-    static const bool dbg = getenv("B200SORT_DEBUG_TIMING") != nullptr;
     if (dbg) cudaEventRecord(c.ev[8], st);
     scan_hist_kernel<<<lo.levels, RADIX, 0, st>>>(d_hist, d_base);
     CUDA_TRY(cudaGetLastError());

@@ -567,6 +567,10 @@ def _hybrid_cases():
 def test_hybrid_path_matches_oracle(monkeypatch, name, dt, a, expect_hybrid):
     torch = torch_mod()
     monkeypatch.setenv("B200SORT_HYBRID", "1")
+    # the route under test is the hybrid one: no early-out for the presorted case, no single-launch
+    # path for the tiny one (tests/test_gpu_sorted_check.py and test_gpu_small_sort.py cover those)
+    monkeypatch.setenv("B200SORT_SORTED_CHECK", "0")
+    monkeypatch.setenv("B200SORT_SMALL", "0")
     key = RadixKey.for_dtype(dt)
     exp = o.sorted_copy(a, key)
     t = torch.from_numpy(np.ascontiguousarray(a).view(np.uint8).reshape(-1).copy()).cuda()

@@ -47,7 +47,7 @@ def test_presorted_primitives_return_early(dt):
     oracle; the GPU must recognise the order for every key transform."""
     rng = np.random.default_rng(500 + np.dtype(dt).num)
     key = RadixKey.for_dtype(dt)
-    for n in (2, 3, 1_025, 70_001):
+    for n in (2, 3, 1_025, 70_001, 70_002, 70_003, 131_072):
         a = o.sorted_copy(rand_bits(rng, dt, n), key)
         got, sh, sd = sort_both(a, key)
         assert got.tobytes() == a.tobytes()
@@ -58,16 +58,24 @@ def test_presorted_primitives_return_early(dt):
         assert sh["levels_run"] == 0 and sh["levels_skipped"] == key.levels
 
 
+@pytest.mark.parametrize("kernel", ["vector", "scalar"])
 @pytest.mark.parametrize("dt", ["u4", "i8", "f4", "f8"])
-def test_one_descending_pair_anywhere_takes_the_full_sort(dt):
+def test_one_descending_pair_anywhere_takes_the_full_sort(monkeypatch, dt, kernel):
     """Strictly increasing keys with exactly one adjacent swap at the positions where the check
-    kernel's thread / chunk / CTA boundaries fall."""
+    kernels' vector / lane / thread / chunk / CTA boundaries fall (B200SORT_SORTED_CHECK=2 keeps
+    key-only arrays on the scalar kernel that records with payload use)."""
+    if kernel == "scalar":
+        monkeypatch.setenv("B200SORT_SORTED_CHECK", "2")
     n = 1_300_000
     key = RadixKey.for_dtype(dt)
     base = (np.arange(n, dtype="i8") - n // 2) * 3
     base = base.astype(dt) if np.dtype(dt).kind != "u" else (base + 2 * n).astype(dt)
     assert o.is_sorted(base, key)
-    for pos in (0, 1, 255, 256, 1_023, 1_024, 1_025, 148 * 8 * 1_024 - 1, n // 2, n - 3, n - 2):
+    # 2^j - 1 and 2^j: the last / first key of every vector, warp, thread-step, chunk and grid stride of
+    # both check kernels (16-byte vectors of 2 or 4 keys, 32 lanes, 256 threads, 4 steps, <= 1184 CTAs)
+    marks = sorted({m for j in range(21) for m in ((1 << j) - 1, 1 << j)} |
+                   {148 * 8 * 1_024 - 1, 148 * 8 * 1_024, n // 2, n - 3, n - 2})
+    for pos in marks:
         if pos + 1 >= n:
             continue
         a = base.copy()
