@@ -370,7 +370,7 @@ int launch_pass(DeviceCtx& c, cudaStream_t st, const PassPlan& pp, const Lowered
 // ---- K1 dispatch (instantiations live in hist_w*.cu) ----
 // Fills d_hist [levels][256] (u64) on the stream.
 int launch_histogram(DeviceCtx& c, cudaStream_t st, const Lowered& lo, const void* src, uint64_t n,
-                     unsigned long long* d_hist) {
+                     unsigned long long* d_hist, const uint32_t* gate = nullptr) {
     CUDA_TRY(cudaMemsetAsync(d_hist, 0, size_t(lo.levels) * RADIX * 8, st));
     const bool aligned = reinterpret_cast<uintptr_t>(src) % 16 == 0;
     const uint32_t words = lo.elem_size / 4;
@@ -390,6 +390,7 @@ int launch_histogram(DeviceCtx& c, cudaStream_t st, const Lowered& lo, const voi
         for (uint32_t w = 0; w < 4; ++w) hp.xorw[w] = 0u;
         for (uint32_t l = 0; l < lo.levels && l < 16; ++l) hp.xorw[l / 4] |= (lo.lv[l].xor_mask & 0xffu) << (8 * (l % 4));
         hp.ghist = d_hist;
+        hp.gate = gate;
         const uint64_t per_thread = 8;
         const int grid =
             int(std::max<uint64_t>(1, std::min<uint64_t>(grid_full, (n + HIST_THREADS * per_thread - 1) /
@@ -414,6 +415,7 @@ int launch_histogram(DeviceCtx& c, cudaStream_t st, const Lowered& lo, const voi
     gp.is_float = lo.is_float ? 1u : 0u;
     gp.sign_byte = lo.sign_byte;
     gp.ghist = d_hist;
+    gp.gate = gate;
     for (uint32_t l = 0; l < MAX_LEVELS; ++l) gp.lv[l] = l < lo.levels ? lo.lv[l] : LevelLowering{0, 0};
     const size_t smem = size_t(lo.levels) * RADIX * 4;
     static bool attr_set = false;
@@ -986,49 +988,29 @@ int sort_device_impl(DeviceCtx& c, cudaStream_t st, void* data, void* tmp, uint6
         }
         return B200_OK;
     }
-    // K0, the already-sorted early-out.  Large inputs wait for its verdict before K1 (one extra
-    // synchronisation, microseconds against a sort of milliseconds; a presorted input then costs one
-    // read of the array); small inputs are latency bound, so K0 just rides in front of K1 and its flag
-    // comes back with the histograms.
-    constexpr uint64_t SORTED_SYNC_MIN = 4ull << 20;
+    // K0, the already-sorted early-out, rides in front of K1 on the same stream.  K1 is gated on K0's
+    // flag on the device (its CTAs leave at once when no pair was out of order), so a presorted input
+    // costs one read of the array and a random one pays no extra synchronisation: the flag comes back
+    // with the histograms.
     const bool check = sorted_check_mode() != 0 && n >= 2;
-    auto sorted_return = [&](uint32_t launches) -> int {
-        CUDA_TRY(cudaEventRecord(c.ev[1], st));
-        CUDA_TRY(cudaEventRecord(c.ev[2], st));
-        CUDA_TRY(cudaStreamSynchronize(st));
-        if (result_ptr) *result_ptr = data;
-        if (stats) {
-            stats->levels_run = 0;
-            stats->levels_skipped = lo.levels;
-            stats->already_sorted = 1;
-            stats->algorithmic_bytes = n * lo.elem_size;
-            stats->kernel_launches = launches;
-            CUDA_TRY(cudaEventElapsedTime(&stats->ms_hist, c.ev[0], c.ev[1]));
-            stats->ms_total = stats->ms_hist;
-        }
-        return B200_OK;
-    };
     static const bool dbg = getenv("B200SORT_DEBUG_TIMING") != nullptr;
     if (check) {
         *c.h_flag = 1;
         rc = launch_sorted_check(c, st, lo, data, n);
         if (rc) return rc;
-        if (n >= SORTED_SYNC_MIN) {
-            if (dbg) cudaEventRecord(c.ev[8], st);
-            const auto t0 = std::chrono::steady_clock::now();
-            CUDA_TRY(cudaStreamSynchronize(st));
-            if (dbg) {
-                float k0 = 0;
-                cudaEventElapsedTime(&k0, c.ev[0], c.ev[8]);
-                const double wall = std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t0).count();
-                fprintf(stderr, "[b200sort] K0 (memset + kernel + flag D2H) %.3f ms on the device, host waited %.3f ms, sorted = %d\n",
-                        k0, wall, *c.h_flag == 0);
-            }
-            if (*c.h_flag == 0) return sorted_return(1);
-        }
+        if (dbg) cudaEventRecord(c.ev[8], st);
     }
-    rc = launch_histogram(c, st, lo, data, n, d_hist);
+    rc = launch_histogram(c, st, lo, data, n, d_hist,
+                          check ? reinterpret_cast<const uint32_t*>(c.d_small + SMALL_FLAG_OFF) : nullptr);
     if (rc) return rc;
+    if (dbg && check) {
+        cudaEventRecord(c.ev[9], st);
+        cudaEventSynchronize(c.ev[9]);
+        float k0 = 0, k1 = 0;
+        cudaEventElapsedTime(&k0, c.ev[0], c.ev[8]);
+        cudaEventElapsedTime(&k1, c.ev[8], c.ev[9]);
+        fprintf(stderr, "[b200sort] K0 (memset + kernel + flag D2H) %.3f ms, K1 %.3f ms, sorted = %d\n", k0, k1, *c.h_flag == 0);
+    }
     if (dbg) cudaEventRecord(c.ev[8], st);
     scan_hist_kernel<<<lo.levels, RADIX, 0, st>>>(d_hist, d_base);
     CUDA_TRY(cudaGetLastError());
@@ -1044,7 +1026,21 @@ int sort_device_impl(DeviceCtx& c, cudaStream_t st, void* data, void* tmp, uint6
         fprintf(stderr, "[b200sort] memset+K1 %.3f ms, scan %.3f ms, D2H hist %.3f ms\n", a, b, d);
     }
 
-    if (check && n < SORTED_SYNC_MIN && *c.h_flag == 0) return sorted_return(3);
+    if (check && *c.h_flag == 0) {  // K0: no pair out of order; K1's CTAs left at once and nothing was counted
+        CUDA_TRY(cudaEventRecord(c.ev[2], st));
+        CUDA_TRY(cudaStreamSynchronize(st));
+        if (result_ptr) *result_ptr = data;
+        if (stats) {
+            stats->levels_run = 0;
+            stats->levels_skipped = lo.levels;
+            stats->already_sorted = 1;
+            stats->algorithmic_bytes = n * lo.elem_size;
+            stats->kernel_launches = 3;  // K0, the gated K1, scan
+            CUDA_TRY(cudaEventElapsedTime(&stats->ms_hist, c.ev[0], c.ev[1]));
+            stats->ms_total = stats->ms_hist;
+        }
+        return B200_OK;
+    }
 
     // levels with a single non-empty bucket are exact no-ops for a stable LSD sort
     std::vector<uint32_t> active;

@@ -21,6 +21,7 @@ struct HistParams {
     uint32_t sign_shift;     // FLOAT: bit of the sign inside the last key word
     uint32_t xorw[4];        // per-level xor masks packed as key words (byte l of the key ^= mask[l])
     unsigned long long* ghist;  // [L][256], zeroed before the launch
+    const uint32_t* gate;       // nullable: K0's out-of-order flag; 0 there = input already sorted, nothing to count
 };
 
 // Bank-rotated counting.  The CTA keeps 32 private 256-bin tables, table b living entirely
@@ -128,6 +129,7 @@ __global__ void __launch_bounds__(HIST_THREADS) hist_fast_kernel(const HistParam
     constexpr int NCOPY = HistRot<L>::NCOPY;
     constexpr bool PACKED = (WORDS == NKW) && (WORDS == 1 || WORDS == 2 || WORDS == 4);
     __shared__ uint32_t sh[32 * RADIX];
+    if (hp.gate && *hp.gate == 0) return;  // K0 ran in front on the same stream and found the input in order
     for (int i = threadIdx.x; i < 32 * RADIX; i += HIST_THREADS) sh[i] = 0;
     __syncthreads();
 
@@ -213,11 +215,13 @@ struct HistGenericParams {
     uint32_t elem_size, levels;
     uint32_t is_float, sign_byte;
     unsigned long long* ghist;
+    const uint32_t* gate;  // as HistParams::gate
     LevelLowering lv[MAX_LEVELS];
 };
 
 static __global__ void __launch_bounds__(HIST_THREADS) hist_generic_kernel(const HistGenericParams hp) {
     extern __shared__ uint32_t shg[];
+    if (hp.gate && *hp.gate == 0) return;
     for (uint32_t i = threadIdx.x; i < hp.levels * RADIX; i += HIST_THREADS) shg[i] = 0;
     __syncthreads();
     const uint64_t gstride = uint64_t(gridDim.x) * HIST_THREADS;

@@ -14,7 +14,7 @@ pytestmark = pytest.mark.gpu
 REC12 = np.dtype([("key", "<u4"), ("lo", "<u4"), ("hi", "<u4")])
 REC6 = np.dtype([("key", "<u2"), ("idx", "<u4")])  # odd stride: byte path of the check kernel
 LARGE = np.dtype([("a", "<u8"), ("b", "<u8"), ("sort_key", "<f4"), ("c", "<u4"), ("d", "<u8"), ("e", "<u8")])
-SYNC_MIN = 4 << 20  # inputs from this size on wait for K0's verdict before K1
+SYNC_MIN = 4 << 20
 SMALL_CAP = 16_384  # 4- and 8-byte records up to this many take the one-launch K3 path instead (no K0)
 
 
@@ -56,6 +56,13 @@ def test_presorted_primitives_return_early(dt):
             continue
         assert sh["already_sorted"] == 1 and sd["already_sorted"] == 1, (dt, n)
         assert sh["levels_run"] == 0 and sh["levels_skipped"] == key.levels
+        # the last pair (past the last full 16-byte vector for the odd lengths) out of order
+        b = a.copy()
+        b[n - 1], b[n - 2] = a[n - 2], a[n - 1]
+        if b.tobytes() != a.tobytes():
+            got, sh, sd = sort_both(b, key)
+            assert got.tobytes() == a.tobytes(), (dt, n)
+            assert sh["already_sorted"] == 0 and sd["already_sorted"] == 0, (dt, n)
 
 
 @pytest.mark.parametrize("kernel", ["vector", "scalar"])
@@ -147,8 +154,9 @@ def test_all_equal_and_negative_zero():
     assert got.tobytes() == np.concatenate([np.array([-0.0, 0.0], dtype="f4"), pad]).tobytes()
 
 
-def test_large_inputs_wait_for_the_verdict_before_k1():
-    """n >= 4 Mi: K0's flag is read before K1 is launched; a presorted input costs one launch."""
+def test_large_presorted_input_skips_k1_on_the_device():
+    """K1 is gated on K0's flag on the device: a presorted input costs one read of the array (K1's
+    CTAs leave at once), whatever its size; late, early and middle violations take the full sort."""
     import torch
 
     n = SYNC_MIN + 12_345
@@ -158,7 +166,7 @@ def test_large_inputs_wait_for_the_verdict_before_k1():
     b = radix_sort_builder(raw, RadixKey.for_dtype("i8"))
     b.sort()
     torch.cuda.synchronize()
-    assert b.stats["already_sorted"] == 1 and b.stats["kernel_launches"] == 1
+    assert b.stats["already_sorted"] == 1 and b.stats["levels_run"] == 0
     assert torch.equal(t, ref)
     for pos in (0, n // 3, n - 2):  # one late, one early and one middle violation
         t = ref.clone()
