@@ -104,7 +104,8 @@ typedef struct {
     uint32_t already_sorted;   /* 1 = K0 found the input in key order and nothing else ran (rdst's
                                   already_sorted shortcut, src/sort_utils.rs:125-136, src/sorter.rs:59-65) */
     uint32_t kernel_launches;  /* kernels of this library launched by the call */
-    uint32_t hybrid;           /* 1 = MSD x2 + shared-memory segment sort (K3) ran instead of LSD passes */
+    uint32_t hybrid;           /* 1 = MSD x2 + shared-memory segment sort (K3) ran instead of LSD passes;
+                                  2 = one MSD pass + K3 on its 256 buckets (mid-size inputs) */
     uint32_t slow_segments;    /* hybrid: segments whose fix-up fell back to a full local LSD */
     uint32_t local_levels;     /* hybrid: levels K3 sorted on chip (levels_run - 2) */
     float ms_joint;            /* hybrid: joint histogram of the two MSD levels + its read-back */

@@ -905,6 +905,84 @@ int sort_small(DeviceCtx& c, cudaStream_t st, void* data, uint64_t n, const Lowe
 }
 
 // ---------------------------------------------------------------------------
+// Mid-size inputs: ONE MSD pass on the top active level, then K3 on its 256 buckets.  This is rdst's
+// own default shape — split on the most significant byte, finish every bucket with an LSB sort that
+// runs in cache (reference src/sorter.rs:105-157, src/tuners/standard_tuner.rs:13-63,
+// src/sorts/lsb_sort.rs:38-128) — for inputs whose top-level buckets each fit one SM's shared
+// memory (<= 16 384 records, i.e. up to ~4 M uniform keys): K0, K1, scan, one K2 pass and one K3
+// launch instead of one K2 pass per level, each of which costs ~15 us of launch and look-back
+// latency at these sizes whatever the data.  The records end up sorted in `tmp`.
+// ---------------------------------------------------------------------------
+int sort_msd1(DeviceCtx& c, cudaStream_t st, void* data, void* tmp, uint64_t n, const Lowered& lo,
+              const std::vector<uint32_t>& active, const unsigned long long* d_base, uint32_t* d_ticket,
+              const PassPlan& pp, bool* done, uint32_t* local_levels) {
+    *done = false;
+    const char* env = getenv("B200SORT_MSD1");  // read per call: tests flip it
+    if ((env && atoi(env) == 0) || hybrid_mode() == 0) return B200_OK;
+    // measured (profiles/r3_k0_small_ladder.md): the MSD pass + K3 + copy back cost about as much as
+    // 3.7 LSD passes at latency-bound sizes, so five active levels always pay, four only from ~1 M records
+    if (active.size() < 4 || (active.size() == 4 && n < (1ull << 20))) return B200_OK;
+    if ((lo.elem_size != 4 && lo.elem_size != 8) || lo.levels > uint32_t(LS_MAXLEV) || !pp.word_path) return B200_OK;
+    if (!word_path_ok(lo, data, tmp)) return B200_OK;
+    SplitParams key;
+    if (lower_prefix(lo, &key) != B200_OK) return B200_OK;
+    const uint32_t top = active.back();
+    const uint64_t* h = c.h_hist + size_t(top) * RADIX;
+    uint64_t max_seg = 0, nonempty = 0, run = 0;
+    for (int b = 0; b < RADIX; ++b) {
+        c.h_joint[b] = run;
+        run += h[b];
+        max_seg = std::max(max_seg, h[b]);
+        nonempty += h[b] ? 1 : 0;
+    }
+    c.h_joint[RADIX] = run;
+    if (run != n || max_seg > uint64_t(LS_CAP)) return B200_OK;
+
+    int rc = ensure_bytes(reinterpret_cast<void**>(&c.d_hyb), &c.hyb_bytes, HYB_BYTES);
+    if (rc) return rc;
+    uint64_t* d_seg = reinterpret_cast<uint64_t*>(c.d_hyb + HYB_SEG_OFF);
+    uint32_t* d_tk = reinterpret_cast<uint32_t*>(c.d_hyb + HYB_TICKET_OFF);
+    const size_t lb_bytes = size_t(pp.num_tiles) * RADIX * 8;
+    rc = ensure_bytes(reinterpret_cast<void**>(&c.d_lookback), &c.lookback_bytes, lb_bytes);
+    if (rc) return rc;
+    CUDA_TRY(cudaMemsetAsync(c.d_lookback, 0, lb_bytes, st));
+    CUDA_TRY(cudaMemsetAsync(d_ticket, 0, 1024, st));
+    CUDA_TRY(cudaMemsetAsync(d_tk, 0, 4096, st));
+    CUDA_TRY(cudaMemcpyAsync(d_seg, c.h_joint, size_t(RADIX + 1) * 8, cudaMemcpyHostToDevice, st));
+    // ---- the MSD pass: data -> tmp, stable, on the top active level ----
+    rc = launch_pass(c, st, pp, lo, data, tmp, n, top, reinterpret_cast<const uint64_t*>(d_base + size_t(top) * RADIX),
+                     d_ticket, 1, nullptr);
+    if (rc) return rc;
+    // ---- K3: every bucket sorted on the remaining active levels, in place in tmp ----
+    LocalSortParams lp;
+    memset(&lp, 0, sizeof(lp));
+    lp.data = static_cast<uint32_t*>(tmp);
+    lp.seg_off = d_seg;
+    lp.nseg = RADIX;
+    lp.ticket = d_tk;
+    lp.nlev = uint32_t(active.size()) - 1;
+    for (uint32_t i = 0; i < lp.nlev; ++i) lp.lv[i] = window_params(lo, key, 8 * active[i], 8);
+    // fast levels as on the hybrid path: radix-sort the top one or two local levels, insertion-sort what
+    // is left of the runs; long runs (duplicates) switch a segment to the full local LSD inside K3
+    const double avg = double(n) / double(std::max<uint64_t>(1, nonempty));
+    uint32_t nfast = avg <= 64.0 ? 1 : 2;
+    if (nfast >= lp.nlev) nfast = 0;
+    const char* force = getenv("B200SORT_HYBRID_NFAST");
+    if (force) nfast = uint32_t(atoi(force)) < lp.nlev ? uint32_t(atoi(force)) : 0;
+    lp.nfast = nfast;
+    lp.fix_shift = nfast ? 8 * active[lp.nlev - nfast] : 0;
+    lp.key = key;
+    lp.slow_segments = d_tk + 300;
+    lp.prof = nullptr;
+    const int grid = int(std::min<uint64_t>(uint64_t(c.sm_count), std::max<uint64_t>(1, nonempty)));
+    rc = lo.elem_size == 4 ? launch_local_sort_w<1>(lo.is_float, grid, st, lp) : launch_local_sort_w<2>(lo.is_float, grid, st, lp);
+    if (rc) return rc;
+    *done = true;
+    *local_levels = lp.nlev;
+    return B200_OK;
+}
+
+// ---------------------------------------------------------------------------
 // K0: is the input already in key order?  (rdst's already_sorted shortcut,
 // reference src/sort_utils.rs:125-136 and src/sorter.rs:59-65.)
 // ---------------------------------------------------------------------------
@@ -1070,8 +1148,18 @@ int sort_device_impl(DeviceCtx& c, cudaStream_t st, void* data, void* tmp, uint6
         if (rc) return rc;
         if (!hybrid_done && where == tmp) std::swap(src, dst);  // MSD pass 1 ran: the records now live in tmp
     }
+    bool msd1_done = false;
+    uint32_t msd1_local = 0;
+    if (variant < 0 && !hybrid_done && src == data) {
+        rc = sort_msd1(c, st, data, tmp, n, lo, active, d_base, d_ticket, pp, &msd1_done, &msd1_local);
+        if (rc) return rc;
+        if (msd1_done) {
+            std::swap(src, dst);  // the sorted records are in tmp
+            hybrid_launches += 2;
+        }
+    }
     const uint32_t n_active = uint32_t(active.size());
-    if (hybrid_done) active.clear();  // nothing left for the LSD loop
+    if (hybrid_done || msd1_done) active.clear();  // nothing left for the LSD loop
     if (!active.empty()) {
         const size_t lb_bytes = size_t(pp.num_tiles) * RADIX * 8;
         rc = ensure_bytes(reinterpret_cast<void**>(&c.d_lookback), &c.lookback_bytes, lb_bytes);
@@ -1100,13 +1188,14 @@ int sort_device_impl(DeviceCtx& c, cudaStream_t st, void* data, void* tmp, uint6
     if (result_ptr) *result_ptr = src;
     CUDA_TRY(cudaEventRecord(c.ev[2], st));
     CUDA_TRY(cudaStreamSynchronize(st));
-    if (hybrid_done) pass = n_active;  // levels the result is sorted on
+    const uint32_t launches = 2 + pass + hybrid_launches + (check ? 1 : 0);  // (K0 +) K1 + scan + passes
+    if (hybrid_done || msd1_done) pass = n_active;  // levels the result is sorted on
     if (stats) {
         stats->levels_run = pass;
         stats->levels_skipped = lo.levels - pass;
-        stats->hybrid = hybrid_done ? 1u : 0u;
+        stats->hybrid = hybrid_done ? 1u : (msd1_done ? 2u : 0u);
         stats->slow_segments = slow_segments;
-        stats->local_levels = hybrid_done ? local_levels : 0;
+        stats->local_levels = hybrid_done ? local_levels : (msd1_done ? msd1_local : 0);
         stats->ms_joint = stats->ms_local = 0.0f;
         if (hybrid_done) {
             CUDA_TRY(cudaEventElapsedTime(&stats->ms_joint, c.ev[4], c.ev[5]));
@@ -1119,7 +1208,7 @@ int sort_device_impl(DeviceCtx& c, cudaStream_t st, void* data, void* tmp, uint6
         CUDA_TRY(cudaEventElapsedTime(&stats->ms_passes, c.ev[1], c.ev[2]));
         CUDA_TRY(cudaEventElapsedTime(&stats->ms_total, c.ev[0], c.ev[2]));
         stats->tiles_per_pass = pp.num_tiles;
-        stats->kernel_launches = (hybrid_done ? 2 + hybrid_launches : 2 + pass + hybrid_launches) + (check ? 1 : 0);  // (K0 +) K1 + scan + passes
+        stats->kernel_launches = launches;
     }
     return B200_OK;
 }
