@@ -1020,7 +1020,8 @@ int launch_sorted_check(DeviceCtx& c, cudaStream_t st, const Lowered& lo, const 
                      sorted_check_mode() != 2;
     if (vec) {
         const uint64_t nvec = n * w / 16;
-        const int vgrid = int(std::max<uint64_t>(1, std::min<uint64_t>(uint64_t(c.sm_count) * 8, (nvec + per_cta - 1) / per_cta)));
+        const uint64_t per_vcta = uint64_t(SC_THREADS) * SC_VEC_ITEMS;
+        const int vgrid = int(std::max<uint64_t>(1, std::min<uint64_t>(uint64_t(c.sm_count) * 8, (nvec + per_vcta - 1) / per_vcta)));
         if (w == 8) sorted_check_vec_kernel<8><<<vgrid, SC_THREADS, 0, st>>>(p, nvec);
         else if (w == 4) sorted_check_vec_kernel<4><<<vgrid, SC_THREADS, 0, st>>>(p, nvec);
         else if (w == 2) sorted_check_vec_kernel<2><<<vgrid, SC_THREADS, 0, st>>>(p, nvec);

@@ -17,7 +17,7 @@
 
 namespace b200 {
 
-constexpr int SC_THREADS = 256, SC_ITEMS = 4;
+constexpr int SC_THREADS = 256, SC_ITEMS = 4, SC_VEC_ITEMS = 4;
 
 struct SortedCheckParams {
     const uint8_t* data;
@@ -96,20 +96,24 @@ __device__ __forceinline__ bool sc_vec_chunk_bad(const SortedCheckParams& p, uin
     constexpr int K = 16 / W;
     const uint4* src = reinterpret_cast<const uint4*>(p.data);
     const int lane = threadIdx.x & 31;
-    uint4 v[SC_ITEMS];
-    uint64_t nxt[SC_ITEMS];
+    const uint64_t idx0 = base + threadIdx.x;
+    // all loads of the chunk in flight before the first compare (the kernel is latency bound; fetching
+    // lane 31's neighbour key lazily inside the compare loop serialised an L2 round trip per step:
+    // u64 3.7 -> 3.1 TB/s, profiles/r3_k0_small_ladder.md)
+    uint4 v[SC_VEC_ITEMS];
+    uint64_t nxt[SC_VEC_ITEMS];
 #pragma unroll
-    for (int k = 0; k < SC_ITEMS; ++k) {
-        const uint64_t idx = base + uint64_t(k) * SC_THREADS + threadIdx.x;
+    for (int k = 0; k < SC_VEC_ITEMS; ++k) {
+        const uint64_t idx = idx0 + uint64_t(k) * SC_THREADS;
         v[k] = make_uint4(0, 0, 0, 0);
         nxt[k] = 0;
         if (idx < nvec) v[k] = ldg_stream(src + idx);
-        if (lane == 31 && idx + 1 < nvec) nxt[k] = sc_image<W>(p, (idx + 1) * K);
+        if (lane == 31 && idx + 1 < nvec) nxt[k] = sc_image<W>(p, (idx + 1) * K);  // the next warp's first key
     }
     bool bad = false;
 #pragma unroll
-    for (int k = 0; k < SC_ITEMS; ++k) {
-        const uint64_t idx = base + uint64_t(k) * SC_THREADS + threadIdx.x;
+    for (int k = 0; k < SC_VEC_ITEMS; ++k) {
+        const uint64_t idx = idx0 + uint64_t(k) * SC_THREADS;
         uint64_t img[K];
 #pragma unroll
         for (int j = 0; j < K; ++j) img[j] = sc_xform<W>(p, sc_unpack<W>(v[k], j));
@@ -125,7 +129,7 @@ __device__ __forceinline__ bool sc_vec_chunk_bad(const SortedCheckParams& p, uin
 template <int W>
 __global__ void __launch_bounds__(SC_THREADS) sorted_check_vec_kernel(const SortedCheckParams p, uint64_t nvec) {
     constexpr int K = 16 / W;
-    constexpr uint64_t PER_ITER = uint64_t(SC_THREADS) * SC_ITEMS;
+    constexpr uint64_t PER_ITER = uint64_t(SC_THREADS) * SC_VEC_ITEMS;
     if (__syncthreads_or(sc_vec_chunk_bad<W>(p, nvec, 0))) {  // the probe
         if (blockIdx.x == 0 && threadIdx.x == 0) *reinterpret_cast<volatile uint32_t*>(p.flag) = 1u;
         return;
