@@ -96,7 +96,6 @@ __device__ __forceinline__ bool sc_vec_chunk_bad(const SortedCheckParams& p, uin
     constexpr int K = 16 / W;
     const uint4* src = reinterpret_cast<const uint4*>(p.data);
     const int lane = threadIdx.x & 31;
-    const uint64_t idx0 = base + threadIdx.x;
     // all loads of the chunk in flight before the first compare (the kernel is latency bound; fetching
     // lane 31's neighbour key lazily inside the compare loop serialised an L2 round trip per step:
     // u64 3.7 -> 3.1 TB/s, profiles/r3_k0_small_ladder.md)
@@ -104,7 +103,7 @@ __device__ __forceinline__ bool sc_vec_chunk_bad(const SortedCheckParams& p, uin
     uint64_t nxt[SC_VEC_ITEMS];
 #pragma unroll
     for (int k = 0; k < SC_VEC_ITEMS; ++k) {
-        const uint64_t idx = idx0 + uint64_t(k) * SC_THREADS;
+        const uint64_t idx = base + uint64_t(k) * SC_THREADS + threadIdx.x;
         v[k] = make_uint4(0, 0, 0, 0);
         nxt[k] = 0;
         if (idx < nvec) v[k] = ldg_stream(src + idx);
@@ -113,7 +112,7 @@ __device__ __forceinline__ bool sc_vec_chunk_bad(const SortedCheckParams& p, uin
     bool bad = false;
 #pragma unroll
     for (int k = 0; k < SC_VEC_ITEMS; ++k) {
-        const uint64_t idx = idx0 + uint64_t(k) * SC_THREADS;
+        const uint64_t idx = base + uint64_t(k) * SC_THREADS + threadIdx.x;
         uint64_t img[K];
 #pragma unroll
         for (int j = 0; j < K; ++j) img[j] = sc_xform<W>(p, sc_unpack<W>(v[k], j));
