@@ -247,6 +247,31 @@ typedef struct b200_window_plan {
 } b200_window_plan;
 int b200_hybrid_plan(const b200_key_desc* desc, const uint64_t* hist, size_t n, b200_window_plan* out);
 
+/*
+ * Planner introspection (host only, no GPU): the route b200_sort_device starts on for `n` records
+ * with these per-level histograms, given 16-byte aligned buffers and variant = auto — the GPU
+ * meaning of Tuner::pick_algorithm (src/tuner.rs:33-35; the reference's own rules:
+ * src/tuners/standard_tuner.rs:13-63, size cut-offs src/sorter.rs:33-45).  `hist` may be NULL when
+ * the answer does not need it (n <= 1, the small-input path).  The already-sorted early-out (K0) is
+ * decided on the data, not here; the hybrid route may still fall back to LSD passes after its joint
+ * histogram if a segment does not fit one SM.
+ */
+typedef enum {
+    B200_ROUTE_LSD = 0,     /* one K2 pass per active level */
+    B200_ROUTE_HYBRID = 1,  /* two MSD passes + K3 (b200_hybrid_plan gives the digits) */
+    B200_ROUTE_MSD1 = 2,    /* one MSD pass on the top active level + K3 on its 256 buckets */
+    B200_ROUTE_SMALL = 3,   /* one K3 launch, the whole array as one segment */
+    B200_ROUTE_TRIVIAL = 4  /* n <= 1: nothing runs (src/radix_sort_builder.rs:151) */
+} b200_route_kind;
+typedef struct b200_route {
+    uint32_t route;          /* b200_route_kind */
+    uint32_t active_levels;  /* levels whose histogram has more than one non-empty bucket */
+    uint32_t levels_run;     /* what b200_stats.levels_run reports for this route */
+    uint32_t msd_level;      /* MSD1: the level of the MSD pass */
+    uint64_t max_bucket;     /* MSD1: the largest bucket of that level (<= 16384) */
+} b200_route;
+int b200_route_plan(const b200_key_desc* desc, const uint64_t* hist, size_t n, b200_route* out);
+
 /* Tuner introspection: the Tuner now only picks a tile/occupancy variant. */
 int b200_variant_count(void);
 const char* b200_variant_name(int variant);

@@ -95,6 +95,21 @@ LIB_PATH = os.path.join(os.path.dirname(os.path.abspath(__file__)), "libb200sort
 _lib = None
 
 # name -> (restype, argtypes): every symbol include/b200sort.h declares
+class Route(C.Structure):
+    """b200_route (include/b200sort.h): the route the planner starts on."""
+
+    _fields_ = [
+        ("route", C.c_uint32),
+        ("active_levels", C.c_uint32),
+        ("levels_run", C.c_uint32),
+        ("msd_level", C.c_uint32),
+        ("max_bucket", C.c_uint64),
+    ]
+
+
+ROUTE_NAMES = {0: "lsd", 1: "hybrid", 2: "msd1", 3: "small", 4: "trivial"}
+
+
 class WindowPlan(C.Structure):
     """b200_window_plan (include/b200sort.h): the digits the hybrid route would sort on."""
 
@@ -178,6 +193,7 @@ SYMBOLS = {
     "b200_host_free": (C.c_int, [C.c_void_p]),
     "b200_release_scratch": (C.c_int, [C.c_int]),
     "b200_hybrid_plan": (C.c_int, [C.POINTER(KeyDesc), C.POINTER(C.c_uint64), C.c_size_t, C.POINTER(WindowPlan)]),
+    "b200_route_plan": (C.c_int, [C.POINTER(KeyDesc), C.POINTER(C.c_uint64), C.c_size_t, C.POINTER(Route)]),
     "b200_variant_count": (C.c_int, []),
     "b200_variant_name": (C.c_char_p, [C.c_int]),
     "b200_strerror": (C.c_char_p, [C.c_int]),

@@ -871,12 +871,15 @@ int sort_hybrid(DeviceCtx& c, cudaStream_t st, void* data, void* tmp, uint64_t n
 // fits one SM's shared memory is sorted by ONE launch — no histogram, no read-back, no passes
 // through HBM, no scratch — which is what bounds the latency of small sorts.
 // ---------------------------------------------------------------------------
-bool small_sort_ok(const Lowered& lo, const void* data, uint64_t n, SplitParams* key) {
+bool small_shape_ok(const Lowered& lo, uint64_t n, SplitParams* key) {  // host-only part of the rule (b200_route_plan)
     const char* env = getenv("B200SORT_SMALL");  // read per call: tests flip it
     if ((env && atoi(env) == 0) || hybrid_mode() == 0 || n > uint64_t(LS_CAP)) return false;
     if (lo.elem_size != 4 && lo.elem_size != 8) return false;
-    if (lo.levels > uint32_t(LS_MAXLEV) || !word_path_ok(lo, data, data)) return false;
+    if (lo.levels > uint32_t(LS_MAXLEV)) return false;
     return lower_prefix(lo, key) == B200_OK;
+}
+bool small_sort_ok(const Lowered& lo, const void* data, uint64_t n, SplitParams* key) {
+    return small_shape_ok(lo, n, key) && word_path_ok(lo, data, data);
 }
 
 int sort_small(DeviceCtx& c, cudaStream_t st, void* data, uint64_t n, const Lowered& lo, const SplitParams& key) {
@@ -913,30 +916,46 @@ int sort_small(DeviceCtx& c, cudaStream_t st, void* data, uint64_t n, const Lowe
 // launch instead of one K2 pass per level, each of which costs ~15 us of launch and look-back
 // latency at these sizes whatever the data.  The records end up sorted in `tmp`.
 // ---------------------------------------------------------------------------
+// The host-only part of the rule: key shape, active levels and the bucket sizes of the MSD level.
+bool msd1_shape_ok(const Lowered& lo, uint64_t n, const uint64_t* hist, const std::vector<uint32_t>& active,
+                   SplitParams* key, uint64_t* max_seg_out, uint64_t* nonempty_out) {
+    const char* env = getenv("B200SORT_MSD1");  // read per call: tests flip it
+    if ((env && atoi(env) == 0) || hybrid_mode() == 0) return false;
+    // measured (profiles/r3_k0_small_ladder.md): the MSD pass + K3 + copy back cost about as much as
+    // 3.7 LSD passes at latency-bound sizes, so five active levels always pay, four only from ~1 M records
+    if (active.size() < 4 || (active.size() == 4 && n < (1ull << 20))) return false;
+    if ((lo.elem_size != 4 && lo.elem_size != 8) || lo.levels > uint32_t(LS_MAXLEV)) return false;
+    if (lower_prefix(lo, key) != B200_OK) return false;
+    const uint64_t* h = hist + size_t(active.back()) * RADIX;
+    uint64_t max_seg = 0, nonempty = 0, total = 0;
+    for (int b = 0; b < RADIX; ++b) {
+        total += h[b];
+        max_seg = std::max(max_seg, h[b]);
+        nonempty += h[b] ? 1 : 0;
+    }
+    *max_seg_out = max_seg;
+    *nonempty_out = nonempty;
+    return total == n && max_seg <= uint64_t(LS_CAP);
+}
+
 int sort_msd1(DeviceCtx& c, cudaStream_t st, void* data, void* tmp, uint64_t n, const Lowered& lo,
               const std::vector<uint32_t>& active, const unsigned long long* d_base, uint32_t* d_ticket,
               const PassPlan& pp, bool* done, uint32_t* local_levels) {
     *done = false;
-    const char* env = getenv("B200SORT_MSD1");  // read per call: tests flip it
-    if ((env && atoi(env) == 0) || hybrid_mode() == 0) return B200_OK;
-    // measured (profiles/r3_k0_small_ladder.md): the MSD pass + K3 + copy back cost about as much as
-    // 3.7 LSD passes at latency-bound sizes, so five active levels always pay, four only from ~1 M records
-    if (active.size() < 4 || (active.size() == 4 && n < (1ull << 20))) return B200_OK;
-    if ((lo.elem_size != 4 && lo.elem_size != 8) || lo.levels > uint32_t(LS_MAXLEV) || !pp.word_path) return B200_OK;
-    if (!word_path_ok(lo, data, tmp)) return B200_OK;
     SplitParams key;
-    if (lower_prefix(lo, &key) != B200_OK) return B200_OK;
+    uint64_t max_seg = 0, nonempty = 0;
+    if (!msd1_shape_ok(lo, n, c.h_hist, active, &key, &max_seg, &nonempty)) return B200_OK;
+    if (!pp.word_path || !word_path_ok(lo, data, tmp)) return B200_OK;
     const uint32_t top = active.back();
-    const uint64_t* h = c.h_hist + size_t(top) * RADIX;
-    uint64_t max_seg = 0, nonempty = 0, run = 0;
-    for (int b = 0; b < RADIX; ++b) {
-        c.h_joint[b] = run;
-        run += h[b];
-        max_seg = std::max(max_seg, h[b]);
-        nonempty += h[b] ? 1 : 0;
+    {
+        const uint64_t* h = c.h_hist + size_t(top) * RADIX;
+        uint64_t run = 0;
+        for (int b = 0; b < RADIX; ++b) {
+            c.h_joint[b] = run;
+            run += h[b];
+        }
+        c.h_joint[RADIX] = run;
     }
-    c.h_joint[RADIX] = run;
-    if (run != n || max_seg > uint64_t(LS_CAP)) return B200_OK;
 
     int rc = ensure_bytes(reinterpret_cast<void**>(&c.d_hyb), &c.hyb_bytes, HYB_BYTES);
     if (rc) return rc;
@@ -1718,6 +1737,65 @@ int b200_hybrid_plan(const b200_key_desc* desc, const uint64_t* hist, size_t n, 
     out->digit_lo[1] = wp.w2_lo, out->digit_width[1] = wp.w2_width;
     out->nlocal = wp.nlocal;
     for (uint32_t i = 0; i < wp.nlocal; ++i) out->local_lo[i] = wp.local_lo[i], out->local_width[i] = wp.local_width[i];
+    return B200_OK;
+}
+
+int b200_route_plan(const b200_key_desc* desc, const uint64_t* hist, size_t n, b200_route* out) {
+    Lowered lo;
+    int rc = lower_desc(desc, &lo);
+    if (rc) return rc;
+    if (!out) return B200_ERR_BAD_ARG;
+    memset(out, 0, sizeof(*out));
+    if (n <= 1) {  // reference src/radix_sort_builder.rs:151
+        out->route = B200_ROUTE_TRIVIAL;
+        return B200_OK;
+    }
+    SplitParams key;
+    if (small_shape_ok(lo, n, &key)) {
+        out->route = B200_ROUTE_SMALL;
+        out->active_levels = out->levels_run = lo.levels;  // no histogram is taken: every declared level is sorted
+        return B200_OK;
+    }
+    if (!hist) return B200_ERR_BAD_ARG;
+    std::vector<uint32_t> active;
+    for (uint32_t l = 0; l < lo.levels; ++l) {
+        bool single = false;
+        for (int b = 0; b < RADIX; ++b)
+            if (hist[size_t(l) * RADIX + b] == n) single = true;
+        if (!single) active.push_back(l);
+    }
+    out->active_levels = out->levels_run = uint32_t(active.size());
+    out->route = B200_ROUTE_LSD;
+    if (active.empty()) return B200_OK;
+    // hybrid: the checks sort_hybrid makes before its first launch
+    const int mode = hybrid_mode();
+    const uint32_t words = lo.elem_size / 4;
+    if (mode != 0 && active.size() >= 3 && lo.elem_size % 4 == 0 && (words == 1 || words == 2) && lo.levels <= 8 &&
+        uint64_t(n) < (1ull << 32) && lower_prefix(lo, &key) == B200_OK &&
+        !(mode == 2 && (active.size() < 5 || uint64_t(n) < (256ull << 20)))) {
+        WindowPlan wp;
+        if (plan_windows(lo, hist, n, &wp)) {
+            bool ok = true;
+            if (wp.aligned && mode == 2) {  // segments expected to fit an SM (independence estimate)
+                uint64_t m1 = 0, m2 = 0;
+                for (int b = 0; b < RADIX; ++b) {
+                    m1 = std::max(m1, hist[size_t(wp.w1_lo / 8) * RADIX + b]);
+                    m2 = std::max(m2, hist[size_t(wp.w2_lo / 8) * RADIX + b]);
+                }
+                ok = double(m1) * double(m2) / double(n) <= 0.97 * LS_CAP;
+            }
+            if (ok) {
+                out->route = B200_ROUTE_HYBRID;
+                return B200_OK;
+            }
+        }
+    }
+    uint64_t max_seg = 0, nonempty = 0;
+    if (msd1_shape_ok(lo, n, hist, active, &key, &max_seg, &nonempty)) {
+        out->route = B200_ROUTE_MSD1;
+        out->msd_level = active.back();
+        out->max_bucket = max_seg;
+    }
     return B200_OK;
 }
 
