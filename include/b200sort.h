@@ -110,6 +110,11 @@ typedef struct {
     uint32_t local_levels;     /* hybrid: levels K3 sorted on chip (levels_run - 2) */
     float ms_joint;            /* hybrid: joint histogram of the two MSD levels + its read-back */
     float ms_local;            /* hybrid: K3 (shared-memory segment sort), CUDA events */
+    uint32_t unstable;         /* hybrid, records that are nothing but their key (every byte a level): bit 0 = the
+                                  unstable flavour ran (K3-U segment sort; equal keys are identical records, so the
+                                  result is bit-identical to the stable engine's — rdst's default entry point is
+                                  radix_sort_unstable, src/radix_sort.rs:21-45), bit 1 / bit 2 = MSD pass 1 / 2 ran
+                                  the atomic-ranking kernel K2-U (flat digits only) */
 } b200_stats;
 
 /*

@@ -72,6 +72,7 @@ class Stats(C.Structure):
         ("local_levels", C.c_uint32),
         ("ms_joint", C.c_float),
         ("ms_local", C.c_float),
+        ("unstable", C.c_uint32),
     ]
 
     def as_dict(self):

@@ -30,6 +30,8 @@
 #include "launch.h"
 #include "onesweep.cuh"
 #include "variants.h"
+#include "unstable.h"
+#include "local_count.cuh"
 
 using namespace b200;
 
@@ -151,6 +153,8 @@ struct DeviceCtx {
     void* h_bounce[2] = {nullptr, nullptr};  // pinned bounce buffers for pageable host memory
     size_t bounce_bytes = 0;
     cudaEvent_t bounce_ev[2] = {};
+    uint32_t* d_slow = nullptr;  // hybrid key-only route: segments K3-U left to the stable K3 ([0] = count)
+    size_t slow_bytes = 0;
 };
 
 constexpr size_t SMALL_HIST_OFF = 0;
@@ -594,13 +598,43 @@ int launch_hist_win_w(bool floatk, int grid, cudaStream_t st, const HistWinParam
     return B200_OK;
 }
 
+// ---- the unstable (key-only) flavour of the hybrid route: K2-U + K3-U (pass_atomic.cuh, local_count.cuh) ----
+// A record that is nothing but its key (every byte is a level) may be permuted freely among equal
+// MSD digits — rdst's default entry point is radix_sort_UNSTABLE and its MSB algorithms do exactly
+// that (reference src/radix_sort.rs:21-45, src/sorts/ska_sort.rs, regions_sort.rs) — and equal keys
+// are identical records, so the result is still bit-identical to the stable engine's.
+bool key_only_record(const Lowered& lo) {
+    const char* env = getenv("B200SORT_UNSTABLE");  // read per call: tests flip it
+    const bool off = env && atoi(env) == 0;
+    return !off && lo.contiguous && lo.key_offset == 0 && lo.levels == lo.elem_size && lo.key_width == lo.elem_size;
+}
+// same-address shared-memory atomics serialise: digits with a bucket above 1/8 of the records stay on the
+// stable pass kernel (ballot path for hot buckets)
+bool digit_is_flat(const uint64_t* hist, uint64_t n) {
+    uint64_t m = 0;
+    for (int b = 0; b < RADIX; ++b) m = std::max(m, hist[b]);
+    return m <= n / 8;
+}
+uint64_t hybrid_min_records(bool key_only) {
+    const char* env = getenv("B200SORT_HYBRID_MIN");
+    if (env) return strtoull(env, nullptr, 10);
+    // stable route: K3 holds one segment per SM at a time, so small segments leave it idle; the unstable
+    // route has the small-segment flavour of K3-U (several CTAs per SM)
+    return key_only ? (8ull << 20) : (256ull << 20);
+}
+MsdULaunch get_msdu_launch(uint32_t words, bool floatk) {
+    const int v = getenv("B200SORT_MSDU_VARIANT") ? atoi(getenv("B200SORT_MSDU_VARIANT")) : 0;  // read per call
+    const int vv = (v >= 0 && v < NUM_MSDU_VARIANTS) ? v : 0;
+    return words == 1 ? get_msdu_launch_w1(floatk, vv) : get_msdu_launch_w2(floatk, vv);
+}
+
 // Returns B200_OK with *done = true when the array was sorted here (result in `data`);
 // *done = false means "not eligible / segments too large": the caller runs the LSD passes.
 // *src_out tells the caller where the (possibly re-partitioned) records are.
 int sort_hybrid(DeviceCtx& c, cudaStream_t st, void* data, void* tmp, uint64_t n, const Lowered& lo,
                 const std::vector<uint32_t>& active, const unsigned long long* d_base, uint32_t* d_ticket, bool* done,
                 void** src_out, uint32_t* launches, uint32_t* slow_segments, uint32_t* local_levels,
-                bool copy_back_counts) {
+                uint32_t* unstable_out) {
     *done = false;
     *src_out = data;
     const int mode = hybrid_mode();
@@ -610,13 +644,12 @@ int sort_hybrid(DeviceCtx& c, cudaStream_t st, void* data, void* tmp, uint64_t n
     if (!word_path_ok(lo, data, tmp) || n >= (1ull << 32)) return B200_OK;
     SplitParams key;
     if (lower_prefix(lo, &key) != B200_OK) return B200_OK;
-    // worth it from 256 M records and five active levels on: the hybrid costs about as much as 4.5 LSD
-    // passes whatever the key width (1 B u64: 22.7 ms against 1.4 + 4.77 ms per level, and an odd number
-    // of LSD passes ends with a 2.5 ms copy back); K3 handles one segment per SM at a time, so segments
-    // below a few thousand records leave it idle, and with four active levels K3's two local levels cost
-    // more than the two K2 passes they replace
-    (void)copy_back_counts;
-    if (mode == 2 && (active.size() < 5 || n < (256ull << 20))) return B200_OK;
+    const bool key_only = key_only_record(lo);
+    // stable route: worth it from 256 M records and five active levels on (it costs about as much as 4.5
+    // LSD passes whatever the key width, and K3 handles one segment per SM at a time).  Unstable route:
+    // cheaper passes and a segment sort that keeps the SMs busy on small segments, so it pays from four
+    // active levels and a few million records on.
+    if (mode == 2 && (active.size() < (key_only ? 4u : 5u) || n < hybrid_min_records(key_only))) return B200_OK;
 
     // ---- the digits: bit windows over the varying bits of the key image (plan_windows) ----
     // keys that do not fill their type — or one rank's range of a sharded sort — still split 65 536 ways
@@ -684,32 +717,49 @@ int sort_hybrid(DeviceCtx& c, cudaStream_t st, void* data, void* tmp, uint64_t n
         if (double(m1) * double(m2) / double(n) > 0.97 * LS_CAP) return B200_OK;
     }
 
-    // ---- MSD pass 1: data -> tmp on the first digit ----
+    // ---- the pass kernels: stable K2 (SEG instantiation) or, for key-only records, K2-U ----
     PassPlan pp{};
     rc = plan_pass(c, lo, n, data, tmp, false, -1, &pp);
     if (rc) return rc;
-    const uint64_t tiles1 = pp.num_tiles;
-    // look-back words: pass 1 needs tiles1 rows; pass 2 at most n / small_tile + 256 rows
-    const uint64_t small_tile = 4096;
-    const size_t lb_rows = size_t(std::max<uint64_t>(tiles1, n / small_tile + 2 * RADIX + 1));
+    PassPlan ps = pp;  // stable, segmented (also the instantiation that reads bit windows)
+    ps.pl = get_pass_launch(words, lo.is_float, false, pp.variant, false, true);
+    if (!ps.pl.kernel || !ps.pl.seg || ps.pl.tile != int(pp.tile)) {
+        g_last_cuda_error = "hybrid: no segmented instantiation of the pass kernel for this variant";
+        return B200_ERR_CUDA;
+    }
+    PassPlan pu = pp;  // unstable
+    if (key_only) {
+        const MsdULaunch ul = get_msdu_launch(words, lo.is_float);
+        pu.pl = PassLaunch{ul.kernel, ul.smem, ul.tile, ul.threads, false, true};
+        pu.tile = uint32_t(ul.tile);
+    }
+    auto occupancy = [&](const PassPlan& q, int* occ) -> int {
+        CUDA_TRY(cudaFuncSetAttribute(q.pl.kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, int(q.pl.smem)));
+        CUDA_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(occ, q.pl.kernel, q.pl.threads, q.pl.smem));
+        *occ = std::max(*occ, 1);
+        return B200_OK;
+    };
+    const bool u1 = key_only && digit_is_flat(hw, n), u2 = key_only && digit_is_flat(hw + RADIX, n);
+    const PassPlan& k1 = u1 ? pu : ps;
+    const PassPlan& k2 = u2 ? pu : ps;
+    int occ1 = 1, occ2 = 1;
+    rc = occupancy(k1, &occ1);
+    if (rc) return rc;
+    rc = occupancy(k2, &occ2);
+    if (rc) return rc;
+    const uint64_t tiles1 = (n + k1.tile - 1) / k1.tile;
+    // look-back rows: pass 1 needs tiles1; pass 2 at most n / tile + 256
+    const uint64_t min_tile = std::min<uint64_t>(std::min(k1.tile, k2.tile), 4096);
+    const size_t lb_rows = size_t(std::max<uint64_t>(tiles1, n / min_tile + 2 * RADIX + 1));
     rc = ensure_bytes(reinterpret_cast<void**>(&c.d_lookback), &c.lookback_bytes, lb_rows * RADIX * 8);
     if (rc) return rc;
     CUDA_TRY(cudaMemsetAsync(c.d_lookback, 0, size_t(tiles1) * RADIX * 8, st));
     CUDA_TRY(cudaMemsetAsync(d_ticket, 0, 1024, st));
     CUDA_TRY(cudaMemsetAsync(c.d_hyb, 0, HYB_SEG_OFF, st));
     CUDA_TRY(cudaMemsetAsync(d_tk, 0, 4096, st));
-    // the segmented instantiation of the pass kernel (it is also the one that reads bit windows)
-    PassPlan ps = pp;
-    ps.pl = get_pass_launch(words, lo.is_float, false, pp.variant, false, true);
-    if (!ps.pl.kernel || !ps.pl.seg || ps.pl.tile != int(pp.tile)) {
-        g_last_cuda_error = "hybrid: no segmented instantiation of the pass kernel for this variant";
-        return B200_ERR_CUDA;
-    }
-    CUDA_TRY(cudaFuncSetAttribute(ps.pl.kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, int(ps.pl.smem)));
-    int occ_seg = 0;
-    CUDA_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ_seg, ps.pl.kernel, ps.pl.threads, ps.pl.smem));
-    occ_seg = std::max(occ_seg, 1);
-    if (aligned) {
+
+    // ---- MSD pass 1: data -> tmp on the first digit ----
+    if (aligned && !u1) {
         rc = launch_pass(c, st, pp, lo, data, tmp, n, A1, reinterpret_cast<const uint64_t*>(d_base + size_t(A1) * RADIX),
                          d_ticket, 1, nullptr);
     } else {
@@ -726,8 +776,9 @@ int sort_hybrid(DeviceCtx& c, cudaStream_t st, void* data, void* tmp, uint64_t n
         CUDA_TRY(cudaMemcpyAsync(d_ts, h_ts, sizeof(h_ts), cudaMemcpyHostToDevice, st));
         CUDA_TRY(cudaMemcpyAsync(d_rs, h_rs, sizeof(h_rs), cudaMemcpyHostToDevice, st));
         CUDA_TRY(cudaMemcpyAsync(d_b1, h_b1, sizeof(h_b1), cudaMemcpyHostToDevice, st));
-        PassPlan p1 = ps;
-        p1.grid = int(std::min<uint64_t>(tiles1, uint64_t(c.sm_count) * occ_seg));
+        PassPlan p1 = k1;
+        p1.num_tiles = uint32_t(tiles1);
+        p1.grid = int(std::min<uint64_t>(tiles1, uint64_t(c.sm_count) * occ1));
         rc = launch_pass(c, st, p1, lo, data, tmp, n, 0, d_b1, d_ticket, 1, nullptr, nullptr, nullptr, nullptr, 0, nullptr,
                          d_ts, d_rs, d_b1, &W1);
     }
@@ -781,7 +832,7 @@ int sort_hybrid(DeviceCtx& c, cudaStream_t st, void* data, void* tmp, uint64_t n
         for (int b1 = 0; b1 < RADIX; ++b1) {
             h_tile_start[b1] = uint32_t(t);
             h_rec_start[b1] = rsum;
-            t += (h1[b1] + pp.tile - 1) / pp.tile;
+            t += (h1[b1] + k2.tile - 1) / k2.tile;
             rsum += h1[b1];
         }
         h_tile_start[RADIX] = uint32_t(t);
@@ -796,10 +847,9 @@ int sort_hybrid(DeviceCtx& c, cudaStream_t st, void* data, void* tmp, uint64_t n
     CUDA_TRY(cudaMemcpyAsync(d_tile_start, h_tile_start, sizeof(h_tile_start), cudaMemcpyHostToDevice, st));
     CUDA_TRY(cudaMemcpyAsync(d_rec_start, h_rec_start, sizeof(h_rec_start), cudaMemcpyHostToDevice, st));
     CUDA_TRY(cudaMemsetAsync(c.d_lookback, 0, size_t(h_tile_start[RADIX]) * RADIX * 8, st));
-    PassPlan p2 = ps;
+    PassPlan p2 = k2;
     p2.num_tiles = h_tile_start[RADIX];
-    p2.grid = int(std::min<uint64_t>(p2.num_tiles, uint64_t(c.sm_count) * occ_seg));
-    const int k = 1;
+    p2.grid = int(std::min<uint64_t>(p2.num_tiles, uint64_t(c.sm_count) * occ2));
     rc = launch_pass(c, st, p2, lo, tmp, data, n, 0, d_seg, d_tk + 1, 1, nullptr, nullptr, nullptr, nullptr, 0, nullptr,
                      d_tile_start, d_rec_start, d_seg, &W2);
     if (rc) return rc;
@@ -814,25 +864,81 @@ int sort_hybrid(DeviceCtx& c, cudaStream_t st, void* data, void* tmp, uint64_t n
     lp.ticket = d_tk;
     lp.nlev = nlocal;
     for (uint32_t i = 0; i < lp.nlev; ++i) lp.lv[i] = local[i];
-    // fast levels: as many of the top local levels as make runs of equal prefixes rare
-    const double avg = double(n) / double(std::max<uint64_t>(1, nonempty));
-    uint32_t nfast = avg <= 64.0 ? 1 : 2;
-    if (max_seg > 4096 * 4) nfast = 2;
-    if (nfast >= lp.nlev) nfast = 0;  // nothing would be left for the fix-up: plain LSD over all local levels
-    const char* force_slow = getenv("B200SORT_HYBRID_NFAST");
-    if (force_slow) nfast = uint32_t(atoi(force_slow)) < lp.nlev ? uint32_t(atoi(force_slow)) : 0;
-    lp.nfast = nfast;
-    lp.fix_shift = nfast ? local_lo[lp.nlev - nfast] : 0;
     lp.key = key;
     lp.slow_segments = d_tk + 300;
-    static const bool k3prof = getenv("B200SORT_K3_PROFILE") != nullptr;
-    lp.prof = k3prof ? reinterpret_cast<unsigned long long*>(d_tk + 320) : nullptr;
-    const int lgrid = int(std::min<uint64_t>(uint64_t(c.sm_count), nonempty ? nonempty : 1));
-    rc = words == 1 ? launch_local_sort_w<1>(lo.is_float, lgrid, st, lp) : launch_local_sort_w<2>(lo.is_float, lgrid, st, lp);
-    if (rc) return rc;
-    *launches += 1;
-    if (slow_segments) {
-        CUDA_TRY(cudaMemcpyAsync(slow_segments, d_tk + 300, 4, cudaMemcpyDeviceToHost, st));
+    uint32_t nfast = 0;
+    if (key_only) {
+        // K3-U: one wide counting-sort level + comparison fix-up fused into the write-out; segments it cannot
+        // finish (a long run of unequal keys inside one counter) go to the stable K3 in list mode
+        const uint32_t slow_bytes = (RADIX * RADIX + 1) * 4;
+        rc = ensure_bytes(reinterpret_cast<void**>(&c.d_slow), &c.slow_bytes, slow_bytes);
+        if (rc) return rc;
+        CUDA_TRY(cudaMemsetAsync(c.d_slow, 0, 4, st));
+        const int force_size = getenv("B200SORT_K3U_SIZE") ? atoi(getenv("B200SORT_K3U_SIZE")) : -1;  // read per call: tests flip it
+        bool small = max_seg <= 4096;
+        if (force_size == 0) small = false;
+        const LocalCountLaunch ll = words == 1 ? get_local_count_launch_w1(lo.is_float, small) : get_local_count_launch_w2(lo.is_float, small);
+        LocalCountParams cp;
+        memset(&cp, 0, sizeof(cp));
+        cp.data = static_cast<uint32_t*>(data);
+        cp.seg_off = d_seg;
+        cp.nseg = RADIX * RADIX;
+        cp.ticket = d_tk + 2;
+        cp.key = key;
+        // the digit starts at the highest bit below D2 that varies at all (plan_windows guarantees there is one)
+        cp.top_bit = 64u - uint32_t(__builtin_clzll(wp.vary & ((1ull << w2_lo) - 1ull)));
+        const int bmax_env = getenv("B200SORT_K3U_BMAX") ? atoi(getenv("B200SORT_K3U_BMAX")) : 0;
+        cp.bmax = uint32_t(bmax_env > 0 ? std::min(bmax_env, ll.cbits) : ll.cbits);
+        cp.slow_list = c.d_slow;
+        CUDA_TRY(cudaFuncSetAttribute(ll.kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, int(ll.smem)));
+        int occ = 1;
+        CUDA_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, ll.kernel, ll.threads, ll.smem));
+        occ = std::max(occ, 1);
+        const int ugrid = int(std::min<uint64_t>(uint64_t(c.sm_count) * occ, nonempty ? nonempty : 1));
+        ll.kernel<<<ugrid, ll.threads, ll.smem, st>>>(cp);
+        CUDA_TRY(cudaGetLastError());
+        *launches += 1;
+        // the leftovers: full stable LSD over every local level, segments from the list
+        lp.list = c.d_slow;
+        lp.nfast = 0;
+        lp.fix_shift = 0;
+        lp.prof = nullptr;
+        const int lgrid = int(std::min<uint64_t>(uint64_t(c.sm_count), nonempty ? nonempty : 1));
+        rc = words == 1 ? launch_local_sort_w<1>(lo.is_float, lgrid, st, lp) : launch_local_sort_w<2>(lo.is_float, lgrid, st, lp);
+        if (rc) return rc;
+        *launches += 1;
+        if (slow_segments) CUDA_TRY(cudaMemcpyAsync(slow_segments, c.d_slow, 4, cudaMemcpyDeviceToHost, st));
+        if (unstable_out) *unstable_out = 1u | (u1 ? 2u : 0u) | (u2 ? 4u : 0u);
+    } else {
+        // fast levels: as many of the top local levels as make runs of equal prefixes rare
+        const double avg = double(n) / double(std::max<uint64_t>(1, nonempty));
+        nfast = avg <= 64.0 ? 1 : 2;
+        if (max_seg > 4096 * 4) nfast = 2;
+        if (nfast >= lp.nlev) nfast = 0;  // nothing would be left for the fix-up: plain LSD over all local levels
+        const char* force_slow = getenv("B200SORT_HYBRID_NFAST");
+        if (force_slow) nfast = uint32_t(atoi(force_slow)) < lp.nlev ? uint32_t(atoi(force_slow)) : 0;
+        lp.nfast = nfast;
+        lp.fix_shift = nfast ? local_lo[lp.nlev - nfast] : 0;
+        static const bool k3prof = getenv("B200SORT_K3_PROFILE") != nullptr;
+        lp.prof = k3prof ? reinterpret_cast<unsigned long long*>(d_tk + 320) : nullptr;
+        const int lgrid = int(std::min<uint64_t>(uint64_t(c.sm_count), nonempty ? nonempty : 1));
+        rc = words == 1 ? launch_local_sort_w<1>(lo.is_float, lgrid, st, lp) : launch_local_sort_w<2>(lo.is_float, lgrid, st, lp);
+        if (rc) return rc;
+        *launches += 1;
+        if (slow_segments) {
+            CUDA_TRY(cudaMemcpyAsync(slow_segments, d_tk + 300, 4, cudaMemcpyDeviceToHost, st));
+        }
+        if (k3prof) {
+            unsigned long long h[8];
+            cudaMemcpyAsync(h, d_tk + 320, sizeof(h), cudaMemcpyDeviceToHost, st);
+            cudaStreamSynchronize(st);
+            double tot = 0;
+            for (int i = 0; i < 8; ++i) tot += double(h[i]);
+            fprintf(stderr, "[b200sort] K3 cycles of thread 0, share per phase: wait/claim %.1f%% rank %.1f%% digit scan %.1f%% scatter %.1f%% "
+                            "read-back %.1f%% fix-up heads %.1f%% fix-up runs %.1f%% prefetch+write-out %.1f%% (%.0f cycles per segment)\n",
+                    100 * h[0] / tot, 100 * h[1] / tot, 100 * h[2] / tot, 100 * h[3] / tot, 100 * h[4] / tot, 100 * h[5] / tot,
+                    100 * h[6] / tot, 100 * h[7] / tot, tot / double(std::max<uint64_t>(1, nonempty)));
+        }
     }
     cudaEventRecord(c.ev[7], st);
     if (dbg) {
@@ -842,21 +948,11 @@ int sort_hybrid(DeviceCtx& c, cudaStream_t st, void* data, void* tmp, uint64_t n
         cudaEventElapsedTime(&b, c.ev[4], c.ev[5]);
         cudaEventElapsedTime(&d, c.ev[5], c.ev[6]);
         cudaEventElapsedTime(&e, c.ev[6], c.ev[7]);
-        fprintf(stderr, "[b200sort] hybrid: MSD pass 1 %.3f ms, joint hist + D2H %.3f ms, MSD pass 2 (%d launches) %.3f ms, K3 %.3f ms"
+        fprintf(stderr, "[b200sort] hybrid%s: MSD pass 1%s %.3f ms, joint hist + D2H %.3f ms, MSD pass 2%s %.3f ms, K3%s %.3f ms"
                         " (max segment %llu, nfast %u of %u local levels; digits: bits %u..%u, %u..%u%s)\n",
-                a, b, k, d, e, (unsigned long long)max_seg, nfast, lp.nlev, w1_lo, w1_lo + 7, w2_lo, w2_lo + w2_width - 1,
+                key_only ? " (key-only)" : "", u1 ? " (K2-U)" : "", a, b, u2 ? " (K2-U)" : "", d, key_only ? "-U" : "", e,
+                (unsigned long long)max_seg, nfast, lp.nlev, w1_lo, w1_lo + 7, w2_lo, w2_lo + w2_width - 1,
                 aligned ? "" : ", window histogram pass");
-    }
-    if (k3prof) {
-        unsigned long long h[8];
-        cudaMemcpyAsync(h, d_tk + 320, sizeof(h), cudaMemcpyDeviceToHost, st);
-        cudaStreamSynchronize(st);
-        double tot = 0;
-        for (int i = 0; i < 8; ++i) tot += double(h[i]);
-        fprintf(stderr, "[b200sort] K3 cycles of thread 0, share per phase: wait/claim %.1f%% rank %.1f%% digit scan %.1f%% scatter %.1f%% "
-                        "read-back %.1f%% fix-up heads %.1f%% fix-up runs %.1f%% prefetch+write-out %.1f%% (%.0f cycles per segment)\n",
-                100 * h[0] / tot, 100 * h[1] / tot, 100 * h[2] / tot, 100 * h[3] / tot, 100 * h[4] / tot, 100 * h[5] / tot,
-                100 * h[6] / tot, 100 * h[7] / tot, tot / double(std::max<uint64_t>(1, nonempty)));
     }
     *done = true;
     *src_out = data;
@@ -1160,11 +1256,11 @@ int sort_device_impl(DeviceCtx& c, cudaStream_t st, void* data, void* tmp, uint6
     // the Tuner's algorithm choice on the GPU: MSD x2 + on-chip segment sort for large inputs whose
     // segments fit an SM, LSD passes otherwise (an explicit variant request always means LSD passes)
     bool hybrid_done = false;
-    uint32_t hybrid_launches = 0, slow_segments = 0, local_levels = 0;
+    uint32_t hybrid_launches = 0, slow_segments = 0, local_levels = 0, unstable = 0;
     if (variant < 0) {
         void* where = data;
         rc = sort_hybrid(c, st, data, tmp, n, lo, active, d_base, d_ticket, &hybrid_done, &where, &hybrid_launches,
-                         &slow_segments, &local_levels, !result_anywhere);
+                         &slow_segments, &local_levels, &unstable);
         if (rc) return rc;
         if (!hybrid_done && where == tmp) std::swap(src, dst);  // MSD pass 1 ran: the records now live in tmp
     }
@@ -1214,6 +1310,7 @@ int sort_device_impl(DeviceCtx& c, cudaStream_t st, void* data, void* tmp, uint6
         stats->levels_run = pass;
         stats->levels_skipped = lo.levels - pass;
         stats->hybrid = hybrid_done ? 1u : (msd1_done ? 2u : 0u);
+        stats->unstable = hybrid_done ? unstable : 0u;
         stats->slow_segments = slow_segments;
         stats->local_levels = hybrid_done ? local_levels : (msd1_done ? msd1_local : 0);
         stats->ms_joint = stats->ms_local = 0.0f;
@@ -1772,7 +1869,7 @@ int b200_route_plan(const b200_key_desc* desc, const uint64_t* hist, size_t n, b
     const uint32_t words = lo.elem_size / 4;
     if (mode != 0 && active.size() >= 3 && lo.elem_size % 4 == 0 && (words == 1 || words == 2) && lo.levels <= 8 &&
         uint64_t(n) < (1ull << 32) && lower_prefix(lo, &key) == B200_OK &&
-        !(mode == 2 && (active.size() < 5 || uint64_t(n) < (256ull << 20)))) {
+        !(mode == 2 && (active.size() < (key_only_record(lo) ? 4u : 5u) || uint64_t(n) < hybrid_min_records(key_only_record(lo))))) {
         WindowPlan wp;
         if (plan_windows(lo, hist, n, &wp)) {
             bool ok = true;

@@ -35,6 +35,8 @@ struct LocalSortParams {
     SplitParams key;           // 64-bit order-preserving image of the whole key (LEVELS <= 8)
     uint32_t* slow_segments;   // telemetry: segments that fell back to the full LSD
     unsigned long long* prof;  // optional [8] cycle counters per phase (thread 0 of every CTA), nullptr = off
+    const uint32_t* list;      // list mode (nullptr = off): sort segments list[1 .. list[0]] only — the ones K3-U
+                               // (local_count.cuh) left behind; the count is read on the device, no host round trip
 };
 
 template <int WORDS>
@@ -76,9 +78,11 @@ __global__ void __launch_bounds__(LS_THREADS, 1) local_sort_kernel(const LocalSo
     uint32_t cnt = 0, IT = 0, e0 = 0;
     uint32_t* g = nullptr;
     Rec<WORDS> r[ITEMS];
+    const uint32_t nseg = p.list ? min(__ldg(p.list), p.nseg) : p.nseg;
     auto fetch = [&](uint32_t sg) {  // header + records of segment sg (nothing for cnt <= 1)
         cnt = 0;
-        if (sg >= p.nseg) return;
+        if (sg >= nseg) return;
+        if (p.list) sg = __ldg(p.list + 1 + sg);
         const uint64_t base = p.seg_off[sg];
         cnt = uint32_t(p.seg_off[sg + 1] - base);
         g = p.data + base * WORDS;
@@ -110,7 +114,7 @@ __global__ void __launch_bounds__(LS_THREADS, 1) local_sort_kernel(const LocalSo
     __syncthreads();
     uint32_t seg = s_seg[0];
     fetch(seg);
-    while (seg < p.nseg) {
+    while (seg < nseg) {
         if (tid == 0) {
             s_seg[3] = atomicAdd(p.ticket, 1u);  // the segment after this one
             s_seg[1] = 0;

@@ -1,0 +1,58 @@
+// unstable_inst.cuh — instantiates K2-U and K3-U for one record width; included by unstable_w{1,2}.cu.
+#pragma once
+#include "local_count.cuh"
+#include "pass_atomic.cuh"
+#include "unstable.h"
+
+namespace b200 {
+
+template <int WORDS, bool FLOATK, int THREADS, int ITEMS, int MINB>
+static MsdULaunch make_msdu(const char* name) {
+    using SM = AtomSmem<WORDS, THREADS, ITEMS>;
+    MsdULaunch l{};
+    l.kernel = &msd_pass_atomic_kernel<WORDS, THREADS, ITEMS, FLOATK, MINB>;
+    l.smem = SM::TOTAL;
+    l.tile = SM::TILE;
+    l.threads = THREADS;
+    l.name = name;
+    return l;
+}
+
+template <int WORDS, bool FLOATK>
+static MsdULaunch pick_msdu(int variant) {
+    if constexpr (WORDS == 1) {
+        switch (variant) {
+            case 0: return make_msdu<WORDS, FLOATK, 256, 32, 4>("u256_i32_occ4");
+            case 1: return make_msdu<WORDS, FLOATK, 256, 48, 2>("u256_i48_occ2");
+            case 2: return make_msdu<WORDS, FLOATK, 512, 24, 2>("u512_i24_occ2");
+            case 3: return make_msdu<WORDS, FLOATK, 256, 16, 5>("u256_i16_occ5");
+        }
+    } else {
+        switch (variant) {
+            case 0: return make_msdu<WORDS, FLOATK, 256, 32, 2>("u256_i32_occ2");
+            case 1: return make_msdu<WORDS, FLOATK, 256, 24, 3>("u256_i24_occ3");
+            case 2: return make_msdu<WORDS, FLOATK, 512, 16, 2>("u512_i16_occ2");
+            case 3: return make_msdu<WORDS, FLOATK, 256, 16, 4>("u256_i16_occ4");
+        }
+    }
+    return MsdULaunch{};
+}
+
+template <int WORDS, bool FLOATK, int THREADS, int CBITS, int MINB>
+static LocalCountLaunch make_local_count() {
+    using SM = LocalCountSmem<WORDS, THREADS, CBITS>;
+    LocalCountLaunch l{};
+    l.kernel = &local_count_kernel<WORDS, FLOATK, THREADS, CBITS, MINB>;
+    l.smem = SM::TOTAL;
+    l.threads = THREADS;
+    l.cap = SM::CAP;
+    l.cbits = CBITS;
+    return l;
+}
+
+template <int WORDS, bool FLOATK>
+static LocalCountLaunch pick_local_count(bool small) {
+    return small ? make_local_count<WORDS, FLOATK, 128, 13, 4>() : make_local_count<WORDS, FLOATK, 512, 15, 1>();
+}
+
+}  // namespace b200

@@ -1,0 +1,10 @@
+// K2-U / K3-U instantiations for 1-word records (split per width so the widths compile in parallel).
+#include "unstable_inst.cuh"
+namespace b200 {
+MsdULaunch get_msdu_launch_w1(bool floatk, int variant) {
+    return floatk ? pick_msdu<1, true>(variant) : pick_msdu<1, false>(variant);
+}
+LocalCountLaunch get_local_count_launch_w1(bool floatk, bool small) {
+    return floatk ? pick_local_count<1, true>(small) : pick_local_count<1, false>(small);
+}
+}  // namespace b200

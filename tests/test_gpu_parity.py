@@ -561,12 +561,24 @@ def _hybrid_cases():
     yield "u64_sorted", "u8", np.sort(rng.integers(0, 2**64, n, dtype="u8")), True
     yield "u64_reverse", "u8", np.sort(rng.integers(0, 2**64, n, dtype="u8"))[::-1].copy(), True
     yield "u64_tiny", "u8", rng.integers(0, 2**64, 1000, dtype="u8"), True
+    # key-only route: two counters of K3-U's wide digit hold ~2.9 k UNEQUAL keys each -> the segment goes to the
+    # slow list and the stable segment sort finishes it
+    yield "u64_slow_list", "u8", top | (rng.integers(0, 2, n, dtype="u8") << np.uint64(40)) | rng.integers(0, 256, n, dtype="u8"), True
+    # heavy duplicates inside big segments: long runs of EQUAL keys need no fix-up (warp check)
+    yield "u64_big_segments_few_values", "u8", top | (rng.integers(0, 3, n, dtype="u8") * np.uint64(0x0000051234567891)), True
+    yield "u32_big_segments", "u4", ((rng.integers(0, 16, n, dtype="u4") << np.uint32(28)) | (rng.integers(0, 16, n, dtype="u4") << np.uint32(20))
+                                     | rng.integers(0, 2**16, n, dtype="u4")), True
 
 
+@pytest.mark.parametrize("unstable", [1, 0], ids=["key_only_route", "stable_route"])
 @pytest.mark.parametrize("name,dt,a,expect_hybrid", list(_hybrid_cases()), ids=[c[0] for c in _hybrid_cases()])
-def test_hybrid_path_matches_oracle(monkeypatch, name, dt, a, expect_hybrid):
+def test_hybrid_path_matches_oracle(monkeypatch, name, dt, a, expect_hybrid, unstable):
+    """Every case is a key-only array, so it runs twice: through the unstable flavour of the route (K2-U atomic
+    ranking + K3-U wide-digit segment sort, the default for key-only records) and through the stable one
+    (B200SORT_UNSTABLE=0: what records with a payload take).  Both must equal the oracle bit for bit."""
     torch = torch_mod()
     monkeypatch.setenv("B200SORT_HYBRID", "1")
+    monkeypatch.setenv("B200SORT_UNSTABLE", str(unstable))
     # the route under test is the hybrid one: no early-out for the presorted case, no single-launch
     # path for the tiny one (tests/test_gpu_sorted_check.py and test_gpu_small_sort.py cover those)
     monkeypatch.setenv("B200SORT_SORTED_CHECK", "0")
@@ -580,18 +592,27 @@ def test_hybrid_path_matches_oracle(monkeypatch, name, dt, a, expect_hybrid):
     assert t.cpu().numpy().tobytes() == exp.tobytes(), name
     if expect_hybrid is not None:
         assert bool(b.stats["hybrid"]) == expect_hybrid, (name, b.stats)
-    if name == "u64_dups":
-        assert b.stats["slow_segments"] > 0
+    if b.stats["hybrid"]:
+        assert bool(b.stats["unstable"] & 1) == bool(unstable), b.stats
+    if name == ("u64_slow_list" if unstable else "u64_dups"):
+        assert b.stats["slow_segments"] > 0, b.stats
+    if unstable and name in ("u64_dups", "u64_big_segments_few_values"):
+        assert b.stats["slow_segments"] == 0, b.stats  # long runs of equal keys are not a reason to fall back
     # the host entry point takes the same route
     h = a.copy()
     radix_sort_unstable(h)
     assert h.tobytes() == exp.tobytes(), name
-    # and both fast-level settings of K3 agree (nfast = 1 leaves more to the insertion fix-up)
-    monkeypatch.setenv("B200SORT_HYBRID_NFAST", "1")
+    if unstable:
+        # the other size of K3-U (512 threads, one CTA per SM) and a narrow digit (long comparison runs)
+        monkeypatch.setenv("B200SORT_K3U_SIZE", "0")
+        monkeypatch.setenv("B200SORT_K3U_BMAX", "9")
+    else:
+        # both fast-level settings of K3 agree (nfast = 1 leaves more to the insertion fix-up)
+        monkeypatch.setenv("B200SORT_HYBRID_NFAST", "1")
     t2 = torch.from_numpy(np.ascontiguousarray(a).view(np.uint8).reshape(-1).copy()).cuda()
     radix_sort_builder(t2, key).sort()
     torch.cuda.synchronize()
-    assert t2.cpu().numpy().tobytes() == exp.tobytes(), name + " nfast=1"
+    assert t2.cpu().numpy().tobytes() == exp.tobytes(), name + " second setting"
 
 
 def test_hybrid_is_stable_for_key_plus_payload_of_one_word():
