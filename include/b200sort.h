@@ -78,15 +78,34 @@ typedef struct {
  * Options — what RadixSortBuilder carries (src/radix_sort_builder.rs:8-12)
  * re-expressed for the device engine.
  */
+/* What a Tuner's answer means on the device (src/tuner.rs:10-35: Algorithm; src/sorter.rs:67-76: where it is
+ * asked).  rdst's nine algorithms are CPU strategies; on the GPU they collapse to the choices below, each
+ * visible in b200_stats. */
+typedef enum {
+    B200_HINT_AUTO = 0,        /* the planner decides (Scanning / Recombinating / MtOop / Comparative and no tuner:
+                                  hybrid MSD route when the input qualifies, LSD passes otherwise) */
+    B200_HINT_LSD = 1,         /* one stable K2 pass per active level, nothing else (Lsb / LrLsb / MtLsb: rdst's
+                                  stable LSB family, src/sorts/lsb_sort.rs:5-7): b200_stats.hybrid == 0 */
+    B200_HINT_LOW_SCRATCH = 2  /* Ska / Regions and with_low_mem_tuner() (rdst's in-place family,
+                                  src/tuners/low_memory_tuner.rs:13-43): LSD passes with the small-tile variant and
+                                  the library's cached scratch pool (n * elem_size + look-back rows) is released
+                                  before the call returns.  PEAK scratch is still one copy of the array: the
+                                  engine has no in-place pass. */
+} b200_route_hint;
+
 typedef struct {
-    uint32_t stable;   /* 1 = rdst's stable order (Lsb/LrLsb/MtLsb, src/sorts/lsb_sort.rs:5-7).
-                          0 = any sorted permutation is legal (default tuner). The engine is a
-                          stable LSD sort either way; the flag is recorded for the tuner. */
-    int32_t variant;   /* < 0 = let the tuner pick (-2: prefer the low-scratch variant);
-                          else index < b200_variant_count() */
+    uint32_t stable;   /* 1 = rdst's stable order (Lsb/LrLsb/MtLsb, src/sorts/lsb_sort.rs:5-7): records with a
+                          payload keep their input order among equal keys.  0 = any sorted permutation is legal
+                          (radix_sort_unstable, src/radix_sort.rs:21-45).  Records with a payload are sorted
+                          stably either way; records that are nothing but their key take the unstable kernels
+                          (b200_stats.unstable) whose result is bit-identical. */
+    int32_t variant;   /* < 0 = let the planner pick the tile / occupancy variant of the pass kernel;
+                          else index < b200_variant_count() (forces LSD passes) */
     int32_t device;    /* CUDA device ordinal; -1 = current device */
     void* stream;      /* cudaStream_t to order the work on; NULL = the library's own (blocking) stream,
                           which is ordered against the legacy default stream */
+    uint32_t route;    /* b200_route_hint */
+    uint32_t _reserved;
 } b200_sort_opts;
 
 typedef struct {
@@ -218,6 +237,70 @@ int b200_ipc_alloc(void** dev_ptr, size_t bytes, void* handle_out);
 int b200_ipc_open(const void* handle, void** dev_ptr);
 int b200_ipc_close(void* dev_ptr);
 int b200_ipc_free(void* dev_ptr);
+
+/*
+ * The sharded sort behind the C ABI: ONE process drives `ngpus` GPUs of one box (one host thread and one stream
+ * per GPU, peer access between the devices), SURVEY.md §8e / BASELINE.json configs[4].  The reference has no
+ * counterpart (RadixSortBuilder::sort takes one `&mut [T]`, src/radix_sort_builder.rs:149-157); this is the entry a
+ * Rust binding calls for inputs larger than one GPU or for 8-GPU mode.  Steps: K1 per shard, histograms merged on
+ * the host, partition level = most significant non-trivial level, P-1 splitters (digit boundaries, or sample-sort
+ * splitters on the 64-bit key prefix when one digit outweighs a rank's share), fused partition + exchange (every
+ * GPU's K2 range-partition pass stores its runs straight into the owners' receive buffers over NVLink), then an
+ * independent local sort per GPU.  Stable.  Records of 4, 8, 12 or 16 bytes.
+ * `devices` = NULL means devices 0 .. ngpus-1.
+ */
+#define B200_MAX_GPUS 16
+typedef struct {
+    uint32_t ngpus;
+    uint32_t level;          /* partition level (0xffffffff: every key equal, nothing moved) */
+    uint32_t splitter_mode;  /* 0 = digit boundaries, 1 = sample-sort splitters on the key prefix */
+    uint32_t kernel_launches;
+    double imbalance;        /* max records any GPU received / the even share */
+    uint64_t max_sent_bytes; /* largest number of bytes one GPU sent to its peers */
+    uint64_t n_out[B200_MAX_GPUS];
+    float ms_plan;           /* K1 + host planning (+ sampling / counting in splitter mode), host clock */
+    float ms_exchange;       /* fused partition + exchange, host clock between the two fences */
+    float ms_local_sort;
+    float ms_h2d, ms_d2h;    /* host entry point only */
+    float ms_total;
+    b200_stats local0;       /* GPU 0's local sort */
+} b200_multi_stats;
+
+/* Shard g = n_in[g] records in DEVICE memory of devices[g] at dev_ptrs[g] (read only).  On return GPU g holds the
+ * g-th key range, sorted: n_out[g] records at out_ptrs[g], a library-owned buffer on devices[g] that stays valid
+ * until the next multi-GPU call or b200_multi_release().  Concatenating the outputs in GPU order gives the sorted
+ * array. */
+int b200_sort_multi_device(void* const* dev_ptrs, const size_t* n_in, int ngpus, const int* devices,
+                           const b200_key_desc* desc, const b200_sort_opts* opts, void** out_ptrs, size_t* n_out,
+                           b200_multi_stats* stats);
+/* `n` records in HOST memory, sorted in place over `ngpus` GPUs: the array is cut into ngpus contiguous shards, every
+ * GPU pulls its shard over its own PCIe link, and GPU g's sorted range is written back behind the ranges of the
+ * lower GPUs.  The multi-GPU form of b200_sort_host. */
+int b200_sort_multi_host(void* host_ptr, size_t n, int ngpus, const int* devices, const b200_key_desc* desc,
+                         const b200_sort_opts* opts, b200_multi_stats* stats);
+int b200_multi_release(void);
+
+/* The host-side exchange planner (no GPU), shared by b200_sort_multi_* and the one-process-per-GPU driver
+ * (rdst_b200/dist.py).  all_hist = [ranks][levels][256] K1 histograms.  level_out = -1: every key equal.
+ * split_out[ranks - 1] digit boundaries (part g = digits in [split[g-1], split[g])), send_matrix_out[ranks][ranks]
+ * (m[r][g] = records rank r sends to rank g). */
+int b200_multi_plan_digits(const uint64_t* all_hist, uint32_t ranks, uint32_t levels, int32_t* level_out,
+                           uint32_t* split_out, int64_t* send_matrix_out, double* imbalance_out);
+/* parts - 1 splitter prefixes = weighted quantiles of the gathered key-prefix samples */
+int b200_multi_choose_sample_splitters(const uint64_t* samples, const double* weights, size_t count, uint32_t parts,
+                                       uint64_t* splitters_out);
+/* less / equal = [ranks][parts - 1] counts from b200_splitter_count_device.  tie_thresholds_out[parts - 1]: boundary b
+ * sends a record LEFT when prefix < s_b, or prefix == s_b and source rank < t_b; send_matrix_out[ranks][parts];
+ * incl_masks_out[ranks] = the incl_mask each rank passes to b200_partition_splitters_device (may be NULL). */
+int b200_multi_plan_splitters(const int64_t* less, const int64_t* equal, const int64_t* n_per_rank,
+                              const uint64_t* splitters, uint32_t ranks, uint32_t parts, int exact_ties,
+                              int64_t* tie_thresholds_out, int64_t* send_matrix_out, uint32_t* incl_masks_out);
+
+/* Host <-> device copies as the host entry points do them: plain DMA for pinned memory; pageable memory (what a
+ * Rust Vec is) goes through pinned bounce buffers filled by several host threads while the previous chunk is on
+ * the wire.  Blocking. */
+int b200_copy_h2d(void* dev_dst, const void* host_src, size_t bytes, int device);
+int b200_copy_d2h(void* host_dst, const void* dev_src, size_t bytes, int device);
 
 /*
  * RadixKey::get_level evaluated on the host through the descriptor — lets the

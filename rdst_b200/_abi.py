@@ -49,7 +49,13 @@ class SortOpts(C.Structure):
         ("variant", C.c_int32),
         ("device", C.c_int32),
         ("stream", C.c_void_p),
+        ("route", C.c_uint32),
+        ("_reserved", C.c_uint32),
     ]
+
+
+HINT_AUTO, HINT_LSD, HINT_LOW_SCRATCH = 0, 1, 2  # b200_route_hint
+B200_MAX_GPUS = 16
 
 
 class Stats(C.Structure):
@@ -77,6 +83,33 @@ class Stats(C.Structure):
 
     def as_dict(self):
         return {n: getattr(self, n) for n, _ in self._fields_}
+
+
+class MultiStats(C.Structure):
+    """b200_multi_stats (include/b200sort.h)."""
+
+    _fields_ = [
+        ("ngpus", C.c_uint32),
+        ("level", C.c_uint32),
+        ("splitter_mode", C.c_uint32),
+        ("kernel_launches", C.c_uint32),
+        ("imbalance", C.c_double),
+        ("max_sent_bytes", C.c_uint64),
+        ("n_out", C.c_uint64 * B200_MAX_GPUS),
+        ("ms_plan", C.c_float),
+        ("ms_exchange", C.c_float),
+        ("ms_local_sort", C.c_float),
+        ("ms_h2d", C.c_float),
+        ("ms_d2h", C.c_float),
+        ("ms_total", C.c_float),
+        ("local0", Stats),
+    ]
+
+    def as_dict(self):
+        d = {n: getattr(self, n) for n, _ in self._fields_ if n not in ("n_out", "local0")}
+        d["n_out"] = [int(x) for x in self.n_out[: self.ngpus]]
+        d["local0"] = self.local0.as_dict()
+        return d
 
 
 class B200SortError(RuntimeError):
@@ -189,6 +222,32 @@ SYMBOLS = {
     "b200_ipc_open": (C.c_int, [C.c_void_p, C.POINTER(C.c_void_p)]),
     "b200_ipc_close": (C.c_int, [C.c_void_p]),
     "b200_ipc_free": (C.c_int, [C.c_void_p]),
+    "b200_sort_multi_device": (
+        C.c_int,
+        [C.POINTER(C.c_void_p), C.POINTER(C.c_size_t), C.c_int, C.POINTER(C.c_int), C.POINTER(KeyDesc), C.POINTER(SortOpts),
+         C.POINTER(C.c_void_p), C.POINTER(C.c_size_t), C.POINTER(MultiStats)],
+    ),
+    "b200_sort_multi_host": (
+        C.c_int,
+        [C.c_void_p, C.c_size_t, C.c_int, C.POINTER(C.c_int), C.POINTER(KeyDesc), C.POINTER(SortOpts), C.POINTER(MultiStats)],
+    ),
+    "b200_multi_release": (C.c_int, []),
+    "b200_multi_plan_digits": (
+        C.c_int,
+        [C.POINTER(C.c_uint64), C.c_uint32, C.c_uint32, C.POINTER(C.c_int32), C.POINTER(C.c_uint32), C.POINTER(C.c_int64),
+         C.POINTER(C.c_double)],
+    ),
+    "b200_multi_choose_sample_splitters": (
+        C.c_int,
+        [C.POINTER(C.c_uint64), C.POINTER(C.c_double), C.c_size_t, C.c_uint32, C.POINTER(C.c_uint64)],
+    ),
+    "b200_multi_plan_splitters": (
+        C.c_int,
+        [C.POINTER(C.c_int64), C.POINTER(C.c_int64), C.POINTER(C.c_int64), C.POINTER(C.c_uint64), C.c_uint32, C.c_uint32,
+         C.c_int, C.POINTER(C.c_int64), C.POINTER(C.c_int64), C.POINTER(C.c_uint32)],
+    ),
+    "b200_copy_h2d": (C.c_int, [C.c_void_p, C.c_void_p, C.c_size_t, C.c_int]),
+    "b200_copy_d2h": (C.c_int, [C.c_void_p, C.c_void_p, C.c_size_t, C.c_int]),
     "b200_get_level": (C.c_int, [C.c_void_p, C.POINTER(KeyDesc), C.c_uint32]),
     "b200_host_alloc": (C.c_int, [C.POINTER(C.c_void_p), C.c_size_t]),
     "b200_host_free": (C.c_int, [C.c_void_p]),

@@ -21,6 +21,7 @@
 #include <cstring>
 #include <mutex>
 #include <string>
+#include <thread>
 #include <vector>
 
 #include "hist.cuh"
@@ -150,9 +151,9 @@ struct DeviceCtx {
     cudaEvent_t aux_ev[5] = {};
     void* d_stage = nullptr;  // device copy of host data for b200_sort_host
     size_t stage_bytes = 0;
-    void* h_bounce[2] = {nullptr, nullptr};  // pinned bounce buffers for pageable host memory
+    void* h_bounce[4] = {};  // pinned bounce buffers for pageable host memory
     size_t bounce_bytes = 0;
-    cudaEvent_t bounce_ev[2] = {};
+    cudaEvent_t bounce_ev[4] = {};
     uint32_t* d_slow = nullptr;  // hybrid key-only route: segments K3-U left to the stable K3 ([0] = count)
     size_t slow_bytes = 0;
 };
@@ -199,13 +200,12 @@ int get_ctx(int device, DeviceCtx** out) {
         // on stream 0 (e.g. a copy into the buffer) and pass stream = NULL are still ordered correctly
         CUDA_TRY(cudaStreamCreateWithFlags(&c.stream, cudaStreamDefault));
         for (auto& ev : c.ev) CUDA_TRY(cudaEventCreate(&ev));
-        for (auto& ev : c.bounce_ev) CUDA_TRY(cudaEventCreateWithFlags(&ev, cudaEventDisableTiming));
         CUDA_TRY(cudaMalloc(&c.d_small, SMALL_BYTES));
         CUDA_TRY(cudaMallocHost(&c.h_hist, size_t(MAX_LEVELS) * RADIX * 8));
         CUDA_TRY(cudaMallocHost(&c.h_joint, size_t(RADIX * RADIX + 1) * 8));
         CUDA_TRY(cudaMallocHost(&c.h_flag, 64));
         for (auto& a : c.aux) CUDA_TRY(cudaStreamCreateWithFlags(&a, cudaStreamNonBlocking));
-        for (auto& ev : c.aux_ev) CUDA_TRY(cudaEventCreateWithFlags(&ev, cudaEventDisableTiming));
+        for (auto& ev : c.aux_ev) CUDA_TRY(cudaEventCreate(&ev));
         c.ready = true;
     }
     *out = &c;
@@ -374,8 +374,8 @@ int launch_pass(DeviceCtx& c, cudaStream_t st, const PassPlan& pp, const Lowered
 // ---- K1 dispatch (instantiations live in hist_w*.cu) ----
 // Fills d_hist [levels][256] (u64) on the stream.
 int launch_histogram(DeviceCtx& c, cudaStream_t st, const Lowered& lo, const void* src, uint64_t n,
-                     unsigned long long* d_hist, const uint32_t* gate = nullptr) {
-    CUDA_TRY(cudaMemsetAsync(d_hist, 0, size_t(lo.levels) * RADIX * 8, st));
+                     unsigned long long* d_hist, const uint32_t* gate = nullptr, bool accumulate = false) {
+    if (!accumulate) CUDA_TRY(cudaMemsetAsync(d_hist, 0, size_t(lo.levels) * RADIX * 8, st));
     const bool aligned = reinterpret_cast<uintptr_t>(src) % 16 == 0;
     const uint32_t words = lo.elem_size / 4;
     bool fast = aligned && lo.elem_size % 4 == 0 && words >= 1 && words <= 4 && lo.contiguous &&
@@ -422,12 +422,8 @@ int launch_histogram(DeviceCtx& c, cudaStream_t st, const Lowered& lo, const voi
     gp.gate = gate;
     for (uint32_t l = 0; l < MAX_LEVELS; ++l) gp.lv[l] = l < lo.levels ? lo.lv[l] : LevelLowering{0, 0};
     const size_t smem = size_t(lo.levels) * RADIX * 4;
-    static bool attr_set = false;
-    if (!attr_set) {
-        CUDA_TRY(cudaFuncSetAttribute(hist_generic_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                      MAX_LEVELS * RADIX * 4));
-        attr_set = true;
-    }
+    // (per device, so set on every call like the other kernels' attributes)
+    CUDA_TRY(cudaFuncSetAttribute(hist_generic_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, MAX_LEVELS * RADIX * 4));
     const int grid = int(std::max<uint64_t>(1, std::min<uint64_t>(grid_full, (n + HIST_THREADS - 1) / HIST_THREADS)));
     hist_generic_kernel<<<grid, HIST_THREADS, smem, st>>>(gp);
     CUDA_TRY(cudaGetLastError());
@@ -615,12 +611,16 @@ bool digit_is_flat(const uint64_t* hist, uint64_t n) {
     for (int b = 0; b < RADIX; ++b) m = std::max(m, hist[b]);
     return m <= n / 8;
 }
-uint64_t hybrid_min_records(bool key_only) {
+uint64_t hybrid_min_records(bool key_only, uint32_t words) {
     const char* env = getenv("B200SORT_HYBRID_MIN");
     if (env) return strtoull(env, nullptr, 10);
-    // stable route: K3 holds one segment per SM at a time, so small segments leave it idle; the unstable
-    // route has the small-segment flavour of K3-U (several CTAs per SM)
-    return key_only ? (8ull << 20) : (256ull << 20);
+    // stable route: K3 holds one segment per SM at a time, so small segments leave it idle.  Key-only route:
+    // K3-U runs several CTAs per SM on small segments, but every segment still costs a few microseconds of
+    // claim / scan / barrier latency, so below ~500 records per segment the LSD passes win (measured, uniform
+    // keys, profiles/r4_k3u_variants.txt: u64 25 M 1.33 against 1.21 ms, 50 M 1.72 against 2.21 ms; u32 100 M
+    // 1.79 against 1.74 ms, 500 M 6.27 against 8.12 ms)
+    if (!key_only) return 256ull << 20;
+    return words == 1 ? (128ull << 20) : (32ull << 20);
 }
 MsdULaunch get_msdu_launch(uint32_t words, bool floatk) {
     const int v = getenv("B200SORT_MSDU_VARIANT") ? atoi(getenv("B200SORT_MSDU_VARIANT")) : 0;  // read per call
@@ -628,13 +628,29 @@ MsdULaunch get_msdu_launch(uint32_t words, bool floatk) {
     return words == 1 ? get_msdu_launch_w1(floatk, vv) : get_msdu_launch_w2(floatk, vv);
 }
 
+// How one sort call is driven (what b200_sort_opts carries, plus what the host entry point adds).
+struct SortCtl {
+    int variant = -1;             // >= 0: that tile variant, LSD passes only
+    uint32_t route = B200_HINT_AUTO;
+    bool result_anywhere = false; // the caller takes the result from wherever it ends up (no copy back)
+    // host entry point: K0 and K1 already ran, chunk by chunk behind the H2D copies; the device histogram
+    // and K0's flag are complete when the stream gets here
+    bool pre_counted = false;
+    // host entry point, pinned memory: D2H of the sorted array starts behind the first finished slice of
+    // the segment sort instead of after the whole sort
+    void* drain_host = nullptr;
+    cudaStream_t drain_stream = nullptr;
+    cudaEvent_t drain_event = nullptr;
+    bool drained = false;         // out: the result is already on its way to drain_host (all of it)
+};
+
 // Returns B200_OK with *done = true when the array was sorted here (result in `data`);
 // *done = false means "not eligible / segments too large": the caller runs the LSD passes.
 // *src_out tells the caller where the (possibly re-partitioned) records are.
 int sort_hybrid(DeviceCtx& c, cudaStream_t st, void* data, void* tmp, uint64_t n, const Lowered& lo,
                 const std::vector<uint32_t>& active, const unsigned long long* d_base, uint32_t* d_ticket, bool* done,
                 void** src_out, uint32_t* launches, uint32_t* slow_segments, uint32_t* local_levels,
-                uint32_t* unstable_out) {
+                uint32_t* unstable_out, SortCtl* ctl) {
     *done = false;
     *src_out = data;
     const int mode = hybrid_mode();
@@ -649,7 +665,7 @@ int sort_hybrid(DeviceCtx& c, cudaStream_t st, void* data, void* tmp, uint64_t n
     // LSD passes whatever the key width, and K3 handles one segment per SM at a time).  Unstable route:
     // cheaper passes and a segment sort that keeps the SMs busy on small segments, so it pays from four
     // active levels and a few million records on.
-    if (mode == 2 && (active.size() < (key_only ? 4u : 5u) || n < hybrid_min_records(key_only))) return B200_OK;
+    if (mode == 2 && (active.size() < (key_only ? 4u : 5u) || n < hybrid_min_records(key_only, words))) return B200_OK;
 
     // ---- the digits: bit windows over the varying bits of the key image (plan_windows) ----
     // keys that do not fill their type — or one rank's range of a sharded sort — still split 65 536 ways
@@ -875,29 +891,62 @@ int sort_hybrid(DeviceCtx& c, cudaStream_t st, void* data, void* tmp, uint64_t n
         if (rc) return rc;
         CUDA_TRY(cudaMemsetAsync(c.d_slow, 0, 4, st));
         const int force_size = getenv("B200SORT_K3U_SIZE") ? atoi(getenv("B200SORT_K3U_SIZE")) : -1;  // read per call: tests flip it
-        bool small = max_seg <= 4096;
-        if (force_size == 0) small = false;
-        const LocalCountLaunch ll = words == 1 ? get_local_count_launch_w1(lo.is_float, small) : get_local_count_launch_w2(lo.is_float, small);
+        int size = max_seg <= 4096 ? 0 : (max_seg <= 8192 ? 1 : 2);
+        if (force_size >= 0 && force_size <= 2) size = std::max(size, force_size);
+        // twice the threads with half the records each: pays for 4-byte keys (0.69 against 0.81 ms at 100 M u32,
+        // 3.59 against 3.88 ms at 500 M f32), loses for 8-byte keys whose 64-register budget spills
+        // (profiles/r4_k3u_variants.txt)
+        const bool wide = getenv("B200SORT_K3U_WIDE") ? atoi(getenv("B200SORT_K3U_WIDE")) != 0 : words == 1;
+        const LocalCountLaunch ll = words == 1 ? get_local_count_launch_w1(lo.is_float, size, wide) : get_local_count_launch_w2(lo.is_float, size, wide);
         LocalCountParams cp;
         memset(&cp, 0, sizeof(cp));
         cp.data = static_cast<uint32_t*>(data);
         cp.seg_off = d_seg;
-        cp.nseg = RADIX * RADIX;
-        cp.ticket = d_tk + 2;
         cp.key = key;
         // the digit starts at the highest bit below D2 that varies at all (plan_windows guarantees there is one)
         cp.top_bit = 64u - uint32_t(__builtin_clzll(wp.vary & ((1ull << w2_lo) - 1ull)));
         const int bmax_env = getenv("B200SORT_K3U_BMAX") ? atoi(getenv("B200SORT_K3U_BMAX")) : 0;
         cp.bmax = uint32_t(bmax_env > 0 ? std::min(bmax_env, ll.cbits) : ll.cbits);
         cp.slow_list = c.d_slow;
+        static const bool k3uprof = getenv("B200SORT_K3_PROFILE") != nullptr;
+        cp.prof = k3uprof ? reinterpret_cast<unsigned long long*>(d_tk + 320) : nullptr;
         CUDA_TRY(cudaFuncSetAttribute(ll.kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, int(ll.smem)));
         int occ = 1;
         CUDA_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, ll.kernel, ll.threads, ll.smem));
         occ = std::max(occ, 1);
         const int ugrid = int(std::min<uint64_t>(uint64_t(c.sm_count) * occ, nonempty ? nonempty : 1));
-        ll.kernel<<<ugrid, ll.threads, ll.smem, st>>>(cp);
-        CUDA_TRY(cudaGetLastError());
-        *launches += 1;
+        // Segments are claimed in memory order, so the sort can run in slices of consecutive segments; the host
+        // entry point uses that to start the D2H copy of a finished slice while the next one is sorted.
+        const bool drain = ctl && ctl->drain_host && n * lo.elem_size >= (size_t(256) << 20);
+        const uint32_t slices = drain ? 8u : 1u;
+        for (uint32_t sl = 0; sl < slices; ++sl) {
+            cp.seg_first = uint32_t(uint64_t(RADIX * RADIX) * sl / slices);
+            cp.nseg = uint32_t(uint64_t(RADIX * RADIX) * (sl + 1) / slices);
+            cp.ticket = d_tk + 2 + sl;
+            ll.kernel<<<ugrid, ll.threads, ll.smem, st>>>(cp);
+            CUDA_TRY(cudaGetLastError());
+            *launches += 1;
+            if (drain) {
+                const size_t lo_b = size_t(c.h_joint[cp.seg_first]) * lo.elem_size, hi_b = size_t(c.h_joint[cp.nseg]) * lo.elem_size;
+                CUDA_TRY(cudaEventRecord(ctl->drain_event, st));
+                CUDA_TRY(cudaStreamWaitEvent(ctl->drain_stream, ctl->drain_event, 0));
+                if (hi_b > lo_b)
+                    CUDA_TRY(cudaMemcpyAsync(static_cast<uint8_t*>(ctl->drain_host) + lo_b, static_cast<const uint8_t*>(data) + lo_b,
+                                             hi_b - lo_b, cudaMemcpyDeviceToHost, ctl->drain_stream));
+            }
+        }
+        if (drain) ctl->drained = true;  // (the caller re-copies everything if a segment went to the slow list)
+        if (k3uprof) {
+            unsigned long long h[8];
+            cudaMemcpyAsync(h, d_tk + 320, sizeof(h), cudaMemcpyDeviceToHost, st);
+            cudaStreamSynchronize(st);
+            double tot = 0;
+            for (int i = 0; i < 8; ++i) tot += double(h[i]);
+            fprintf(stderr, "[b200sort] K3-U cycles of thread 0, share per phase: wait/claim %.1f%% count %.1f%% scan %.1f%% scatter %.1f%% "
+                            "fetch-issue %.1f%% fix-up %.1f%% write-out %.1f%% zero %.1f%% (%.0f cycles per segment)\n",
+                    100 * h[0] / tot, 100 * h[1] / tot, 100 * h[2] / tot, 100 * h[3] / tot, 100 * h[4] / tot, 100 * h[5] / tot,
+                    100 * h[6] / tot, 100 * h[7] / tot, tot / double(std::max<uint64_t>(1, nonempty)));
+        }
         // the leftovers: full stable LSD over every local level, segments from the list
         lp.list = c.d_slow;
         lp.nfast = 0;
@@ -1107,7 +1156,8 @@ int sorted_check_mode() {  // B200SORT_SORTED_CHECK=0 switches the early-out off
 }
 
 // Enqueues K0 over records [0, n) and the read-back of its flag into c.h_flag (no synchronisation).
-int launch_sorted_check(DeviceCtx& c, cudaStream_t st, const Lowered& lo, const void* data, uint64_t n) {
+int launch_sorted_check(DeviceCtx& c, cudaStream_t st, const Lowered& lo, const void* data, uint64_t n, bool first = true,
+                        bool last = true) {
     uint32_t* d_flag = reinterpret_cast<uint32_t*>(c.d_small + SMALL_FLAG_OFF);
     SortedCheckParams p;
     memset(&p, 0, sizeof(p));
@@ -1127,7 +1177,7 @@ int launch_sorted_check(DeviceCtx& c, cudaStream_t st, const Lowered& lo, const 
         p.keep = lo.levels >= 8 ? ~0ull : ((1ull << (8 * lo.levels)) - 1ull);
         for (uint32_t l = 0; l < lo.levels; ++l) p.flip |= uint64_t(lo.lv[l].xor_mask & 0xffu) << (8 * l);
     }
-    CUDA_TRY(cudaMemsetAsync(d_flag, 0, 4, st));
+    if (first) CUDA_TRY(cudaMemsetAsync(d_flag, 0, 4, st));
     const uint64_t per_cta = uint64_t(SC_THREADS) * SC_ITEMS;
     const int grid = int(std::max<uint64_t>(1, std::min<uint64_t>(uint64_t(c.sm_count) * 8, (p.n_pairs + per_cta - 1) / per_cta)));
     // key-only arrays: the vectorised kernel (B200SORT_SORTED_CHECK=2 keeps the scalar one, for tests)
@@ -1147,7 +1197,7 @@ int launch_sorted_check(DeviceCtx& c, cudaStream_t st, const Lowered& lo, const 
     else if (w == 2) sorted_check_kernel<2><<<grid, SC_THREADS, 0, st>>>(p);
     else sorted_check_kernel<1><<<grid, SC_THREADS, 0, st>>>(p);
     CUDA_TRY(cudaGetLastError());
-    CUDA_TRY(cudaMemcpyAsync(c.h_flag, d_flag, 4, cudaMemcpyDeviceToHost, st));
+    if (last) CUDA_TRY(cudaMemcpyAsync(c.h_flag, d_flag, 4, cudaMemcpyDeviceToHost, st));
     return B200_OK;
 }
 
@@ -1155,7 +1205,13 @@ int launch_sorted_check(DeviceCtx& c, cudaStream_t st, const Lowered& lo, const 
 // The sort proper, device resident.
 // ---------------------------------------------------------------------------
 int sort_device_impl(DeviceCtx& c, cudaStream_t st, void* data, void* tmp, uint64_t n, const Lowered& lo,
-                     int variant, bool result_anywhere, void** result_ptr, b200_stats* stats) {
+                     SortCtl& ctl, void** result_ptr, b200_stats* stats) {
+    // what the route hint means (include/b200sort.h b200_route_hint): LSD = passes only, like an explicit variant;
+    // LOW_SCRATCH = passes with the small-tile variant (the caller releases the scratch pool afterwards)
+    int variant = ctl.variant;
+    if (variant < 0 && ctl.route == B200_HINT_LOW_SCRATCH) variant = kSmallVariant;
+    const bool auto_route = ctl.variant < 0 && ctl.route == B200_HINT_AUTO;
+    const bool result_anywhere = ctl.result_anywhere;
     unsigned long long* d_hist = reinterpret_cast<unsigned long long*>(c.d_small + SMALL_HIST_OFF);
     unsigned long long* d_base = reinterpret_cast<unsigned long long*>(c.d_small + SMALL_BASE_OFF);
     uint32_t* d_ticket = reinterpret_cast<uint32_t*>(c.d_small + SMALL_TICKET_OFF);
@@ -1163,7 +1219,7 @@ int sort_device_impl(DeviceCtx& c, cudaStream_t st, void* data, void* tmp, uint6
     CUDA_TRY(cudaEventRecord(c.ev[0], st));
     int rc = B200_OK;
     SplitParams small_key;
-    if (variant < 0 && small_sort_ok(lo, data, n, &small_key)) {
+    if (auto_route && !ctl.pre_counted && small_sort_ok(lo, data, n, &small_key)) {
         rc = sort_small(c, st, data, n, lo, small_key);
         if (rc) return rc;
         CUDA_TRY(cudaEventRecord(c.ev[1], st));
@@ -1188,22 +1244,30 @@ int sort_device_impl(DeviceCtx& c, cudaStream_t st, void* data, void* tmp, uint6
     // with the histograms.
     const bool check = sorted_check_mode() != 0 && n >= 2;
     static const bool dbg = getenv("B200SORT_DEBUG_TIMING") != nullptr;
-    if (check) {
-        *c.h_flag = 1;
-        rc = launch_sorted_check(c, st, lo, data, n);
+    if (ctl.pre_counted) {
+        // the host entry point ran K0 and K1 behind its H2D chunks; only the flag has to come back
+        if (check) {
+            *c.h_flag = 1;
+            CUDA_TRY(cudaMemcpyAsync(c.h_flag, c.d_small + SMALL_FLAG_OFF, 4, cudaMemcpyDeviceToHost, st));
+        }
+    } else {
+        if (check) {
+            *c.h_flag = 1;
+            rc = launch_sorted_check(c, st, lo, data, n);
+            if (rc) return rc;
+            if (dbg) cudaEventRecord(c.ev[8], st);
+        }
+        rc = launch_histogram(c, st, lo, data, n, d_hist,
+                              check ? reinterpret_cast<const uint32_t*>(c.d_small + SMALL_FLAG_OFF) : nullptr);
         if (rc) return rc;
-        if (dbg) cudaEventRecord(c.ev[8], st);
-    }
-    rc = launch_histogram(c, st, lo, data, n, d_hist,
-                          check ? reinterpret_cast<const uint32_t*>(c.d_small + SMALL_FLAG_OFF) : nullptr);
-    if (rc) return rc;
-    if (dbg && check) {
-        cudaEventRecord(c.ev[9], st);
-        cudaEventSynchronize(c.ev[9]);
-        float k0 = 0, k1 = 0;
-        cudaEventElapsedTime(&k0, c.ev[0], c.ev[8]);
-        cudaEventElapsedTime(&k1, c.ev[8], c.ev[9]);
-        fprintf(stderr, "[b200sort] K0 (memset + kernel + flag D2H) %.3f ms, K1 %.3f ms, sorted = %d\n", k0, k1, *c.h_flag == 0);
+        if (dbg && check) {
+            cudaEventRecord(c.ev[9], st);
+            cudaEventSynchronize(c.ev[9]);
+            float k0 = 0, k1 = 0;
+            cudaEventElapsedTime(&k0, c.ev[0], c.ev[8]);
+            cudaEventElapsedTime(&k1, c.ev[8], c.ev[9]);
+            fprintf(stderr, "[b200sort] K0 (memset + kernel + flag D2H) %.3f ms, K1 %.3f ms, sorted = %d\n", k0, k1, *c.h_flag == 0);
+        }
     }
     if (dbg) cudaEventRecord(c.ev[8], st);
     scan_hist_kernel<<<lo.levels, RADIX, 0, st>>>(d_hist, d_base);
@@ -1257,16 +1321,16 @@ int sort_device_impl(DeviceCtx& c, cudaStream_t st, void* data, void* tmp, uint6
     // segments fit an SM, LSD passes otherwise (an explicit variant request always means LSD passes)
     bool hybrid_done = false;
     uint32_t hybrid_launches = 0, slow_segments = 0, local_levels = 0, unstable = 0;
-    if (variant < 0) {
+    if (auto_route) {
         void* where = data;
         rc = sort_hybrid(c, st, data, tmp, n, lo, active, d_base, d_ticket, &hybrid_done, &where, &hybrid_launches,
-                         &slow_segments, &local_levels, &unstable);
+                         &slow_segments, &local_levels, &unstable, &ctl);
         if (rc) return rc;
         if (!hybrid_done && where == tmp) std::swap(src, dst);  // MSD pass 1 ran: the records now live in tmp
     }
     bool msd1_done = false;
     uint32_t msd1_local = 0;
-    if (variant < 0 && !hybrid_done && src == data) {
+    if (auto_route && !hybrid_done && src == data) {
         rc = sort_msd1(c, st, data, tmp, n, lo, active, d_base, d_ticket, pp, &msd1_done, &msd1_local);
         if (rc) return rc;
         if (msd1_done) {
@@ -1304,7 +1368,8 @@ int sort_device_impl(DeviceCtx& c, cudaStream_t st, void* data, void* tmp, uint6
     if (result_ptr) *result_ptr = src;
     CUDA_TRY(cudaEventRecord(c.ev[2], st));
     CUDA_TRY(cudaStreamSynchronize(st));
-    const uint32_t launches = 2 + pass + hybrid_launches + (check ? 1 : 0);  // (K0 +) K1 + scan + passes
+    if (ctl.drained && slow_segments) ctl.drained = false;  // some segments were finished after their slice was copied
+    const uint32_t launches = (ctl.pre_counted ? 1 : 2 + (check ? 1 : 0)) + pass + hybrid_launches;  // (K0 +) K1 + scan + passes
     if (hybrid_done || msd1_done) pass = n_active;  // levels the result is sorted on
     if (stats) {
         stats->levels_run = pass;
@@ -1354,115 +1419,275 @@ int b200_sort_device(void* dev_ptr, void* dev_tmp, size_t n, const b200_key_desc
     int rc = lower_desc(desc, &lo);
     if (rc) return rc;
     if (stats) memset(stats, 0, sizeof(*stats));
+    if (opts && opts->route > B200_HINT_LOW_SCRATCH) return B200_ERR_BAD_ARG;
     if (n <= 1) return B200_OK;  // reference src/radix_sort_builder.rs:151
     if (!dev_ptr) return B200_ERR_BAD_ARG;
     DeviceCtx* c = nullptr;
     rc = get_ctx(opts ? opts->device : -1, &c);
     if (rc) return rc;
-    std::lock_guard<std::mutex> lk(c->mu);
-    DeviceGuard guard(c->dev);
-    cudaStream_t st = (opts && opts->stream) ? static_cast<cudaStream_t>(opts->stream) : c->stream;
-    void* tmp = dev_tmp;
-    if (!tmp) {
-        rc = ensure_bytes(&c->d_tmp, &c->tmp_bytes, n * lo.elem_size);
-        if (rc) return rc;
-        tmp = c->d_tmp;
+    {
+        std::lock_guard<std::mutex> lk(c->mu);
+        DeviceGuard guard(c->dev);
+        cudaStream_t st = (opts && opts->stream) ? static_cast<cudaStream_t>(opts->stream) : c->stream;
+        void* tmp = dev_tmp;
+        if (!tmp) {
+            rc = ensure_bytes(&c->d_tmp, &c->tmp_bytes, n * lo.elem_size);
+            if (rc) return rc;
+            tmp = c->d_tmp;
+        }
+        SortCtl ctl;
+        ctl.variant = opts ? opts->variant : -1;
+        ctl.route = opts ? opts->route : uint32_t(B200_HINT_AUTO);
+        rc = sort_device_impl(*c, st, dev_ptr, tmp, n, lo, ctl, nullptr, stats);
     }
-    return sort_device_impl(*c, st, dev_ptr, tmp, n, lo, opts ? opts->variant : -1, false, nullptr, stats);
+    if (rc == B200_OK && opts && opts->route == B200_HINT_LOW_SCRATCH) rc = b200_release_scratch(c->dev);
+    return rc;
 }
 
+}  // extern "C"
+
+namespace {
+
+// ---- host <-> device copies -------------------------------------------------------------------
+// Pinned memory: plain DMA.  Pageable memory (what a Rust Vec is): the DMA engine cannot read it, so the
+// bytes go through pinned bounce buffers; several host threads fill (drain) a buffer while the previous
+// one is on the wire, so the copy runs at PCIe speed instead of one core's memcpy speed.
+constexpr size_t BOUNCE_CHUNK = size_t(32) << 20;
+constexpr int NBOUNCE = 4;
+
+bool host_is_pinned(const void* p) {
+    cudaPointerAttributes attr;
+    if (cudaPointerGetAttributes(&attr, p) == cudaSuccess) return attr.type == cudaMemoryTypeHost || attr.type == cudaMemoryTypeManaged;
+    cudaGetLastError();
+    return false;
+}
+
+int copy_threads() {
+    static const int t = [] {
+        const char* env = getenv("B200SORT_COPY_THREADS");
+        if (env && atoi(env) > 0) return std::min(atoi(env), 64);
+        const unsigned hc = std::thread::hardware_concurrency();
+        return int(std::max(1u, std::min(8u, hc ? hc / 2 : 4u)));
+    }();
+    return t;
+}
+
+void par_memcpy(void* dst, const void* src, size_t len) {
+    const int T = copy_threads();
+    if (T <= 1 || len < (size_t(4) << 20)) {
+        memcpy(dst, src, len);
+        return;
+    }
+    const size_t per = ((len + T - 1) / T + 4095) / 4096 * 4096;
+    std::vector<std::thread> th;
+    for (int t = 1; t < T; ++t) {
+        const size_t off = per * t;
+        if (off >= len) break;
+        th.emplace_back([=] { memcpy(static_cast<uint8_t*>(dst) + off, static_cast<const uint8_t*>(src) + off, std::min(per, len - off)); });
+    }
+    memcpy(dst, src, std::min(per, len));
+    for (auto& t : th) t.join();
+}
+
+int ensure_bounce(DeviceCtx& c) {
+    if (c.h_bounce[0]) return B200_OK;
+    for (int i = 0; i < NBOUNCE; ++i) {
+        CUDA_TRY(cudaMallocHost(&c.h_bounce[i], BOUNCE_CHUNK));
+        CUDA_TRY(cudaEventCreateWithFlags(&c.bounce_ev[i], cudaEventDisableTiming));
+    }
+    c.bounce_bytes = BOUNCE_CHUNK;
+    return B200_OK;
+}
+
+// Enqueues (pinned) or performs (pageable: returns when the last chunk is queued) the copy of `bytes` bytes to
+// the device on stream `st`.  `chunk_done(lo, hi)` is called after the bytes [lo, hi) have been queued, so the
+// caller can queue work on them behind the copy.
+template <class F>
+int copy_in(DeviceCtx& c, cudaStream_t st, void* dev_dst, const void* host_src, size_t bytes, size_t chunk, size_t align,
+            F chunk_done) {
+    const bool pinned = host_is_pinned(host_src);
+    if (!pinned) {
+        int rc = ensure_bounce(c);
+        if (rc) return rc;
+        chunk = std::max<size_t>(align, std::min(chunk, BOUNCE_CHUNK) / align * align);  // chunks end on `align` boundaries
+    }
+    int k = 0;
+    for (size_t off = 0; off < bytes; off += chunk) {
+        const size_t len = std::min(chunk, bytes - off);
+        const uint8_t* src = static_cast<const uint8_t*>(host_src) + off;
+        if (pinned) {
+            CUDA_TRY(cudaMemcpyAsync(static_cast<uint8_t*>(dev_dst) + off, src, len, cudaMemcpyHostToDevice, st));
+        } else {
+            CUDA_TRY(cudaEventSynchronize(c.bounce_ev[k]));  // the DMA that last used this buffer is done
+            par_memcpy(c.h_bounce[k], src, len);
+            CUDA_TRY(cudaMemcpyAsync(static_cast<uint8_t*>(dev_dst) + off, c.h_bounce[k], len, cudaMemcpyHostToDevice, st));
+            CUDA_TRY(cudaEventRecord(c.bounce_ev[k], st));
+            k = (k + 1) % NBOUNCE;
+        }
+        int rc = chunk_done(off, off + len);
+        if (rc) return rc;
+    }
+    return B200_OK;
+}
+
+// Copies `bytes` bytes from the device to host memory on stream `st`; returns when they are in host memory
+// (pageable) or queued (pinned: the caller synchronises the stream).
+int copy_out(DeviceCtx& c, cudaStream_t st, void* host_dst, const void* dev_src, size_t bytes) {
+    if (host_is_pinned(host_dst)) {
+        CUDA_TRY(cudaMemcpyAsync(host_dst, dev_src, bytes, cudaMemcpyDeviceToHost, st));
+        return B200_OK;
+    }
+    int rc = ensure_bounce(c);
+    if (rc) return rc;
+    size_t pend_off[NBOUNCE] = {}, pend_len[NBOUNCE] = {};
+    size_t off = 0;
+    int k = 0;
+    bool any = true;
+    while (off < bytes || any) {
+        if (pend_len[k]) {  // the oldest DMA: wait for it, then spread its bytes with all copy threads
+            CUDA_TRY(cudaEventSynchronize(c.bounce_ev[k]));
+            par_memcpy(static_cast<uint8_t*>(host_dst) + pend_off[k], c.h_bounce[k], pend_len[k]);
+            pend_len[k] = 0;
+        }
+        if (off < bytes) {
+            const size_t len = std::min(BOUNCE_CHUNK, bytes - off);
+            CUDA_TRY(cudaMemcpyAsync(c.h_bounce[k], static_cast<const uint8_t*>(dev_src) + off, len, cudaMemcpyDeviceToHost, st));
+            CUDA_TRY(cudaEventRecord(c.bounce_ev[k], st));
+            pend_off[k] = off, pend_len[k] = len;
+            off += len;
+        }
+        k = (k + 1) % NBOUNCE;
+        any = false;
+        for (int i = 0; i < NBOUNCE; ++i) any = any || pend_len[i] != 0;
+    }
+    return B200_OK;
+}
+
+}  // namespace
+
+extern "C" {
+
+int b200_copy_h2d(void* dev_dst, const void* host_src, size_t bytes, int device) {
+    if (bytes == 0) return B200_OK;
+    if (!dev_dst || !host_src) return B200_ERR_BAD_ARG;
+    DeviceCtx* c = nullptr;
+    int rc = get_ctx(device, &c);
+    if (rc) return rc;
+    std::lock_guard<std::mutex> lk(c->mu);
+    DeviceGuard guard(c->dev);
+    rc = copy_in(*c, c->stream, dev_dst, host_src, bytes, size_t(256) << 20, 4096, [](size_t, size_t) { return int(B200_OK); });
+    if (rc) return rc;
+    CUDA_TRY(cudaStreamSynchronize(c->stream));
+    return B200_OK;
+}
+
+int b200_copy_d2h(void* host_dst, const void* dev_src, size_t bytes, int device) {
+    if (bytes == 0) return B200_OK;
+    if (!host_dst || !dev_src) return B200_ERR_BAD_ARG;
+    DeviceCtx* c = nullptr;
+    int rc = get_ctx(device, &c);
+    if (rc) return rc;
+    std::lock_guard<std::mutex> lk(c->mu);
+    DeviceGuard guard(c->dev);
+    rc = copy_out(*c, c->stream, host_dst, dev_src, bytes);
+    if (rc) return rc;
+    CUDA_TRY(cudaStreamSynchronize(c->stream));
+    return B200_OK;
+}
+
+// The `&mut [T]`-in-host-RAM drop-in.  Timeline on a large input: the H2D copy runs in chunks on a copy stream;
+// K0 (sorted check) and K1 (all-level histogram) of chunk i run on the compute stream while chunk i + 1 is on
+// the wire, so the sort proper starts the moment the last byte lands; on the key-only hybrid route the D2H copy
+// starts behind the first finished slice of the segment sort.
 int b200_sort_host(void* host_ptr, size_t n, const b200_key_desc* desc, const b200_sort_opts* opts,
                    b200_stats* stats) {
     Lowered lo;
     int rc = lower_desc(desc, &lo);
     if (rc) return rc;
     if (stats) memset(stats, 0, sizeof(*stats));
+    if (opts && opts->route > B200_HINT_LOW_SCRATCH) return B200_ERR_BAD_ARG;
     if (n <= 1) return B200_OK;
     if (!host_ptr) return B200_ERR_BAD_ARG;
     DeviceCtx* c = nullptr;
     rc = get_ctx(opts ? opts->device : -1, &c);
     if (rc) return rc;
-    std::lock_guard<std::mutex> lk(c->mu);
-    DeviceGuard guard(c->dev);
-    cudaStream_t st = (opts && opts->stream) ? static_cast<cudaStream_t>(opts->stream) : c->stream;
-    const size_t bytes = n * lo.elem_size;
-    rc = ensure_bytes(&c->d_stage, &c->stage_bytes, bytes);
-    if (rc) return rc;
-    rc = ensure_bytes(&c->d_tmp, &c->tmp_bytes, bytes);
-    if (rc) return rc;
+    {
+        std::lock_guard<std::mutex> lk(c->mu);
+        DeviceGuard guard(c->dev);
+        cudaStream_t st = (opts && opts->stream) ? static_cast<cudaStream_t>(opts->stream) : c->stream;
+        cudaStream_t cs = c->aux[0];  // copies
+        const size_t bytes = n * lo.elem_size;
+        rc = ensure_bytes(&c->d_stage, &c->stage_bytes, bytes);
+        if (rc) return rc;
+        rc = ensure_bytes(&c->d_tmp, &c->tmp_bytes, bytes);
+        if (rc) return rc;
+        const bool pinned = host_is_pinned(host_ptr);
+        SortCtl ctl;
+        ctl.variant = opts ? opts->variant : -1;
+        ctl.route = opts ? opts->route : uint32_t(B200_HINT_AUTO);
+        ctl.result_anywhere = true;
+        // count behind the copy when the input is large enough for the chunks to matter
+        static const bool overlap_off = getenv("B200SORT_HOST_OVERLAP") && atoi(getenv("B200SORT_HOST_OVERLAP")) == 0;
+        const bool pre = !overlap_off && bytes >= (size_t(64) << 20);
+        const bool check = sorted_check_mode() != 0;
+        unsigned long long* d_hist = reinterpret_cast<unsigned long long*>(c->d_small + SMALL_HIST_OFF);
+        const size_t rec_align = size_t(lo.elem_size) * 16;  // chunk boundaries keep 16-byte alignment for every record size
+        size_t chunk = std::max<size_t>(size_t(128) << 20, bytes / 16) / rec_align * rec_align;
+        if (!pre) chunk = (bytes + rec_align - 1) / rec_align * rec_align;
 
-    cudaPointerAttributes attr;
-    bool pinned = false;
-    if (cudaPointerGetAttributes(&attr, host_ptr) == cudaSuccess) {
-        pinned = attr.type == cudaMemoryTypeHost || attr.type == cudaMemoryTypeManaged;
-    } else {
-        cudaGetLastError();
-    }
-    constexpr size_t CHUNK = size_t(64) << 20;
-    if (!pinned && !c->h_bounce[0]) {
-        for (int i = 0; i < 2; ++i) CUDA_TRY(cudaMallocHost(&c->h_bounce[i], CHUNK));
-        c->bounce_bytes = CHUNK;
-    }
-
-    CUDA_TRY(cudaEventRecord(c->ev[10], st));
-    if (pinned) {
-        CUDA_TRY(cudaMemcpyAsync(c->d_stage, host_ptr, bytes, cudaMemcpyHostToDevice, st));
-    } else {
-        // pageable memory: stage through two pinned bounce buffers so the DMA of
-        // chunk i overlaps the host memcpy of chunk i+1
-        size_t off = 0;
-        int k = 0;
-        while (off < bytes) {
-            const size_t len = std::min(CHUNK, bytes - off);
-            CUDA_TRY(cudaEventSynchronize(c->bounce_ev[k]));
-            memcpy(c->h_bounce[k], static_cast<const uint8_t*>(host_ptr) + off, len);
-            CUDA_TRY(cudaMemcpyAsync(static_cast<uint8_t*>(c->d_stage) + off, c->h_bounce[k], len,
-                                     cudaMemcpyHostToDevice, st));
-            CUDA_TRY(cudaEventRecord(c->bounce_ev[k], st));
-            off += len;
-            k ^= 1;
+        CUDA_TRY(cudaEventRecord(c->ev[10], st));
+        CUDA_TRY(cudaStreamWaitEvent(cs, c->ev[10], 0));  // the copies start after whatever the caller queued before
+        if (pre) CUDA_TRY(cudaMemsetAsync(d_hist, 0, size_t(lo.levels) * RADIX * 8, st));
+        uint8_t* stage = static_cast<uint8_t*>(c->d_stage);
+        rc = copy_in(*c, cs, stage, host_ptr, bytes, chunk, rec_align, [&](size_t lo_b, size_t hi_b) -> int {
+            if (!pre) return B200_OK;
+            CUDA_TRY(cudaEventRecord(c->aux_ev[0], cs));
+            CUDA_TRY(cudaStreamWaitEvent(st, c->aux_ev[0], 0));
+            const uint64_t r0 = lo_b / lo.elem_size, r1 = hi_b / lo.elem_size;
+            if (check) {  // pairs (r0 - 1, r0) .. (r1 - 2, r1 - 1): the pair that straddles two chunks belongs to the later one
+                const uint64_t first = r0 ? r0 - 1 : 0;
+                if (r1 - first >= 2) {
+                    int e = launch_sorted_check(*c, st, lo, stage + first * lo.elem_size, r1 - first, r0 == 0, false);
+                    if (e) return e;
+                }
+            }
+            return launch_histogram(*c, st, lo, stage + lo_b, r1 - r0, d_hist, nullptr, true);
+        });
+        if (rc) return rc;
+        CUDA_TRY(cudaEventRecord(c->aux_ev[1], cs));
+        CUDA_TRY(cudaStreamWaitEvent(st, c->aux_ev[1], 0));
+        CUDA_TRY(cudaEventRecord(c->ev[11], st));
+        ctl.pre_counted = pre;
+        if (pinned) {
+            ctl.drain_host = host_ptr;
+            ctl.drain_stream = cs;
+            ctl.drain_event = c->aux_ev[2];
+        }
+        void* result = nullptr;
+        b200_stats local{};
+        rc = sort_device_impl(*c, st, c->d_stage, c->d_tmp, n, lo, ctl, &result, &local);
+        if (rc) return rc;
+        CUDA_TRY(cudaEventRecord(c->aux_ev[3], st));  // (ev[5] / ev[6] belong to the hybrid route's phase times)
+        if (local.already_sorted) {
+            // K0 found the input in key order: the caller's buffer already holds the result
+        } else if (ctl.drained) {
+            CUDA_TRY(cudaStreamSynchronize(cs));
+        } else {
+            if (ctl.drain_host) CUDA_TRY(cudaStreamSynchronize(cs));  // partial drains of a sort that then took the slow list
+            rc = copy_out(*c, st, host_ptr, result, bytes);
+            if (rc) return rc;
+        }
+        CUDA_TRY(cudaEventRecord(c->aux_ev[4], st));
+        CUDA_TRY(cudaStreamSynchronize(st));
+        if (stats) {
+            *stats = local;
+            if (pre) stats->kernel_launches += uint32_t((bytes + chunk - 1) / chunk) * (check ? 2u : 1u);
+            CUDA_TRY(cudaEventElapsedTime(&stats->ms_h2d, c->ev[10], c->ev[11]));
+            CUDA_TRY(cudaEventElapsedTime(&stats->ms_d2h, c->aux_ev[3], c->aux_ev[4]));
+            CUDA_TRY(cudaEventElapsedTime(&stats->ms_total, c->ev[10], c->aux_ev[4]));
         }
     }
-    CUDA_TRY(cudaEventRecord(c->ev[11], st));
-    void* result = nullptr;
-    b200_stats local{};
-    rc = sort_device_impl(*c, st, c->d_stage, c->d_tmp, n, lo, opts ? opts->variant : -1, true, &result, &local);
-    if (rc) return rc;
-    CUDA_TRY(cudaEventRecord(c->ev[5], st));
-    if (local.already_sorted) {
-        // K0 found the input in key order: the caller's buffer already holds the result
-    } else if (pinned) {
-        CUDA_TRY(cudaMemcpyAsync(host_ptr, result, bytes, cudaMemcpyDeviceToHost, st));
-    } else {
-        size_t off = 0;
-        int k = 0;
-        size_t pend_off[2] = {0, 0}, pend_len[2] = {0, 0};
-        while (off < bytes || pend_len[0] || pend_len[1]) {
-            if (pend_len[k]) {
-                CUDA_TRY(cudaEventSynchronize(c->bounce_ev[k]));
-                memcpy(static_cast<uint8_t*>(host_ptr) + pend_off[k], c->h_bounce[k], pend_len[k]);
-                pend_len[k] = 0;
-            }
-            if (off < bytes) {
-                const size_t len = std::min(CHUNK, bytes - off);
-                CUDA_TRY(cudaMemcpyAsync(c->h_bounce[k], static_cast<const uint8_t*>(result) + off, len,
-                                         cudaMemcpyDeviceToHost, st));
-                CUDA_TRY(cudaEventRecord(c->bounce_ev[k], st));
-                pend_off[k] = off;
-                pend_len[k] = len;
-                off += len;
-            }
-            k ^= 1;
-        }
-    }
-    CUDA_TRY(cudaEventRecord(c->ev[6], st));
-    CUDA_TRY(cudaStreamSynchronize(st));
-    if (stats) {
-        *stats = local;
-        CUDA_TRY(cudaEventElapsedTime(&stats->ms_h2d, c->ev[10], c->ev[11]));
-        CUDA_TRY(cudaEventElapsedTime(&stats->ms_d2h, c->ev[5], c->ev[6]));
-        CUDA_TRY(cudaEventElapsedTime(&stats->ms_total, c->ev[10], c->ev[6]));
-    }
+    if (opts && opts->route == B200_HINT_LOW_SCRATCH) return b200_release_scratch(c->dev);
     return B200_OK;
 }
 
@@ -1806,9 +2031,9 @@ int b200_release_scratch(int device) {
     std::lock_guard<std::mutex> lk(c->mu);
     DeviceGuard guard(c->dev);
     void** ptrs[] = {&c->d_tmp, reinterpret_cast<void**>(&c->d_lookback), &c->d_stage,
-                     reinterpret_cast<void**>(&c->d_sample)};
-    size_t* sizes[] = {&c->tmp_bytes, &c->lookback_bytes, &c->stage_bytes, &c->sample_bytes};
-    for (int i = 0; i < 4; ++i) {
+                     reinterpret_cast<void**>(&c->d_sample), reinterpret_cast<void**>(&c->d_slow)};
+    size_t* sizes[] = {&c->tmp_bytes, &c->lookback_bytes, &c->stage_bytes, &c->sample_bytes, &c->slow_bytes};
+    for (int i = 0; i < 5; ++i) {
         if (*ptrs[i]) cudaFree(*ptrs[i]);
         *ptrs[i] = nullptr;
         *sizes[i] = 0;
@@ -1869,7 +2094,7 @@ int b200_route_plan(const b200_key_desc* desc, const uint64_t* hist, size_t n, b
     const uint32_t words = lo.elem_size / 4;
     if (mode != 0 && active.size() >= 3 && lo.elem_size % 4 == 0 && (words == 1 || words == 2) && lo.levels <= 8 &&
         uint64_t(n) < (1ull << 32) && lower_prefix(lo, &key) == B200_OK &&
-        !(mode == 2 && (active.size() < (key_only_record(lo) ? 4u : 5u) || uint64_t(n) < hybrid_min_records(key_only_record(lo))))) {
+        !(mode == 2 && (active.size() < (key_only_record(lo) ? 4u : 5u) || uint64_t(n) < hybrid_min_records(key_only_record(lo), words)))) {
         WindowPlan wp;
         if (plan_windows(lo, hist, n, &wp)) {
             bool ok = true;

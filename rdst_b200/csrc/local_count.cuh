@@ -12,10 +12,10 @@
 //            conflicts), one block scan, counters := exclusive bases;
 //   scatter  one ATOMS.ADD per record returns its position; the record goes to the staging buffer;
 //            afterwards counter d holds the END of digit d's run (= the start of digit d + 1's);
-//   fix-up + write-out, fused: records are read back in position order; a record whose digit run
-//            holds c > 1 records ranks itself among the other c - 1 by the whole key image
-//            (a comparison sort of the run, one record per thread, neighbouring addresses) and is
-//            stored straight to its final place in global memory.
+//   fix-up   the scan also lists every counter that holds >= 2 records (a "run" of the staging
+//            buffer); one thread per run orders it by the whole key image — a compare-and-swap for
+//            the common run of two, an insertion sort up to LC_MAXRUN records;
+//   write-out  the staging buffer goes back where the segment came from, coalesced.
 //
 // A wide digit leaves runs of expected length < 0.5, so the radix part is one level instead of the
 // stable engine's two (local_sort.cuh) and nothing has to be stable: records with equal keys are
@@ -23,30 +23,35 @@
 // duplicates: checked by a warp, nothing to do then); otherwise the segment is appended to
 // `slow_list` and the stable segment sort (local_sort_kernel in list mode) handles it afterwards.
 #pragma once
+#include <type_traits>
+
 #include "pass_atomic.cuh"
 
 namespace b200 {
 
-constexpr int LC_ITEMS = 32, LC_MAXRUN = 16;
+constexpr int LC_MAXRUN = 16;
 
 struct LocalCountParams {
     uint32_t* data;           // sorted in place, segment by segment
     const uint64_t* seg_off;  // [nseg + 1] record offsets of the segments
+    uint32_t seg_first;       // this launch sorts segments [seg_first, nseg)
     uint32_t nseg;
     uint32_t* ticket;         // zeroed before the launch
     SplitParams key;          // 64-bit order-preserving image of the whole key
     uint32_t top_bit;         // image bits [0, top_bit) are unsorted inside a segment (>= 1)
     uint32_t bmax;            // cap on the digit width (<= CBITS of the instantiation)
     uint32_t* slow_list;      // [0] = count, [1 ..] = ids of the segments left to the stable segment sort
+    unsigned long long* prof; // optional [8] cycle counters per phase (thread 0 of every CTA), nullptr = off
 };
 
-template <int WORDS, int THREADS, int CBITS>
+template <int WORDS, int THREADS, int ITEMS, int CBITS>
 struct LocalCountSmem {
-    static constexpr int CAP = THREADS * LC_ITEMS;
-    static constexpr size_t OUT_BYTES = size_t(CAP) * WORDS * 4;
+    static constexpr int CAP = THREADS * ITEMS;
+    static constexpr size_t OUT_BYTES = (size_t(CAP + 2) * WORDS * 4 + 127) / 128 * 128;  // + the shift that aligns record pairs
     static constexpr size_t CNT_BYTES = (size_t(1) << CBITS) * 2;
+    static constexpr size_t RUN_BYTES = size_t(CAP / 2) * 4;  // a segment of c records has at most c / 2 runs of >= 2
     static constexpr size_t MISC_BYTES = 256;
-    static constexpr size_t TOTAL = OUT_BYTES + CNT_BYTES + MISC_BYTES;
+    static constexpr size_t TOTAL = OUT_BYTES + CNT_BYTES + RUN_BYTES + MISC_BYTES;
 };
 
 // The order-preserving image of a record that is nothing but its key (1 or 2 words, key at offset 0, every
@@ -75,50 +80,94 @@ __device__ __forceinline__ typename KeyImage<WORDS>::T key_image(const Rec<WORDS
     }
 }
 
-template <int WORDS, bool FLOATK, int THREADS, int CBITS, int MINB>
+template <int WORDS, bool FLOATK, int THREADS, int ITEMS, int CBITS, int MINB>
 __global__ void __launch_bounds__(THREADS, MINB) local_count_kernel(const LocalCountParams p) {
-    using SM = LocalCountSmem<WORDS, THREADS, CBITS>;
+    using SM = LocalCountSmem<WORDS, THREADS, ITEMS, CBITS>;
     using KT = typename KeyImage<WORDS>::T;
-    constexpr int ITEMS = LC_ITEMS, WARPS = THREADS / 32;
+    constexpr int WARPS = THREADS / 32;
+    static_assert(ITEMS % 8 == 0, "scatter batches of eight");
     extern __shared__ __align__(128) uint8_t smem_raw[];
     uint32_t* s_out = reinterpret_cast<uint32_t*>(smem_raw);
     uint32_t* s_cnt = reinterpret_cast<uint32_t*>(smem_raw + SM::OUT_BYTES);
-    uint8_t* misc = smem_raw + SM::OUT_BYTES + SM::CNT_BYTES;
-    volatile uint32_t* s_seg = reinterpret_cast<volatile uint32_t*>(misc);  // [0] first id, [1] next id, [2] long run seen, [3] slow
-    uint32_t* s_wtot = reinterpret_cast<uint32_t*>(misc + 64);              // WARPS warp totals
+    uint32_t* s_runs = reinterpret_cast<uint32_t*>(smem_raw + SM::OUT_BYTES + SM::CNT_BYTES);  // {count:16 | first position:16}
+    uint8_t* misc = smem_raw + SM::OUT_BYTES + SM::CNT_BYTES + SM::RUN_BYTES;
+    // [0] first id, [1] next id; per trip parity p: [4p + 2] long run seen, [4p + 3] slow
+    // (a trip's flags are cleared two trips later, so no thread can still be reading them)
+    volatile uint32_t* s_seg = reinterpret_cast<volatile uint32_t*>(misc);
+    uint32_t par = 0;
+    uint32_t* s_wtot = reinterpret_cast<uint32_t*>(misc + 64);  // WARPS warp totals
 
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const uint32_t cnt_base = smem_u32(s_cnt);
     const KT xorv = KT(p.key.xorv);
     for (int i = tid; i < int(SM::CNT_BYTES / 16); i += THREADS) reinterpret_cast<uint4*>(s_cnt)[i] = make_uint4(0, 0, 0, 0);
 
-    uint32_t cnt = 0;
+    // Global memory is touched two records at a time (16 bytes for u64 keys): half the load / store
+    // instructions, which is what the memory phases of this kernel wait on (lg_throttle).  A segment starts
+    // at any record, so: `head` records (0 or 1) up to pair alignment, npairs aligned pairs, maybe one tail
+    // record.  The order of records inside a segment is free, so thread t simply takes pairs t, t + THREADS, ...;
+    // head and tail go to the last slots of the last thread (free whenever they exist, as cnt <= CAP).
+    uint32_t cnt = 0, head = 0, vmask = 0;  // vmask: bit j = r[j] holds a record
     uint32_t* g = nullptr;
     Rec<WORDS> r[ITEMS];
-    auto fetch = [&](uint32_t sg) {  // header + records of segment sg (order is free: coalesced element order)
+    using Vec2 = typename std::conditional<WORDS == 1, uint2, uint4>::type;
+    auto fetch = [&](uint32_t sg) {
         cnt = 0;
+        vmask = 0;
         if (sg >= p.nseg) return;
         const uint64_t base = p.seg_off[sg];
         cnt = uint32_t(p.seg_off[sg + 1] - base);
         g = p.data + base * WORDS;
+        head = uint32_t(base) & 1u;
         if (cnt <= 1) return;
+        const uint32_t npairs = (cnt - head) >> 1;
+        const Vec2* gp = reinterpret_cast<const Vec2*>(g + head * WORDS);
 #pragma unroll
-        for (int j = 0; j < ITEMS; ++j) {
-            const uint32_t e = uint32_t(j * THREADS + tid);
-            if (e < cnt) r[j] = load_rec<WORDS>(g, e);
+        for (int k0 = 0; k0 < ITEMS / 2; k0 += 4) {
+            if (uint32_t(k0 * THREADS) < npairs) {  // block-uniform: small segments skip the empty batches
+#pragma unroll
+                for (int k = k0; k < k0 + 4; ++k) {
+                    const uint32_t v = uint32_t(k * THREADS + tid);
+                    if (v < npairs) {
+                        const Vec2 x = gp[v];
+                        if constexpr (WORDS == 1) {
+                            r[2 * k].w[0] = x.x, r[2 * k + 1].w[0] = x.y;
+                        } else {
+                            r[2 * k].w[0] = x.x, r[2 * k].w[1] = x.y, r[2 * k + 1].w[0] = x.z, r[2 * k + 1].w[1] = x.w;
+                        }
+                        vmask |= 3u << (2 * k);
+                    }
+                }
+            }
+        }
+        if (tid == THREADS - 1) {
+            if (head) r[ITEMS - 2] = load_rec<WORDS>(g, 0), vmask |= 1u << (ITEMS - 2);
+            if ((cnt - head) & 1u) r[ITEMS - 1] = load_rec<WORDS>(g, cnt - 1), vmask |= 1u << (ITEMS - 1);
         }
     };
-    if (tid == 0) s_seg[0] = atomicAdd(p.ticket, 1u);
+
+    long long t_last = p.prof ? clock64() : 0;
+    auto tick = [&](int k) {
+        if (p.prof && tid == 0) {
+            const long long t = clock64();
+            atomicAdd(p.prof + k, (unsigned long long)(t - t_last));
+            t_last = t;
+        }
+    };
+    if (tid == 0) s_seg[0] = p.seg_first + atomicAdd(p.ticket, 1u);
     __syncthreads();
     uint32_t seg = s_seg[0];
     fetch(seg);
     while (seg < p.nseg) {
+        par ^= 1u;
+        volatile uint32_t* flag = s_seg + 4 * par;  // [2] long run seen, [3] slow
         if (tid == 0) {
-            s_seg[1] = atomicAdd(p.ticket, 1u);
-            s_seg[2] = 0;
-            s_seg[3] = 0;
+            s_seg[1] = p.seg_first + atomicAdd(p.ticket, 1u);
+            flag[2] = 0;
+            flag[3] = 0;
         }
         __syncthreads();  // (0) previous segment done, counters clean, next id visible
+        tick(0);
         const uint32_t next_seg = s_seg[1];
         if (cnt <= 1) {
             seg = next_seg;
@@ -126,87 +175,125 @@ __global__ void __launch_bounds__(THREADS, MINB) local_count_kernel(const LocalC
             __syncthreads();  // everyone has read the next id before thread 0 claims another one
             continue;
         }
-        const uint32_t cur_cnt = cnt, cur_seg = seg;
+        const uint32_t cur_cnt = cnt, cur_seg = seg, cur_head = head, mine = vmask;
         uint32_t* const cur_g = g;
-        // records this thread holds: elements tid, tid + THREADS, ...
-        const int mine = int((cur_cnt - uint32_t(tid) + THREADS - 1) / THREADS) * int(uint32_t(tid) < cur_cnt);
+        // staging positions are shifted by `head`, so that the aligned pairs of the write-out are aligned here too
+        uint32_t* const st = s_out + cur_head * WORDS;
+        auto key_at = [&](uint32_t i) { return key_image<WORDS, FLOATK>(load_rec<WORDS>(st, i), xorv); };
         // digit width of this segment: 2..4 counters per record, within [1, min(bmax, top_bit)]
         uint32_t b = 33u - uint32_t(__clz(int(cur_cnt - 1)));  // ceil(log2 cnt) + 1 for cnt >= 2
         b = b < p.bmax ? b : p.bmax;
         b = b < p.top_bit ? b : p.top_bit;
         const uint32_t shift = p.top_bit - b;
+        const bool exact = shift == 0;  // the digit is everything that is left of the key: no fix-up
         const uint32_t dmask = (1u << b) - 1u;
         const uint32_t NW = b ? (1u << (b - 1)) : 1u;  // packed counter words
         auto digit_of = [&](const Rec<WORDS>& x) { return uint32_t(key_image<WORDS, FLOATK>(x, xorv) >> shift) & dmask; };
 
         // ---- count ----
+        // (batches of 8 records = 4 pair slots; a batch no thread has records in is skipped: block-uniform test)
+        const uint32_t cur_pairs = (cur_cnt - cur_head) >> 1;
+        const bool leftovers = cur_head || ((cur_cnt - cur_head) & 1u);
+        auto batch_live = [&](int j0) { return uint32_t(j0 / 2 * THREADS) < cur_pairs || (j0 == ITEMS - 8 && leftovers); };
 #pragma unroll
-        for (int j = 0; j < ITEMS; ++j) {
-            if (j < mine) {
-                const uint32_t d = digit_of(r[j]);
-                red_add_shared(cnt_base + (d >> 1) * 4, 1u << ((d & 1u) * 16));
+        for (int j0 = 0; j0 < ITEMS; j0 += 8) {
+            if (batch_live(j0)) {
+#pragma unroll
+                for (int j = j0; j < j0 + 8; ++j) {
+                    if (mine >> j & 1u) {
+                        const uint32_t d = digit_of(r[j]);
+                        red_add_shared(cnt_base + (d >> 1) * 4, 1u << ((d & 1u) * 16));
+                    }
+                }
             }
         }
         __syncthreads();  // (1)
-        // ---- scan: counters := exclusive bases ----
+        tick(1);
+        // ---- scan: counters := exclusive bases; counters holding >= 2 records go to the run list ----
+        // The run list is private to the warp: a warp whose counters hold `t` records after `r` records of the
+        // warps before it lists at most t / 2 runs, in entries [r / 2, (r + t) / 2) — no shared counter.
+        // warp-collective: reserve `nr` consecutive entries for this lane, returns the first
+        uint32_t my_runs = 0, runs_at = 0;  // warp-uniform: entries written so far, first entry of my region
+        auto reserve = [&](uint32_t nr) -> uint32_t {
+            uint32_t incl = nr;
+#pragma unroll
+            for (int o = 1; o < 32; o <<= 1) {
+                const uint32_t y = __shfl_up_sync(0xffffffffu, incl, o);
+                if (lane >= o) incl += y;
+            }
+            const uint32_t first = runs_at + my_runs + incl - nr;
+            my_runs += __shfl_sync(0xffffffffu, incl, 31);
+            return first;
+        };
         const bool vec = NW >= uint32_t(WARPS) * 128u;  // block-uniform
         if (vec) {
             // every warp owns a contiguous run of words and walks it 128 words (one uint4 per lane) at a time
             const uint32_t per_warp = NW / WARPS;
             uint4* base4 = reinterpret_cast<uint4*>(s_cnt + uint32_t(warp) * per_warp);
             const uint32_t rounds = per_warp / 128;
-            uint32_t acc = 0, mx = 0;  // packed halves: per-lane sums stay below 2^16 (a segment has <= 16 384 records)
+            uint32_t acc = 0;  // packed halves: per-lane sums stay below 2^16 (a segment has <= 16 384 records)
             for (uint32_t q = 0; q < rounds; ++q) {
                 const uint4 v = base4[q * 32 + lane];
                 acc += v.x + v.y + v.z + v.w;
-                mx = __vmaxu2(mx, __vmaxu2(__vmaxu2(v.x, v.y), __vmaxu2(v.z, v.w)));
             }
             uint32_t tot = (acc & 0xffffu) + (acc >> 16);
 #pragma unroll
             for (int o = 16; o > 0; o >>= 1) tot += __shfl_xor_sync(0xffffffffu, tot, o);
             if (lane == 0) s_wtot[warp] = tot;
-            if (max(mx & 0xffffu, mx >> 16) > uint32_t(LC_MAXRUN)) s_seg[2] = 1;
             __syncthreads();  // (2)
-            uint32_t run = 0;  // records before this warp's words
+            uint32_t run = (lane < warp && lane < WARPS) ? s_wtot[lane] : 0u;  // records before this warp's words
 #pragma unroll
-            for (int w = 0; w < WARPS; ++w)
-                if (w < warp) run += s_wtot[w];
+            for (int o = 16; o > 0; o >>= 1) run += __shfl_xor_sync(0xffffffffu, run, o);
+            runs_at = run >> 1;
             for (uint32_t q = 0; q < rounds; ++q) {
                 uint4 v = base4[q * 32 + lane];
+                // word {c1:c0} -> {at + c0 : at}; counters with c >= 2 -> run list entries (static indices: registers)
+                uint32_t c[8], a8[9];
+                c[0] = v.x & 0xffffu, c[1] = v.x >> 16, c[2] = v.y & 0xffffu, c[3] = v.y >> 16;
+                c[4] = v.z & 0xffffu, c[5] = v.z >> 16, c[6] = v.w & 0xffffu, c[7] = v.w >> 16;
+                uint32_t nr = 0;
+                if (!exact) {
+#pragma unroll
+                    for (int k = 0; k < 8; ++k) nr += c[k] >= 2 ? 1u : 0u;
+                }
+                // one warp scan for both: {runs of this lane : records of this lane}
                 const uint32_t packed = v.x + v.y + v.z + v.w;
-                const uint32_t mysum = (packed & 0xffffu) + (packed >> 16);
-                uint32_t incl = mysum;
+                const uint32_t both = ((packed & 0xffffu) + (packed >> 16)) | (nr << 16);
+                uint32_t incl = both;
 #pragma unroll
                 for (int o = 1; o < 32; o <<= 1) {
                     const uint32_t y = __shfl_up_sync(0xffffffffu, incl, o);
                     if (lane >= o) incl += y;
                 }
-                uint32_t at = run + incl - mysum;
-                run += __shfl_sync(0xffffffffu, incl, 31);
-                // word {c1:c0} -> {at + c0 : at}; at += c0 + c1
-                uint32_t t;
-                t = v.x, v.x = at * 0x10001u + (t << 16), at += (t & 0xffffu) + (t >> 16);
-                t = v.y, v.y = at * 0x10001u + (t << 16), at += (t & 0xffffu) + (t >> 16);
-                t = v.z, v.z = at * 0x10001u + (t << 16), at += (t & 0xffffu) + (t >> 16);
-                t = v.w, v.w = at * 0x10001u + (t << 16);
+                const uint32_t excl = incl - both, tot = __shfl_sync(0xffffffffu, incl, 31);
+                a8[0] = run + (excl & 0xffffu);
+#pragma unroll
+                for (int k = 0; k < 8; ++k) a8[k + 1] = a8[k] + c[k];
+                v.x = a8[0] | (a8[1] << 16), v.y = a8[2] | (a8[3] << 16), v.z = a8[4] | (a8[5] << 16), v.w = a8[6] | (a8[7] << 16);
                 base4[q * 32 + lane] = v;
+                if (!exact) {
+                    uint32_t slot = runs_at + my_runs + (excl >> 16);
+#pragma unroll
+                    for (int k = 0; k < 8; ++k)
+                        if (c[k] >= 2) s_runs[slot++] = a8[k] | (c[k] << 16);
+                    my_runs += tot >> 16;
+                }
+                run += tot & 0xffffu;
             }
         } else {
             // small tables: thread t owns words [t * W, (t + 1) * W), walked from word (t mod W) on and around
             const uint32_t W = NW >= uint32_t(THREADS) ? NW / THREADS : 1u;
             const bool scanner = uint32_t(tid) < NW;
             const uint32_t w0 = uint32_t(tid) * W, rot = uint32_t(tid) & (W - 1);
-            uint32_t total = 0, wrapped = 0, mx = 0;  // wrapped = sum of the words before `rot`
+            uint32_t total = 0, wrapped = 0;  // wrapped = sum of the words before `rot`
             if (scanner) {
                 for (uint32_t k = 0; k < W; ++k) {
                     const uint32_t idx = (rot + k) & (W - 1);
                     const uint32_t v = s_cnt[w0 + idx];
                     const uint32_t lo = v & 0xffffu, hi = v >> 16;
-                    mx = max(mx, max(lo, hi));
                     total += lo + hi;
                     if (idx < rot) wrapped += lo + hi;
                 }
-                if (mx > uint32_t(LC_MAXRUN)) s_seg[2] = 1;
             }
             uint32_t incl = total;
 #pragma unroll
@@ -216,33 +303,43 @@ __global__ void __launch_bounds__(THREADS, MINB) local_count_kernel(const LocalC
             }
             if (lane == 31) s_wtot[warp] = incl;
             __syncthreads();  // (2)
-            if (scanner) {
-                uint32_t excl = incl - total;
+            uint32_t excl = incl - total, wbase = 0;
 #pragma unroll
-                for (int w = 0; w < WARPS; ++w)
-                    if (w < warp) excl += s_wtot[w];
-                uint32_t run = excl + wrapped;
-                for (uint32_t k = 0; k < W; ++k) {
-                    const uint32_t idx = (rot + k) & (W - 1);
-                    if (k && idx == 0) run = excl;  // wrapped around: back at the first word of my run
+            for (int w = 0; w < WARPS; ++w)
+                if (w < warp) wbase += s_wtot[w];
+            excl += wbase;
+            runs_at = wbase >> 1;
+            uint32_t run = excl + wrapped;
+            for (uint32_t k = 0; k < W; ++k) {  // W is block-uniform: the appends below are warp-collective
+                const uint32_t idx = (rot + k) & (W - 1);
+                if (k && idx == 0) run = excl;  // wrapped around: back at the first word of my run
+                uint32_t lo = 0, hi = 0, at = 0;
+                if (scanner) {
                     const uint32_t v = s_cnt[w0 + idx];
-                    const uint32_t lo = v & 0xffffu, hi = v >> 16;
+                    lo = v & 0xffffu, hi = v >> 16, at = run;
                     s_cnt[w0 + idx] = run | ((run + lo) << 16);
                     run += lo + hi;
+                }
+                if (!exact) {
+                    uint32_t slot = reserve((lo >= 2 ? 1u : 0u) + (hi >= 2 ? 1u : 0u));
+                    if (lo >= 2) s_runs[slot++] = at | (lo << 16);
+                    if (hi >= 2) s_runs[slot] = (at + lo) | (hi << 16);
                 }
             }
         }
         __syncthreads();  // (3)
-        // ---- scatter: the atomic hands out positions; afterwards counter d = end of digit d's run ----
-        // (in batches of 8: eight atomics in flight per thread before the first dependent store)
+        tick(2);
+        // ---- scatter: the atomic hands out positions (in batches of 8: eight atomics in flight per thread
+        // before the first dependent store) ----
 #pragma unroll
         for (int j0 = 0; j0 < ITEMS; j0 += 8) {
+            if (!batch_live(j0)) continue;
             uint32_t pos[8];
 #pragma unroll
             for (int u = 0; u < 8; ++u) {
                 const int j = j0 + u;
                 pos[u] = 0;
-                if (j < mine) {
+                if (mine >> j & 1u) {
                     const uint32_t d = digit_of(r[j]);
                     const uint32_t sh = (d & 1u) * 16;
                     pos[u] = (atom_add_shared(cnt_base + (d >> 1) * 4, 1u << sh) >> sh) & 0xffffu;
@@ -251,94 +348,83 @@ __global__ void __launch_bounds__(THREADS, MINB) local_count_kernel(const LocalC
 #pragma unroll
             for (int u = 0; u < 8; ++u) {
                 const int j = j0 + u;
-                if (j < mine) store_rec<WORDS>(s_out, pos[u], r[j]);
+                if (mine >> j & 1u) store_rec<WORDS>(st, pos[u], r[j]);
             }
         }
-        __syncthreads();  // (4)
-        const uint16_t* c16 = reinterpret_cast<const uint16_t*>(s_cnt);
-        if (shift != 0 && s_seg[2]) {
-            // a run longer than LC_MAXRUN: fine if all its keys are equal (nothing to order), else the
-            // stable segment sort takes this segment
-            const uint32_t NC = dmask + 1u;
-            for (uint32_t d0 = uint32_t(warp) * 32; d0 < NC; d0 += WARPS * 32) {
-                const uint32_t d = d0 + lane;
-                uint32_t start = 0, end = 0;
-                if (d < NC) {
-                    end = c16[d];
-                    start = d ? c16[d - 1] : 0u;
+        __syncthreads();  // (4) the staging buffer is sorted by the digit; the run list is complete
+        tick(3);
+        // ---- prefetch the next segment ----
+        seg = next_seg;
+        fetch(seg);
+        tick(4);
+        // ---- fix-up: one thread per run of records that share a digit, ordered by the whole key ----
+        // (every warp works through its own list)
+        const uint32_t nruns = exact ? 0u : my_runs;
+        for (uint32_t q = lane; q < nruns; q += 32) {
+            const uint32_t e = s_runs[runs_at + q], at = e & 0xffffu, c = e >> 16;
+            if (c == 2) {
+                const Rec<WORDS> x = load_rec<WORDS>(st, at), y = load_rec<WORDS>(st, at + 1);
+                if (key_image<WORDS, FLOATK>(y, xorv) < key_image<WORDS, FLOATK>(x, xorv)) {
+                    store_rec<WORDS>(st, at, y);
+                    store_rec<WORDS>(st, at + 1, x);
                 }
-                uint32_t m = __ballot_sync(0xffffffffu, end - start > uint32_t(LC_MAXRUN));
+            } else if (c <= uint32_t(LC_MAXRUN)) {
+                for (uint32_t a = at + 1; a < at + c; ++a) {  // insertion sort
+                    const Rec<WORDS> x = load_rec<WORDS>(st, a);
+                    const KT kx = key_image<WORDS, FLOATK>(x, xorv);
+                    uint32_t j = a;
+                    while (j > at) {
+                        const Rec<WORDS> y = load_rec<WORDS>(st, j - 1);
+                        if (key_image<WORDS, FLOATK>(y, xorv) <= kx) break;
+                        store_rec<WORDS>(st, j, y);
+                        --j;
+                    }
+                    if (j != a) store_rec<WORDS>(st, j, x);
+                }
+            } else {
+                flag[2] = 1;  // a long run: checked below
+            }
+        }
+        __syncthreads();  // (5)
+        tick(5);
+        if (flag[2]) {
+            // runs longer than LC_MAXRUN: fine if all their keys are equal (heavy duplicates: nothing to order),
+            // else the stable segment sort takes this segment
+            for (uint32_t q0 = 0; q0 < nruns; q0 += 32) {
+                const uint32_t e = q0 + lane < nruns ? s_runs[runs_at + q0 + lane] : 0u;
+                uint32_t m = __ballot_sync(0xffffffffu, (e >> 16) > uint32_t(LC_MAXRUN));
                 while (m) {
                     const int src = __ffs(m) - 1;
                     m &= m - 1;
-                    const uint32_t s = __shfl_sync(0xffffffffu, start, src), e = __shfl_sync(0xffffffffu, end, src);
-                    const KT k0 = key_image<WORDS, FLOATK>(load_rec<WORDS>(s_out, s), xorv);
+                    const uint32_t ee = __shfl_sync(0xffffffffu, e, src), at = ee & 0xffffu, c = ee >> 16;
+                    const KT k0 = key_at(at);
                     bool same = true;
-                    for (uint32_t i = s + 1 + lane; i < e; i += 32)
-                        same = same && key_image<WORDS, FLOATK>(load_rec<WORDS>(s_out, i), xorv) == k0;
-                    if (!__all_sync(0xffffffffu, same) && lane == 0) s_seg[3] = 1;
+                    for (uint32_t i = at + 1 + lane; i < at + c; i += 32) same = same && key_at(i) == k0;
+                    if (!__all_sync(0xffffffffu, same) && lane == 0) flag[3] = 1;
                 }
             }
             __syncthreads();
         }
-        const bool slow = s_seg[3] != 0;
-        // ---- prefetch the next segment, then fix-up + write-out ----
-        seg = next_seg;
-        fetch(seg);
-        if (slow) {
+        // ---- write-out ----
+        if (flag[3]) {
             if (tid == 0) {
                 const uint32_t at = atomicAdd(p.slow_list, 1u);
                 p.slow_list[1 + at] = cur_seg;
             }
-        } else if (shift == 0) {
-            // the digit was everything that was left of the key: the staging buffer is sorted
-            for (uint32_t i = tid; i < cur_cnt; i += THREADS) store_rec<WORDS>(cur_g, uint64_t(i), load_rec<WORDS>(s_out, i));
         } else {
-            // four records per thread and trip, loads first: the run bounds and the neighbours' keys are
-            // chains of dependent shared-memory loads
-            constexpr int FB = 4;
-            for (uint32_t i0 = tid; i0 < cur_cnt; i0 += FB * THREADS) {
-                Rec<WORDS> x[FB];
-                KT kx[FB];
-                uint32_t start[FB], end[FB];
-#pragma unroll
-                for (int u = 0; u < FB; ++u) {
-                    const uint32_t i = i0 + u * THREADS;
-                    if (i < cur_cnt) x[u] = load_rec<WORDS>(s_out, i);
-                }
-#pragma unroll
-                for (int u = 0; u < FB; ++u) {
-                    const uint32_t i = i0 + u * THREADS;
-                    start[u] = end[u] = 0;
-                    kx[u] = 0;
-                    if (i < cur_cnt) {
-                        kx[u] = key_image<WORDS, FLOATK>(x[u], xorv);
-                        const uint32_t d = uint32_t(kx[u] >> shift) & dmask;
-                        end[u] = c16[d];
-                        start[u] = d ? c16[d - 1] : 0u;
-                    }
-                }
-#pragma unroll
-                for (int u = 0; u < FB; ++u) {
-                    const uint32_t i = i0 + u * THREADS;
-                    if (i < cur_cnt) {
-                        uint32_t pos = i;
-                        const uint32_t c = end[u] - start[u];
-                        if (c > 1 && c <= uint32_t(LC_MAXRUN)) {
-                            pos = start[u];
-                            for (uint32_t j = start[u]; j < end[u]; ++j) {
-                                const KT ky = key_image<WORDS, FLOATK>(load_rec<WORDS>(s_out, j), xorv);
-                                pos += (ky < kx[u] || (ky == kx[u] && j < i)) ? 1u : 0u;
-                            }
-                        }
-                        store_rec<WORDS>(cur_g, uint64_t(pos), x[u]);
-                    }
-                }
-            }
+            // aligned pairs: one vector load from the staging buffer, one vector store
+            const uint32_t npairs = (cur_cnt - cur_head) >> 1;
+            Vec2* gp = reinterpret_cast<Vec2*>(cur_g + cur_head * WORDS);
+            const Vec2* sp = reinterpret_cast<const Vec2*>(s_out + 2 * cur_head * WORDS);  // = st + head: record `head`
+            for (uint32_t v = tid; v < npairs; v += THREADS) gp[v] = sp[v];
+            if (tid == 0 && cur_head) store_rec<WORDS>(cur_g, 0, load_rec<WORDS>(st, 0));
+            if (tid == 32 % THREADS && ((cur_cnt - cur_head) & 1u)) store_rec<WORDS>(cur_g, uint64_t(cur_cnt - 1), load_rec<WORDS>(st, cur_cnt - 1));
         }
-        __syncthreads();  // (5) counters no longer read
+        tick(6);
+        // the counters are dead since barrier (4); barrier (0) of the next trip orders this against the next count
         for (uint32_t i = tid; i < NW / 4; i += THREADS) reinterpret_cast<uint4*>(s_cnt)[i] = make_uint4(0, 0, 0, 0);
         if (NW < 4 && uint32_t(tid) < NW) s_cnt[tid] = 0;
+        tick(7);
     }
 }
 

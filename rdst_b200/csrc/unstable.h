@@ -20,8 +20,8 @@ struct MsdULaunch {
 MsdULaunch get_msdu_launch_w1(bool floatk, int variant);
 MsdULaunch get_msdu_launch_w2(bool floatk, int variant);
 
-// K3-U comes in two sizes: `small` = 128 threads, segments <= 4096 records, several CTAs per SM;
-// otherwise 512 threads, segments <= 16384 records, one CTA per SM.
+// K3-U comes in three sizes: 0 = 128 threads, segments <= 4096 records, several CTAs per SM; 1 = 256 threads,
+// <= 8192 records, two CTAs per SM; 2 = 512 threads, <= 16384 records, one CTA per SM.
 struct LocalCountLaunch {
     void (*kernel)(const LocalCountParams);
     size_t smem;
@@ -29,6 +29,6 @@ struct LocalCountLaunch {
     int cap;    // records per segment
     int cbits;  // widest digit
 };
-LocalCountLaunch get_local_count_launch_w1(bool floatk, bool small);
-LocalCountLaunch get_local_count_launch_w2(bool floatk, bool small);
+LocalCountLaunch get_local_count_launch_w1(bool floatk, int size, bool wide);
+LocalCountLaunch get_local_count_launch_w2(bool floatk, int size, bool wide);
 }  // namespace b200

@@ -38,11 +38,11 @@ static MsdULaunch pick_msdu(int variant) {
     return MsdULaunch{};
 }
 
-template <int WORDS, bool FLOATK, int THREADS, int CBITS, int MINB>
+template <int WORDS, bool FLOATK, int THREADS, int ITEMS, int CBITS, int MINB>
 static LocalCountLaunch make_local_count() {
-    using SM = LocalCountSmem<WORDS, THREADS, CBITS>;
+    using SM = LocalCountSmem<WORDS, THREADS, ITEMS, CBITS>;
     LocalCountLaunch l{};
-    l.kernel = &local_count_kernel<WORDS, FLOATK, THREADS, CBITS, MINB>;
+    l.kernel = &local_count_kernel<WORDS, FLOATK, THREADS, ITEMS, CBITS, MINB>;
     l.smem = SM::TOTAL;
     l.threads = THREADS;
     l.cap = SM::CAP;
@@ -50,9 +50,21 @@ static LocalCountLaunch make_local_count() {
     return l;
 }
 
+// size 0 / 1 / 2 = segments of <= 4096 / 8192 / 16384 records; wide = twice the threads with half the records each
 template <int WORDS, bool FLOATK>
-static LocalCountLaunch pick_local_count(bool small) {
-    return small ? make_local_count<WORDS, FLOATK, 128, 13, 4>() : make_local_count<WORDS, FLOATK, 512, 15, 1>();
+static LocalCountLaunch pick_local_count(int size, bool wide) {
+    if (wide) {
+        switch (size) {
+            case 0: return make_local_count<WORDS, FLOATK, 256, 16, 13, 4>();
+            case 1: return make_local_count<WORDS, FLOATK, 512, 16, 14, 2>();
+            default: return make_local_count<WORDS, FLOATK, 1024, 16, 15, 1>();
+        }
+    }
+    switch (size) {
+        case 0: return make_local_count<WORDS, FLOATK, 128, 32, 13, 4>();
+        case 1: return make_local_count<WORDS, FLOATK, 256, 32, 14, 2>();
+        default: return make_local_count<WORDS, FLOATK, 512, 32, 15, 1>();
+    }
 }
 
 }  // namespace b200

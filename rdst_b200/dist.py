@@ -24,6 +24,56 @@ from .radix_key import RadixKey
 
 
 # --------------------------------------------------------------------------- host logic
+# The exchange planner lives in the C library (csrc/multi.cu: b200_multi_plan_*), shared with the single-process
+# entry points b200_sort_multi_*; plan_digits / plan_sample_splitters / plan_splitters below call it.  The numpy
+# functions that follow are the MODEL of the same rules: the CPU test double of tests/test_dist_gloo.py runs on
+# them, and tests/test_multi_plan_cpu.py checks that the C planner agrees with them case by case.
+def plan_digits(all_hist: np.ndarray):
+    """[P, L, 256] K1 histograms -> (level, split[P-1], send matrix [P, P], imbalance) from the C planner."""
+    lib = _abi.lib()
+    h = np.ascontiguousarray(all_hist, dtype=np.uint64)
+    P, L = h.shape[0], h.shape[1]
+    level = C.c_int32()
+    split = np.zeros(max(1, P - 1), dtype=np.uint32)
+    m = np.zeros((P, P), dtype=np.int64)
+    imb = C.c_double(1.0)
+    _abi.check(lib.b200_multi_plan_digits(h.ctypes.data_as(C.POINTER(C.c_uint64)), P, L, C.byref(level),
+                                          split.ctypes.data_as(C.POINTER(C.c_uint32)),
+                                          m.ctypes.data_as(C.POINTER(C.c_int64)), C.byref(imb)))
+    return int(level.value), split[: P - 1], m, float(imb.value)
+
+
+def plan_sample_splitters(samples: np.ndarray, weights: np.ndarray, parts: int) -> np.ndarray:
+    lib = _abi.lib()
+    v = np.ascontiguousarray(samples, dtype=np.uint64)
+    w = np.ascontiguousarray(weights, dtype=np.float64)
+    out = np.zeros(parts - 1, dtype=np.uint64)
+    _abi.check(lib.b200_multi_choose_sample_splitters(v.ctypes.data_as(C.POINTER(C.c_uint64)),
+                                                      w.ctypes.data_as(C.POINTER(C.c_double)), len(v), parts,
+                                                      out.ctypes.data_as(C.POINTER(C.c_uint64))))
+    return out
+
+
+def plan_splitters(less: np.ndarray, equal: np.ndarray, n_per_rank: np.ndarray, splitters: np.ndarray, parts: int,
+                   exact_ties: bool = True):
+    """-> (tie thresholds t[P-1], send matrix [R, P], incl masks [R]) from the C planner."""
+    lib = _abi.lib()
+    le = np.ascontiguousarray(less, dtype=np.int64)
+    eq = np.ascontiguousarray(equal, dtype=np.int64)
+    npr = np.ascontiguousarray(n_per_rank, dtype=np.int64)
+    sp = np.ascontiguousarray(splitters, dtype=np.uint64)
+    R = le.shape[0]
+    t = np.zeros(parts - 1, dtype=np.int64)
+    m = np.zeros((R, parts), dtype=np.int64)
+    masks = np.zeros(R, dtype=np.uint32)
+    i64 = C.POINTER(C.c_int64)
+    _abi.check(lib.b200_multi_plan_splitters(le.ctypes.data_as(i64), eq.ctypes.data_as(i64), npr.ctypes.data_as(i64),
+                                             sp.ctypes.data_as(C.POINTER(C.c_uint64)), R, parts, 1 if exact_ties else 0,
+                                             t.ctypes.data_as(i64), m.ctypes.data_as(i64),
+                                             masks.ctypes.data_as(C.POINTER(C.c_uint32))))
+    return t, m, masks
+
+
 def pick_partition_level(global_hist: np.ndarray) -> int:
     """Most significant level whose global histogram is not a single bucket (rdst's
     trivial-level skip, reference src/sorts/ska_sort.rs:52-54, applied to the splitters).
@@ -154,6 +204,7 @@ class CudaEngine:
         self.desc = key.to_desc()
         self.lib = _abi.lib()
         self.launches = 0
+        self.c_planner = True
 
     def _opts(self):
         o = _abi.SortOpts()
@@ -161,6 +212,7 @@ class CudaEngine:
         o.variant = -1
         o.device = self.torch.cuda.current_device()
         o.stream = _abi.torch_stream_handle(self.torch)
+        o.route = 0
         return o
 
     def empty(self, n_records):
@@ -394,7 +446,9 @@ def sharded_sort(local, n_local: int, key: RadixKey, engine=None, group=None, re
                  and key.elem_size <= 16)
     bounds = hist_c = None
     if pipelined:
-        bounds = [(n_local * c) // ce_chunks for c in range(ce_chunks + 1)]
+        # interior chunk bounds on multiples of 16 records: every supported record size then starts a chunk on a
+        # 16-byte boundary, which the word kernels and the fast histogram need
+        bounds = [min(n_local, ((n_local * c) // ce_chunks) // 16 * 16) for c in range(ce_chunks)] + [n_local]
         es = key.elem_size
         hist_c = [eng.histogram(local[bounds[c] * es: bounds[c + 1] * es], bounds[c + 1] - bounds[c]) for c in range(ce_chunks)]
         hist = np.sum(hist_c, axis=0).astype(np.uint64)
@@ -405,13 +459,17 @@ def sharded_sort(local, n_local: int, key: RadixKey, engine=None, group=None, re
     gathered = [mine.new_empty(mine.shape) for _ in range(world)]
     dist.all_gather(gathered, mine, group=group)
     all_hist = np.stack([g.cpu().numpy() for g in gathered])  # [P, L, 256]
-    global_hist = all_hist.sum(axis=0)
-    level = pick_partition_level(global_hist)
+    c_planner = getattr(eng, "c_planner", False)  # product engine: the planner of the C library
+    if c_planner:
+        level, split, m, _imb = plan_digits(all_hist)
+    else:
+        level = pick_partition_level(all_hist.sum(axis=0))
     if level < 0:
         return local, n_local  # every key equal: any arrangement is sorted
     # 3. splitters on digit boundaries of that level
-    split = choose_splitters(global_hist[level], world)
-    m = send_matrix(all_hist[:, level, :], split, world)
+    if not c_planner:
+        split = choose_splitters(all_hist.sum(axis=0)[level], world)
+        m = send_matrix(all_hist[:, level, :], split, world)
     # 3b. skewed keys: digit boundaries cannot balance the ranks -> full-resolution splitters
     splitters = t_thr = None
     import time as _time
@@ -438,7 +496,7 @@ def sharded_sort(local, n_local: int, key: RadixKey, engine=None, group=None, re
             if c:
                 vals.append(a[1: 1 + c].view(np.uint64))
                 wts.append(np.full(c, n_per_rank[r] / c))
-        splitters = choose_sample_splitters(np.concatenate(vals), np.concatenate(wts), world)
+        splitters = (plan_sample_splitters if c_planner else choose_sample_splitters)(np.concatenate(vals), np.concatenate(wts), world)
         plan_t["gather_choose_ms"] = (_time.perf_counter() - _t0) * 1e3
         _t0 = _time.perf_counter()
         less, equal = eng.splitter_count(local, n_local, splitters)
@@ -448,8 +506,12 @@ def sharded_sort(local, n_local: int, key: RadixKey, engine=None, group=None, re
         gc = [mine_c.new_empty(mine_c.shape) for _ in range(world)]
         dist.all_gather(gc, mine_c, group=group)
         allc = np.stack([g.cpu().numpy() for g in gc])  # [P, 2, P-1]
-        t_thr, m = plan_splitter_exchange(allc[:, 0, :], allc[:, 1, :], n_per_rank, splitters, world,
-                                          exact_ties=key.levels <= 8)
+        if c_planner:
+            t_thr, m, _masks = plan_splitters(allc[:, 0, :], allc[:, 1, :], n_per_rank, splitters, world,
+                                              exact_ties=key.levels <= 8)
+        else:
+            t_thr, m = plan_splitter_exchange(allc[:, 0, :], allc[:, 1, :], n_per_rank, splitters, world,
+                                              exact_ties=key.levels <= 8)
         plan_t["gather_plan_ms"] = (_time.perf_counter() - _t0) * 1e3
     send_counts, recv_counts = m[rank], m[:, rank]
     n_recv = int(recv_counts.sum())

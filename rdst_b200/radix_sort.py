@@ -16,8 +16,8 @@ import numpy as np
 
 from . import _abi
 from .radix_key import RadixKey, key_for_array
-from .tuner import (ALGORITHM_VARIANT, STABLE_ALGORITHMS, LowMemoryTuner, SingleThreadedTuner, StandardTuner, Tuner,
-                    TuningParams)
+from .tuner import (ALGORITHM_ROUTE, HINT_LOW_SCRATCH, STABLE_ALGORITHMS, LowMemoryTuner, SingleThreadedTuner,
+                    StandardTuner, Tuner, TuningParams)
 
 _STANDARD = StandardTuner()
 _LOW_MEM = LowMemoryTuner()
@@ -79,6 +79,9 @@ class RadixSortBuilder:
         return self
 
     def with_low_mem_tuner(self):  # :86-90
+        """LowMemoryTuner answers Ska / Regions for anything large (reference low_memory_tuner.rs:13-43): the
+        engine's low-scratch route — LSD passes with the small-tile variant, scratch pool released after the
+        call.  Peak scratch is still one copy of the array (there is no in-place pass on the device)."""
         self._tuner = _LOW_MEM
         return self
 
@@ -97,8 +100,9 @@ class RadixSortBuilder:
         return self
 
     def with_stable(self, stable: bool = True):
-        """Ask for rdst's stable order (what Lsb / LrLsb / MtLsb produce).  The engine is a
-        stable LSD sort in every mode; the flag is recorded in the options."""
+        """Ask for rdst's stable order (what Lsb / LrLsb / MtLsb produce).  Records with a payload are sorted
+        stably in every mode; records that are nothing but their key take the unstable kernels, whose
+        result is bit-identical (equal keys are identical records)."""
         self._stable = bool(stable)
         return self
 
@@ -117,8 +121,9 @@ class RadixSortBuilder:
         custom = self._tuner not in (_STANDARD, _LOW_MEM, _SINGLE)
         if custom:
             return self._sort_with_custom_tuner(lib, desc, opts, stats, n, on_device)
+        opts.route = 0
         if self._tuner is _LOW_MEM and self._variant < 0:
-            opts.variant = -2  # library's low-scratch choice
+            opts.route = HINT_LOW_SCRATCH
         if on_device:
             import torch
 
@@ -152,8 +157,7 @@ class RadixSortBuilder:
             p = TuningParams(threads=torch.cuda.get_device_properties(dev).multi_processor_count, level=L - 1,
                              total_levels=L, input_len=n, parent_len=None)
             algo = self._tuner.pick_algorithm(p, top)
-            if self._variant < 0:
-                opts.variant = ALGORITHM_VARIANT.get(algo, -1)
+            opts.route = ALGORITHM_ROUTE.get(algo, 0) if self._variant < 0 else 0
             if algo in STABLE_ALGORITHMS:
                 opts.stable = 1
             _abi.check(lib.b200_sort_device(t.data_ptr(), None, n, C.byref(desc), C.byref(opts), C.byref(stats)))
@@ -161,7 +165,31 @@ class RadixSortBuilder:
                 host.copy_(t)
         self.stats = stats.as_dict()
         self.stats["algorithm"] = algo.name
+        self.stats["route_hint"] = int(opts.route)
         return None
+
+
+def sort_multi_host(data, key: RadixKey | None = None, gpus=None):
+    """Sort a host array over several GPUs of this box in ONE process (b200_sort_multi_host): the array is cut
+    into len(gpus) shards, every GPU pulls its shard over its own PCIe link, the shards are range-partitioned
+    over NVLink (fused partition + exchange) and sorted locally, and the sorted ranges are written back in
+    place.  The multi-GPU form of `radix_sort_unstable` on a host `&mut [T]`; returns the b200_multi_stats dict."""
+    key = key_for_array(data, key)
+    if key.levels == 0:
+        raise _abi.LevelsZeroError(1, "RadixKey must have at least 1 level")
+    ptr, n, on_device, _, _keep = _buffer_info(data, key)
+    if on_device:
+        raise ValueError("sort_multi_host takes a host array")
+    lib = _abi.lib()
+    if gpus is None:
+        import torch
+
+        gpus = list(range(torch.cuda.device_count()))
+    devs = (C.c_int * len(gpus))(*gpus)
+    desc = key.to_desc()
+    st = _abi.MultiStats()
+    _abi.check(lib.b200_sort_multi_host(ptr, n, len(gpus), devs, C.byref(desc), None, C.byref(st)))
+    return st.as_dict()
 
 
 def radix_sort_builder(data, key: RadixKey | None = None) -> RadixSortBuilder:

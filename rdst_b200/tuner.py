@@ -1,11 +1,13 @@
 """tuner — the reference's Tuner API (reference src/tuner.rs:1-40), re-purposed.
 
 In the reference a Tuner picks one of nine CPU algorithms per chunk and recursion level
-(reference src/sorter.rs:67-76).  On the GPU there is one algorithm — a stable LSD sweep —
-so a Tuner is asked ONCE per sort, with the top level's 256 counts (from the K1
-histogram), and its answer only selects the tile / occupancy variant of the pass kernel.
-`Algorithm` keeps the reference's names so user tuners keep compiling; every name maps to
-a variant of the same kernel (see ALGORITHM_VARIANT).
+(reference src/sorter.rs:67-76).  The device engine does not recurse, so a Tuner is asked ONCE
+per sort — with TuningParams for the top level and that level's 256 counts, from the K1
+histogram — and its answer selects the engine's route (ALGORITHM_ROUTE): the stable LSB family
+forces LSD passes, the in-place family the low-scratch route, everything else leaves the choice
+to the planner.  b200_stats (hybrid, levels_run, variant) shows what ran.  The built-in tuners
+keep the reference's threshold tables, so the Algorithm reported for a given (len, counts) is
+the reference's.
 """
 from __future__ import annotations
 
@@ -35,19 +37,23 @@ class Algorithm(enum.Enum):  # reference src/tuner.rs:10-21 (multi-threaded feat
     Ska = 8
 
 
-# -1 = let the library pick.  All algorithms yield rdst's stable LSD order; the in-place
-# family (Ska / Regions, what LowMemoryTuner prefers) maps to the smaller-tile variant
-# whose look-back array and staging use less scratch.
-ALGORITHM_VARIANT = {
-    Algorithm.MtOop: -1,
-    Algorithm.MtLsb: -1,
-    Algorithm.Scanning: -1,
-    Algorithm.Recombinating: -1,
-    Algorithm.Comparative: -1,
-    Algorithm.LrLsb: -1,
-    Algorithm.Lsb: -1,
-    Algorithm.Regions: -1,
-    Algorithm.Ska: -1,
+# What each Algorithm means to the device engine (include/b200sort.h b200_route_hint).  rdst's nine
+# algorithms are CPU strategies; on the GPU they collapse to three observable choices:
+#   the stable LSB family            -> LSD passes only, stable order   (b200_stats.hybrid == 0)
+#   the in-place family (Ska/Regions, what LowMemoryTuner prefers, reference low_memory_tuner.rs:13-43)
+#                                    -> LSD passes, small-tile variant, scratch pool released after the call
+#   the out-of-place MSB-first ones  -> the planner's own choice (hybrid MSD route when the input qualifies)
+HINT_AUTO, HINT_LSD, HINT_LOW_SCRATCH = 0, 1, 2
+ALGORITHM_ROUTE = {
+    Algorithm.MtOop: HINT_AUTO,
+    Algorithm.Scanning: HINT_AUTO,
+    Algorithm.Recombinating: HINT_AUTO,
+    Algorithm.Comparative: HINT_AUTO,
+    Algorithm.MtLsb: HINT_LSD,
+    Algorithm.LrLsb: HINT_LSD,
+    Algorithm.Lsb: HINT_LSD,
+    Algorithm.Regions: HINT_LOW_SCRATCH,
+    Algorithm.Ska: HINT_LOW_SCRATCH,
 }
 
 STABLE_ALGORITHMS = {Algorithm.Lsb, Algorithm.LrLsb, Algorithm.MtLsb}  # reference lsb_sort.rs:5-7, mt_lsb_sort.rs:12-15

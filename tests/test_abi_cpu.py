@@ -45,8 +45,10 @@ def test_version_and_variants():
 def test_struct_layouts_match_header():
     assert C.sizeof(_abi.Level) == 4
     assert C.sizeof(_abi.KeyDesc) == 24 + 4 * 64
-    assert C.sizeof(_abi.SortOpts) == 24
+    assert C.sizeof(_abi.SortOpts) == 32 and _abi.SortOpts.route.offset == 24
     assert _abi.Stats.algorithmic_bytes.offset == 16
+    assert C.sizeof(_abi.Stats) == 88 and _abi.Stats.unstable.offset == 84
+    assert C.sizeof(_abi.MultiStats) == 272 and _abi.MultiStats.local0.offset == 184
 
 
 KEYS = [RadixKey.for_dtype(d) for d in ("u1", "u2", "u4", "u8", "i1", "i2", "i4", "i8", "f4", "f8")] + [
@@ -129,3 +131,32 @@ def test_tuner_tables_match_the_oracle_restatement():
     assert st.pick_algorithm(tuner.TuningParams(8, 7, 8, 6_000_000, None), skew) is tuner.Algorithm.Regions
     assert lm.pick_algorithm(p, flat) is tuner.Algorithm.Regions
     assert sg.pick_algorithm(tuner.TuningParams(1, 3, 4, 900_000, None), flat) is tuner.Algorithm.Ska
+
+
+def test_every_algorithm_maps_to_a_route_hint():
+    """The policy hook (reference src/tuner.rs:33-35) has an observable meaning on the device: the stable LSB
+    family forces LSD passes, the in-place family the low-scratch route, the rest leaves it to the planner."""
+    assert set(tuner.ALGORITHM_ROUTE) == set(tuner.Algorithm)
+    for a in (tuner.Algorithm.Lsb, tuner.Algorithm.LrLsb, tuner.Algorithm.MtLsb):
+        assert tuner.ALGORITHM_ROUTE[a] == _abi.HINT_LSD and a in tuner.STABLE_ALGORITHMS
+    for a in (tuner.Algorithm.Ska, tuner.Algorithm.Regions):
+        assert tuner.ALGORITHM_ROUTE[a] == _abi.HINT_LOW_SCRATCH
+    for a in (tuner.Algorithm.Scanning, tuner.Algorithm.Recombinating, tuner.Algorithm.MtOop, tuner.Algorithm.Comparative):
+        assert tuner.ALGORITHM_ROUTE[a] == _abi.HINT_AUTO
+    # an unknown hint is rejected before anything runs
+    d = RadixKey.for_dtype("u4").to_desc()
+    o_ = _abi.SortOpts()
+    o_.variant, o_.device, o_.route = -1, -1, 7
+    assert _abi.lib().b200_sort_device(None, None, 10, C.byref(d), C.byref(o_), None) == 6  # B200_ERR_BAD_ARG
+
+
+def test_multi_gpu_entry_points_validate_arguments_without_a_device():
+    l = _abi.lib()
+    d = RadixKey.for_dtype("u8").to_desc()
+    assert l.b200_sort_multi_host(None, 0, 0, None, C.byref(d), None, None) == 6     # ngpus < 1
+    assert l.b200_sort_multi_host(None, 0, 17, None, C.byref(d), None, None) == 6    # ngpus > B200_MAX_GPUS
+    z = RadixKey.for_dtype("u8", levels=0).to_desc()
+    assert l.b200_sort_multi_host(None, 0, 2, None, C.byref(z), None, None) == 1     # LEVELS == 0
+    odd = RadixKey.byte_array(5).to_desc()
+    assert l.b200_sort_multi_host(None, 0, 2, None, C.byref(odd), None, None) == 2   # records of 4..16 bytes, multiple of 4
+    assert l.b200_multi_release() == 0

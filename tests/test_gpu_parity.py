@@ -520,6 +520,175 @@ def test_config4_struct_100m_stable_property():
     _abi.lib().b200_release_scratch(-1)
 
 
+def _float_image(torch, t):
+    """Order-preserving integer image of IEEE bit patterns held in an int tensor (total order, reference
+    src/radix_key_impl.rs:162-185): negative -> all bits flipped, else the sign bit flipped; compared as signed
+    after flipping the sign bit back, i.e. plain `t` for non-negative and `~t ^ MIN` for negative patterns."""
+    mn = -2**63 if t.dtype == torch.int64 else -2**31
+    return torch.where(t < 0, ~t ^ mn, t)
+
+
+def test_config3_f32_500m_properties():
+    """BASELINE configs[2], first half: 500 M f32 random bit patterns (about half negative), NaN- and Inf-free.
+    Sortedness under the float total order, multiset checksums, and exact equality with the oracle on a
+    2 M-record slice of the same generator."""
+    torch = torch_mod()
+    g = torch.Generator(device="cuda").manual_seed(0x5EED0003)
+    n = 500_000_000
+    t = torch.randint(-2**31, 2**31, (n,), dtype=torch.int32, device="cuda", generator=g)
+    t = torch.where(((t >> 23) & 0xFF) == 0xFF, t & -2139095041, t)  # clear the exponent of NaN / Inf patterns
+    assert 0.45 < float((t < 0).float().mean()) < 0.55
+    small = t[:2_000_000].cpu().numpy().view("f4")
+    chk = int(t.to(torch.int64).sum()), int((t.to(torch.int64) * 0x9E3779B1 ^ (t.to(torch.int64) >> 7)).sum())
+    key = RadixKey.for_dtype("f4")
+    b = radix_sort_builder(t, key)
+    b.sort()
+    torch.cuda.synchronize()
+    img = _float_image(torch, t)
+    assert bool((img[1:] >= img[:-1]).all())
+    del img
+    assert chk == (int(t.to(torch.int64).sum()), int((t.to(torch.int64) * 0x9E3779B1 ^ (t.to(torch.int64) >> 7)).sum()))
+    h = small.copy()
+    radix_sort_unstable(h)
+    assert h.tobytes() == o.sorted_copy(small, key).tobytes()
+    _abi.lib().b200_release_scratch(-1)
+
+
+def test_config3_i64_500m_properties():
+    """BASELINE configs[2], second half: 500 M i64 including negatives."""
+    torch = torch_mod()
+    g = torch.Generator(device="cuda").manual_seed(0x5EED0013)
+    n = 500_000_000
+    t = torch.randint(-2**63, 2**63 - 1, (n,), dtype=torch.int64, device="cuda", generator=g)
+    small = t[:2_000_000].cpu().numpy().view("i8")
+    chk = int(t.sum()), int((t ^ (t >> 9)).sum())
+    key = RadixKey.for_dtype("i8")
+    b = radix_sort_builder(t, key)
+    b.sort()
+    torch.cuda.synchronize()
+    assert b.stats["hybrid"] == 1 and b.stats["unstable"] & 1, b.stats  # key-only route at this size
+    assert bool((t[1:] >= t[:-1]).all())
+    assert chk == (int(t.sum()), int((t ^ (t >> 9)).sum()))
+    h = small.copy()
+    radix_sort_unstable(h)
+    assert h.tobytes() == o.sorted_copy(small, key).tobytes()
+    _abi.lib().b200_release_scratch(-1)
+
+
+def test_config4_struct_1b_stable_property():
+    """BASELINE configs[3] at its stated size: 1 B records {u32 key (LEVELS = 3), 8-byte payload = input index},
+    12 GB + 12 GB of scratch.  Stable <=> within equal keys the payload indices ascend; every index survives."""
+    torch = torch_mod()
+    g = torch.Generator(device="cuda").manual_seed(0x5EED0014)
+    n = 1_000_000_000
+    rec = torch.empty((n, 3), dtype=torch.int32, device="cuda")
+    step = 1 << 28
+    for i in range(0, n, step):  # in slices: no 4 GB temporaries next to the 12 GB array
+        j = min(n, i + step)
+        rec[i:j, 0] = torch.randint(0, 1 << 24, (j - i,), dtype=torch.int32, device="cuda", generator=g)
+        rec[i:j, 1] = torch.arange(i, j, dtype=torch.int32, device="cuda")
+    rec[:, 2] = 0
+    b = radix_sort_builder(rec, RadixKey("uint", 12, 3, 0, 4)).with_stable(True)
+    b.sort()
+    torch.cuda.synchronize()
+    assert b.stats["levels_run"] == 3 and b.stats["unstable"] == 0, b.stats
+    ok, idx_sum = True, 0
+    for i in range(0, n - 1, step):
+        j = min(n - 1, i + step)
+        k0, k1 = rec[i:j, 0], rec[i + 1:j + 1, 0]
+        i0, i1 = rec[i:j, 1], rec[i + 1:j + 1, 1]
+        ok = ok and bool((k1 >= k0).all()) and bool(((k1 > k0) | (i1 > i0)).all())
+    for i in range(0, n, step):
+        idx_sum += int(rec[i:min(n, i + step), 1].to(torch.int64).sum())
+    assert ok
+    assert idx_sum == n * (n - 1) // 2
+    assert int(rec[:, 2].abs().max()) == 0
+    del rec
+    _abi.lib().b200_release_scratch(-1)
+
+
+def test_tuner_answers_select_observable_routes():
+    """The policy hook (reference src/tuner.rs:33-35, asked at src/sorter.rs:67-76): a user Tuner's Algorithm
+    changes what the engine runs, and b200_stats shows it."""
+    torch = torch_mod()
+
+    class One(tuner.Tuner):
+        def __init__(self, algo):
+            self.algo, self.seen = algo, None
+
+        def pick_algorithm(self, p, counts):
+            self.seen = (p.level, p.total_levels, p.input_len, p.parent_len, len(counts), sum(counts))
+            return self.algo
+
+    rng = np.random.default_rng(5)
+    n = 40_000_000  # above the key-only hybrid gate for u64
+    a = rng.integers(0, 2**64, n, dtype="u8")
+    exp = np.sort(a)
+    got = {}
+    for algo in (tuner.Algorithm.Scanning, tuner.Algorithm.Lsb, tuner.Algorithm.Ska):
+        t = torch.from_numpy(a.copy()).cuda()
+        tn = One(algo)
+        b = radix_sort_builder(t.view(torch.uint8), RadixKey.for_dtype("u8")).with_tuner(tn)
+        b.sort()
+        torch.cuda.synchronize()
+        assert np.array_equal(t.cpu().numpy(), exp), algo
+        assert tn.seen == (7, 8, n, None, 256, n)
+        got[algo] = b.stats
+    assert got[tuner.Algorithm.Scanning]["hybrid"] == 1 and got[tuner.Algorithm.Scanning]["route_hint"] == 0
+    assert got[tuner.Algorithm.Lsb]["hybrid"] == 0 and got[tuner.Algorithm.Lsb]["levels_run"] == 8
+    assert got[tuner.Algorithm.Ska]["hybrid"] == 0 and got[tuner.Algorithm.Ska]["route_hint"] == 2
+    assert got[tuner.Algorithm.Ska]["variant"] != got[tuner.Algorithm.Lsb]["variant"]  # the small-tile variant
+    # with_low_mem_tuner(): same route through the builder, and the scratch pool is gone afterwards
+    free0 = torch.cuda.mem_get_info()[0]
+    t = torch.from_numpy(a.copy()).cuda()
+    free1 = torch.cuda.mem_get_info()[0]
+    b = radix_sort_builder(t.view(torch.uint8), RadixKey.for_dtype("u8")).with_low_mem_tuner()
+    b.sort()
+    torch.cuda.synchronize()
+    assert np.array_equal(t.cpu().numpy(), exp)
+    assert b.stats["hybrid"] == 0
+    assert torch.cuda.mem_get_info()[0] >= free1 - (64 << 20), "the low-scratch route keeps no scratch pool"
+    del free0
+
+
+def test_host_entry_pinned_and_pageable_overlapped_paths():
+    """b200_sort_host on inputs large enough for its overlapped timeline (K0 / K1 behind the H2D chunks; D2H behind
+    the first slice of the segment sort): pinned and pageable memory, random and presorted, key-only and payload."""
+    torch = torch_mod()
+    rng = np.random.default_rng(6)
+    n = 40_000_000
+    a = rng.integers(0, 2**64, n, dtype="u8")
+    exp = np.sort(a)
+    for pinned in (False, True):
+        h = torch.from_numpy(a.copy())
+        if pinned:
+            h = h.pin_memory()
+        arr = h.numpy()
+        b = radix_sort_builder(arr, RadixKey.for_dtype("u8"))
+        b.sort()
+        assert np.array_equal(arr, exp), pinned
+        assert b.stats["hybrid"] == 1 and b.stats["ms_h2d"] > 0 and b.stats["ms_d2h"] >= 0
+        b2 = radix_sort_builder(arr, RadixKey.for_dtype("u8"))  # presorted now: K0 behind the chunks says so
+        b2.sort()
+        assert b2.stats["already_sorted"] == 1 and np.array_equal(arr, exp)
+    # one swapped pair exactly on a chunk boundary of the chunked K0 must be seen
+    srt = exp.copy()
+    cut = (128 << 20) // 8  # first chunk boundary in records
+    srt[cut - 1], srt[cut] = srt[cut], srt[cut - 1]
+    b3 = radix_sort_builder(srt, RadixKey.for_dtype("u8"))
+    b3.sort()
+    assert b3.stats["already_sorted"] == 0 and np.array_equal(srt, exp)
+    # 12-byte records (chunk boundaries that are not powers of two), stable
+    rec = np.dtype([("key", "<u4"), ("idx", "<u8")])
+    r = np.zeros(12_000_000, dtype=rec)
+    r["key"] = rng.integers(0, 1 << 20, len(r))
+    r["idx"] = np.arange(len(r))
+    key = RadixKey.field(rec, "key", 3)
+    hr = r.copy()
+    radix_sort_builder(hr, key).with_stable(True).sort()
+    assert hr.tobytes() == o.stable_sorted(r, key).tobytes()
+
+
 # ---------------------------------------------------------------------------------------------
 # Hybrid path (two MSD passes + K3 shared-memory segment sort): must give the oracle's answer
 # bit for bit on every input the LSD path handles.  B200SORT_HYBRID=1 forces it at small sizes.
@@ -604,7 +773,7 @@ def test_hybrid_path_matches_oracle(monkeypatch, name, dt, a, expect_hybrid, uns
     assert h.tobytes() == exp.tobytes(), name
     if unstable:
         # the other size of K3-U (512 threads, one CTA per SM) and a narrow digit (long comparison runs)
-        monkeypatch.setenv("B200SORT_K3U_SIZE", "0")
+        monkeypatch.setenv("B200SORT_K3U_SIZE", "2")
         monkeypatch.setenv("B200SORT_K3U_BMAX", "9")
     else:
         # both fast-level settings of K3 agree (nfast = 1 leaves more to the insertion fix-up)

@@ -103,10 +103,23 @@ def test_hybrid_route_rule_on_synthetic_histograms():
     name, r = route(k8, n, uniform_hist(8, n, range(8)))  # BASELINE configs[1]
     assert name == "hybrid" and r.levels_run == 8
     assert route(k8, n, uniform_hist(8, n, range(5)))[0] == "hybrid"          # 40-bit keys: five active levels
-    assert route(k8, n, uniform_hist(8, n, range(4)))[0] == "lsd"             # four: passes are cheaper
-    assert route(k4, n, uniform_hist(4, n, range(4)))[0] == "lsd"             # u32: four levels
-    assert route(k8, 200_000_000, uniform_hist(8, 200_000_000, range(8)))[0] == "lsd"  # below 256 Mi records
+    # records that are nothing but their key take the unstable flavour of the route (K2-U + K3-U), which pays
+    # from four active levels and far smaller inputs on
+    assert route(k8, n, uniform_hist(8, n, range(4)))[0] == "hybrid"
+    assert route(k8, n, uniform_hist(8, n, range(3)))[0] == "lsd"             # three: passes are cheaper
+    assert route(k4, n, uniform_hist(4, n, range(4)))[0] == "hybrid"          # u32, 1 B keys
+    assert route(k4, 100_000_000, uniform_hist(4, 100_000_000, range(4)))[0] == "lsd"   # u32 below 128 Mi records
+    assert route(k4, 500_000_000, uniform_hist(4, 500_000_000, range(4)))[0] == "hybrid"
+    assert route(k8, 200_000_000, uniform_hist(8, 200_000_000, range(8)))[0] == "hybrid"
+    assert route(k8, 50_000_000, uniform_hist(8, 50_000_000, range(8)))[0] == "hybrid"
+    assert route(k8, 25_000_000, uniform_hist(8, 25_000_000, range(8)))[0] == "lsd"     # u64 below 32 Mi records
     assert route(k8, 5_000_000_000, uniform_hist(8, 5_000_000_000, range(8)))[0] == "lsd"  # 32-bit offsets in K3
+    # records with a payload stay on the stable flavour: five active levels, 256 Mi records
+    rec8 = RadixKey.field(REC8, "key", 4)
+    assert route(rec8, n, uniform_hist(4, n, range(4)))[0] == "lsd"
+    rec16 = RadixKey("uint", 8, 6, 0, 8)  # u64 with LEVELS = 6: the two top bytes are payload
+    assert route(rec16, n, uniform_hist(6, n, range(6)))[0] == "hybrid"
+    assert route(rec16, 200_000_000, uniform_hist(6, 200_000_000, range(6)))[0] == "lsd"
     # two values on the top level: the expected segment (n / 2 / 256) does not fit an SM
     h = uniform_hist(8, n, range(8))
     h[7, :] = 0
