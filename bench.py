@@ -12,7 +12,14 @@ Timing: CUDA events on the launching stream around each step's sort; the in-plac
 input is restored (device-to-device copy) between steps outside the event pairs, so the
 timed region starts with the unsorted input resident in HBM.  Inputs (8 GB) are far larger
 than L2, no flush needed.  Max over ranks.  `e2e` = same metric through the public host API
-(radix_sort_unstable on a pinned host array: H2D + sort + D2H inside the timed region).
+with HOST buffers, H2D + sort + D2H inside the timed region: at N=1 radix_sort_builder(pinned numpy
+array).sort() -> b200_sort_host (plus `e2e_pageable`: the same call on ordinary pageable memory, what a
+Rust Vec is); at N>1 rdst_b200.sort_multi_host -> b200_sort_multi_host, ONE process driving all N GPUs
+from one host array of N x n keys (run by rank 0 while the other ranks wait on a CPU barrier).
+After the timed loop at N>1 the GLOBAL result is verified on the devices (outside the timed region):
+every rank's range sorted under the key's order, max(rank r) <= min(rank r + 1), record count and two
+multiset checksums equal to the input's; the outcome is the `verified` object of the JSON line.
+--all-configs prints one line per BASELINE.json config that fits this GPU count (kept in profiles/).
 
 --impl reference: the reference's CPU path.  The reference is a pure-Rust crate and this
 image has no Rust toolchain, so what is timed is oracle/ (the C restatement of rdst's
@@ -47,11 +54,34 @@ WORKLOADS = {
     "u64_1b_zipf": ("u8", 1_000_000_000, "zipf", "configs[4] skewed: Zipf(1.1) ranks as u64 keys"),
     "u64_1b_zipf_hashed": ("u8", 1_000_000_000, "zipf_hashed",
                            "configs[4] skewed: hashed Zipf(1.1) ranks (heavy duplicates, every level non-trivial)"),
+    "struct12_1b_stable": ("rec12", 1_000_000_000, "struct",
+                           "BASELINE configs[3]: {u32 key with LEVELS=3, 8-byte payload} x 1B records, stable order"),
 }
+# the BASELINE.json configs a 1-GPU run covers (--all-configs)
+ALL_CONFIGS_N1 = ["u32_100m_uniform", "u64_1b_uniform", "f32_500m", "i64_500m", "struct12_1b_stable"]
+ALL_CONFIGS_NX = ["u64_1b_uniform", "u64_1b_zipf", "u64_1b_zipf_hashed"]
 CPU_SAMPLE = 200_000_000  # records of the same generator the CPU baseline sorts per step
 
 
+def key_of(dtype):
+    from rdst_b200 import RadixKey
+
+    if dtype == "rec12":  # benches/struct_sort.rs shape scaled down to BASELINE configs[3]: partial-LEVELS u32 key + payload
+        return RadixKey("uint", 12, 3, 0, 4)
+    return RadixKey.for_dtype(dtype)
+
+
+def np_dtype(dtype):
+    return np.dtype([("key", "<u4"), ("idx", "<u8")]) if dtype == "rec12" else np.dtype(dtype)
+
+
 def gen_host(dtype, n, gen, seed):
+    if dtype == "rec12":
+        rng = np.random.default_rng(seed)
+        a = np.zeros(n, dtype=np_dtype(dtype))
+        a["key"] = rng.integers(0, 1 << 24, n, dtype=np.uint32)
+        a["idx"] = np.arange(n, dtype=np.uint64)
+        return a
     rng = np.random.default_rng(seed)
     dt = np.dtype(dtype)
     if gen in ("zipf", "zipf_hashed"):
@@ -74,6 +104,15 @@ def gen_host(dtype, n, gen, seed):
 def gen_device(torch, dtype, n, gen, seed):
     """Same distributions generated on the device (flat int64/int32 storage of the key bits)."""
     g = torch.Generator(device="cuda").manual_seed(seed)
+    if dtype == "rec12":  # [n, 3] int32: key (24 random bits), payload = the record's input index (two words)
+        rec = torch.empty((n, 3), dtype=torch.int32, device="cuda")
+        step = 1 << 28
+        for i in range(0, n, step):
+            j = min(n, i + step)
+            rec[i:j, 0] = torch.randint(0, 1 << 24, (j - i,), dtype=torch.int32, device="cuda", generator=g)
+            rec[i:j, 1] = torch.arange(i, j, dtype=torch.int32, device="cuda")
+        rec[:, 2] = 0
+        return rec
     dt = np.dtype(dtype)
     if dt.itemsize == 8:
         if gen in ("zipf", "zipf_hashed"):
@@ -202,9 +241,8 @@ class ClockSampler:
 def cpu_baseline(dtype, gen, steps, warmup, sample=CPU_SAMPLE):
     """oracle/ (C restatement of rdst's default multi-threaded path) timed on the host cores."""
     import oracle_ffi as o
-    from rdst_b200 import RadixKey
 
-    key = RadixKey.for_dtype(dtype)
+    key = key_of(dtype)
     cores = o.hardware_threads()
     src = gen_host(dtype, sample, gen, 0x5EED0002)
     work = np.empty_like(src)
@@ -212,12 +250,15 @@ def cpu_baseline(dtype, gen, steps, warmup, sample=CPU_SAMPLE):
     for i in range(warmup + steps):
         np.copyto(work, src)
         t0 = time.perf_counter()
-        o.sort(work, key, tuner="standard", multi_threaded=True, threads=cores)
+        if dtype == "rec12":  # rdst's stable order, multi-threaded: a tuner answering MtLsb (src/sorts/mt_lsb_sort.rs)
+            o.sort(work, key, tuner="single_algo", algo="MtLsb", multi_threaded=True, threads=cores)
+        else:
+            o.sort(work, key, tuner="standard", multi_threaded=True, threads=cores)
         dt = time.perf_counter() - t0
         if i >= warmup:
             times.append(dt)
     assert o.is_sorted(work[:: max(1, sample // 1_000_000)].copy(), key)
-    ok = bool(np.all(work[1:] >= work[:-1])) if np.dtype(dtype).kind == "u" else True
+    ok = bool(np.all(work[1:] >= work[:-1])) if np_dtype(dtype).kind == "u" else True
     assert ok, "CPU baseline produced an unsorted result"
     return {"value": sample / statistics.median(times) / 1e9, "unit": "Gkeys/s", "cores": cores, "kind": "port",
             "sample": f"{sample} {dtype} keys of the same generator per step (of {WORKLOADS_N[dtype, gen]}), "
@@ -241,7 +282,8 @@ def run_reference(args):
     line = {
         "impl": "reference", "metric": "Gkeys/s sorted", "value": cb["value"], "unit": "Gkeys/s",
         "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms,
-        "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": np.dtype(dtype).name.replace("uint", "u"),
+        "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+        "dtype": "u32 key + 8-byte payload" if dtype == "rec12" else np.dtype(dtype).name.replace("uint", "u").replace("float", "f").replace("int", "i"),
         "data": "synthetic", "config": {"workload": f"{args.workload}: {desc}", "records_per_step": sample,
                                         "note": "bounded sample of the workload, CPU host cores only"},
         "cpu_baseline": cb,
@@ -252,29 +294,39 @@ def run_reference(args):
     return 0
 
 
-def run_b200(args):
-    import torch
-    import torch.distributed as dist
+def key_image(torch, t, dtype):
+    """Signed integer image of the stored bit patterns that orders like the key (u: sign bit flipped, i: as is,
+    f: IEEE total order) — for on-device checks."""
+    kind = np_dtype(dtype).kind
+    mn = -2**63 if t.dtype == torch.int64 else -2**31
+    if kind == "u":
+        return t ^ mn
+    if kind == "f":
+        return torch.where(t < 0, ~t ^ mn, t)
+    return t
 
-    from rdst_b200 import RadixKey, _abi, radix_sort_builder
+
+def checksums(torch, t):
+    """Two wrapping 64-bit multiset checksums of an integer tensor (order-independent)."""
+    x = t.to(torch.int64).reshape(-1)
+    return int(x.sum()), int(((x * 0x9E3779B1) ^ (x >> 7)).sum())
+
+
+def run_one(args, workload, torch, dist, world, rank, local_rank, cpu_group):
+    from rdst_b200 import _abi, radix_sort_builder, sort_multi_host
     from rdst_b200.dist import CudaEngine, sharded_sort
 
-    world = int(os.environ.get("WORLD_SIZE", "1"))
-    rank = int(os.environ.get("RANK", "0"))
-    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
-    assert torch.cuda.is_available(), "bench.py needs a GPU (no CPU fallback)"
-    torch.cuda.set_device(local_rank)
-    if world > 1:
-        dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
-    dtype, n, gen, desc = WORKLOADS[args.workload]
+    dtype, n, gen, desc = WORKLOADS[workload]
     if args.n:
         n = args.n
-    key = RadixKey.for_dtype(dtype)
+    key = key_of(dtype)
     es = key.elem_size
     nbytes = n * es
+    struct = dtype == "rec12"
 
     src = gen_device(torch, dtype, n, gen, 0x5EED0002 + rank)           # pristine input, never sorted
     work = torch.empty_like(src)
+    in_chk = checksums(torch, src) if world > 1 else None
     eng = CudaEngine(key)
     scratch = {"tmp": torch.empty(nbytes, dtype=torch.uint8, device="cuda")}
     if world > 1:
@@ -331,43 +383,49 @@ def run_b200(args):
     ms_steps = [ev0[i].elapsed_time(ev1[i]) for i in range(args.steps)]
     ms_total = sum(ms_steps)
 
-    # cheap on-device verification of the last step (outside the timed region)
+    # ---- verification of the last step on the device, outside the timed region ----
+    # every key type through its order-preserving image; at N>1 the GLOBAL order (boundaries between ranks),
+    # the record count and two multiset checksums against the input's
     res = out[: n_out * es].view(torch.int64 if es == 8 else torch.int32)
-    flip = -2**63 if es == 8 else -2**31
-    if np.dtype(dtype).kind == "u":
-        u = res ^ flip
-        ok = bool((u[1:] >= u[:-1]).all()) if n_out > 1 else True
-        assert ok, "result is not sorted"
-        del u
+    verified = {"records_out": int(n_out)}
+    if struct:
+        r3 = res.view(-1, 3)
+        k0, k1, i0, i1 = r3[:-1, 0], r3[1:, 0], r3[:-1, 1], r3[1:, 1]
+        verified["sorted"] = bool((k1 >= k0).all()) if n_out > 1 else True
+        verified["stable"] = bool(((k1 > k0) | (i1 > i0)).all()) if n_out > 1 else True
+        first_last = [int(r3[0, 0]), int(r3[-1, 0])] if n_out else [0, 0]
+    else:
+        img = key_image(torch, res, dtype)
+        step = 1 << 28
+        ok = True
+        for i in range(0, max(0, n_out - 1), step):
+            j = min(n_out - 1, i + step)
+            ok = ok and bool((img[i + 1:j + 1] >= img[i:j]).all())
+        verified["sorted"] = ok
+        first_last = [int(img[0]), int(img[-1])] if n_out else [0, 0]
+        del img
+    assert verified["sorted"], "result is not sorted"
+    if world > 1:
+        fl = torch.tensor(first_last + [int(n_out)], dtype=torch.int64, device="cuda")
+        allfl = [torch.empty_like(fl) for _ in range(world)]
+        dist.all_gather(allfl, fl)
+        allfl = [[int(v) for v in t.tolist()] for t in allfl]
+        nonempty = [x for x in allfl if x[2] > 0]
+        verified["rank_boundaries_ordered"] = all(a[1] <= b[0] for a, b in zip(nonempty, nonempty[1:]))
+        tot = torch.tensor([n_out] + list(checksums(torch, res)) + list(in_chk), dtype=torch.int64, device="cuda")
+        dist.all_reduce(tot)  # wrapping int64 sums
+        tot = [int(v) for v in tot.tolist()]
+        verified["records_total"] = tot[0]
+        verified["records_expected"] = n * world
+        verified["multiset_checksums_match"] = tot[1:3] == tot[3:5]
+        verified["records_per_rank"] = [x[2] for x in allfl]
+        assert verified["rank_boundaries_ordered"], "ranges of neighbouring ranks overlap"
+        assert tot[0] == n * world, "records were lost or duplicated in the exchange"
+        assert verified["multiset_checksums_match"], "output is not a permutation of the input"
+    elif not struct:
+        verified["multiset_checksums_match"] = checksums(torch, res) == checksums(torch, src)
+        assert verified["multiset_checksums_match"]
     st_local = last.get("local", {})
-
-    # ---- e2e: the public host API on a pinned host buffer, H2D + sort + D2H per step ----
-    e2e = None
-    if not args.no_e2e:
-        e2e_steps = max(1, min(args.steps, args.e2e_steps))
-        host_src = torch.empty(n, dtype=src.dtype).pin_memory()
-        host_src.copy_(src)
-        host_work = torch.empty(n, dtype=src.dtype).pin_memory()
-        harr = host_work.numpy().view(dtype)
-        e_times = []
-        for i in range(1 + e2e_steps):
-            host_work.copy_(host_src)
-            barrier()
-            t0 = time.perf_counter()
-            b = radix_sort_builder(harr, key)
-            b.sort()  # blocking: returns when the sorted data is back in host memory
-            e_times.append(time.perf_counter() - t0)
-            launches_e2e = b.stats["kernel_launches"]
-        e_times = e_times[1:]
-        assert bool(np.all(harr[1:] >= harr[:-1])) if np.dtype(dtype).kind == "u" else True
-        e_t = torch.tensor([sum(e_times) / len(e_times)], device="cuda")
-        if world > 1:
-            dist.all_reduce(e_t, op=dist.ReduceOp.MAX)
-        e2e = {"value": n * world / float(e_t.item()) / 1e9, "unit": "Gkeys/s", "h2d_bytes_per_step": nbytes * world,
-               "d2h_bytes_per_step": nbytes * world, "steps": e2e_steps, "ms_per_step": float(e_t.item()) * 1e3,
-               "api": "rdst_b200.radix_sort_builder(pinned numpy array).sort() -> b200_sort_host",
-               "ms_h2d": b.stats["ms_h2d"], "ms_d2h": b.stats["ms_d2h"], "ms_sort_device": b.stats["ms_hist"] + b.stats["ms_passes"]}
-        del host_src, host_work
 
     t = torch.tensor([ms_total], device="cuda")
     if world > 1:
@@ -378,10 +436,100 @@ def run_b200(args):
         nr = torch.tensor([int(last.get("n_recv", 0))], dtype=torch.int64, device="cuda")
         dist.all_reduce(nr, op=dist.ReduceOp.MAX)
         max_n_recv = int(nr.item())
+
+    # ---- e2e: the public host API on HOST buffers, H2D + sort + D2H per step ----
+    e2e = e2e_pageable = None
+    if not args.no_e2e and world == 1:
+        e2e_steps = max(1, min(args.steps, args.e2e_steps))
+        npdt = np_dtype(dtype)
+
+        def host_run(pinned):
+            hs = torch.empty(n * es, dtype=torch.uint8)
+            hw = torch.empty(n * es, dtype=torch.uint8)
+            if pinned:
+                hs, hw = hs.pin_memory(), hw.pin_memory()
+            hs.copy_(src.view(torch.uint8).view(-1))
+            harr = hw.numpy().view(npdt)
+            times, b = [], None
+            for i in range(1 + e2e_steps):
+                hw.copy_(hs)
+                torch.cuda.synchronize()
+                t0 = time.perf_counter()
+                b = radix_sort_builder(harr, key)
+                (b.with_stable(True) if struct else b).sort()  # blocking: returns when the sorted data is back in host memory
+                times.append(time.perf_counter() - t0)
+            times = times[1:]
+            k = harr["key"] if struct else harr
+            assert bool(np.all(k[1:] >= k[:-1])) if npdt.kind != "f" else True
+            sec = sum(times) / len(times)
+            return {"value": n / sec / 1e9, "unit": "Gkeys/s", "h2d_bytes_per_step": nbytes, "d2h_bytes_per_step": nbytes,
+                    "steps": e2e_steps, "ms_per_step": sec * 1e3,
+                    "api": f"rdst_b200.radix_sort_builder({'pinned' if pinned else 'pageable'} numpy array).sort() -> b200_sort_host",
+                    "ms_h2d": b.stats["ms_h2d"], "ms_d2h_after_sort": b.stats["ms_d2h"],
+                    "ms_sort_device": b.stats["ms_hist"] + b.stats["ms_passes"], "ms_total_device_clock": b.stats["ms_total"],
+                    "overlap": "K0/K1 run behind the H2D chunks; D2H starts behind the first slice of the segment sort (pinned)"}
+
+        e2e = host_run(True)
+        e2e_pageable = host_run(False)
+        e2e_pageable["copy_threads"] = int(os.environ.get("B200SORT_COPY_THREADS", "0")) or "min(8, host threads / 2)"
+    elif not args.no_e2e:
+        # ONE process drives all N GPUs from one host array (b200_sort_multi_host): rank 0 runs it, the others wait on
+        # a CPU barrier.  The per-rank device buffers of the timed loop are released first.
+        del work, wbuf, out, res
+        scratch.clear()
+        _abi.lib().b200_release_scratch(-1)
+        torch.cuda.empty_cache()
+        dist.barrier(group=cpu_group)
+        e2e = {"value": None}
+        if rank == 0:
+            try:
+                import psutil
+
+                avail = psutil.virtual_memory().available
+            except Exception:
+                avail = 0
+            n_e2e = n
+            while n_e2e > (1 << 20) and 2.3 * world * n_e2e * es > avail > 0:
+                n_e2e //= 2
+            total = n_e2e * world
+            hs = torch.empty(total * es, dtype=torch.uint8).pin_memory()
+            hw = torch.empty(total * es, dtype=torch.uint8).pin_memory()
+            for r in range(world):  # the same per-rank generator, shard by shard through this rank's GPU
+                shard = gen_device(torch, dtype, n_e2e, gen, 0x5EED0002 + r)
+                hs[r * n_e2e * es:(r + 1) * n_e2e * es].copy_(shard.view(torch.uint8).view(-1))
+                del shard
+            torch.cuda.empty_cache()
+            harr = hw.numpy().view(np_dtype(dtype))
+            times, st = [], None
+            e2e_steps = max(1, min(args.steps, args.e2e_steps, 2))
+            for i in range(1 + e2e_steps):
+                hw.copy_(hs)
+                t0 = time.perf_counter()
+                st = sort_multi_host(harr, key, gpus=list(range(world)))
+                times.append(time.perf_counter() - t0)
+            times = times[1:]
+            ok = True
+            stepv = 1 << 27
+            kk = harr["key"] if struct else harr
+            for i in range(0, total - 1, stepv):
+                j = min(total - 1, i + stepv)
+                ok = ok and bool(np.all(kk[i + 1:j + 1] >= kk[i:j])) if np_dtype(dtype).kind != "f" else ok
+            assert ok, "multi-GPU host sort result is not sorted"
+            sec = sum(times) / len(times)
+            e2e = {"value": total / sec / 1e9, "unit": "Gkeys/s", "h2d_bytes_per_step": total * es, "d2h_bytes_per_step": total * es,
+                   "steps": e2e_steps, "ms_per_step": sec * 1e3, "records": total, "records_per_gpu": n_e2e,
+                   "api": "rdst_b200.sort_multi_host(pinned numpy array) -> b200_sort_multi_host: one process, all N GPUs, "
+                          "one host array of N x n keys sorted in place",
+                   "ms_h2d": st["ms_h2d"], "ms_d2h": st["ms_d2h"], "ms_plan": st["ms_plan"], "ms_exchange": st["ms_exchange"],
+                   "ms_local_sort": st["ms_local_sort"], "splitter_mode": st["splitter_mode"], "imbalance": st["imbalance"],
+                   "verified_sorted": bool(ok)}
+            if n_e2e != n:
+                e2e["note"] = f"host RAM on this box holds {n_e2e} records per GPU twice over (pinned), not {n}: e2e ran at that size"
+            del hs, hw
+            _abi.lib().b200_multi_release()
+        dist.barrier(group=cpu_group)
     if rank != 0:
-        if world > 1:
-            dist.destroy_process_group()
-        return 0
+        return None
 
     peaks = {}
     try:
@@ -400,69 +548,77 @@ def run_b200(args):
     except Exception:
         pass
     if passes and ms_passes > 0:
-        hybrid = bool(st_local.get("hybrid"))
+        hybrid = int(st_local.get("hybrid", 0)) == 1
+        unstable = int(st_local.get("unstable", 0))
+        moved_per_launch = 2 * n_sorted * es  # every kernel of the path reads and writes each record once
         whole_bytes = n_sorted * es * (1 + 2 * passes)
-        whole = whole_bytes / ((st_local["ms_hist"] + ms_passes) * 1e-3) / 1e9
+        ms_whole = st_local["ms_hist"] + ms_passes
+        whole = whole_bytes / (ms_whole * 1e-3) / 1e9
         if hybrid:
-            # dominant kernel = K3: it does the work of `local_levels` LSD passes on chip
+            # dominant kernel = the segment sort (K3-U for key-only records, K3 otherwise): ONE read and ONE write of
+            # every record through HBM; the levels it covers run in shared memory
             nl = int(st_local["local_levels"])
             ms_k3 = float(st_local["ms_local"])
             ms_k2 = (ms_passes - ms_k3 - float(st_local["ms_joint"])) / 2.0
-            per_launch_bytes = 2 * n_sorted * es * nl
-            ach = per_launch_bytes / (ms_k3 * 1e-3) / 1e9
-            roof = {"bound": "hbm", "kernel": f"K3 local_sort_kernel: shared-memory segment sort covering {nl} of the {passes} levels "
-                                              "(hybrid path: 2 MSD K2 passes + K3)",
-                    "achieved": ach, "peak": peak, "unit": "GB/s", "frac": ach / peak, "traffic": None, "peak_source": peak_src,
-                    "algorithmic_bytes_per_launch": per_launch_bytes, "launches_per_step": 1, "avg_launch_ms": ms_k3,
-                    "how": "algorithmic bytes = 2*n*S per level K3 sorts (SURVEY 8d) / the library's CUDA-event time of K3 in the last "
-                           "step; K3 reads and writes every record once (see traffic), the levels run in shared memory",
-                    "k2_msd_pass": {"kernel": "lsd_pass_or16_kernel, variant " + str(st_local.get("variant")),
-                                    "algorithmic_bytes_per_launch": 2 * n_sorted * es, "launches_per_step": 2, "avg_launch_ms": ms_k2,
-                                    "achieved": 2 * n_sorted * es / (ms_k2 * 1e-3) / 1e9,
-                                    "frac": 2 * n_sorted * es / (ms_k2 * 1e-3) / 1e9 / peak},
-                    "ms_joint_histogram": float(st_local["ms_joint"]), "slow_segments": int(st_local.get("slow_segments", 0)),
-                    # what K3 actually moves through HBM (one read + one write of every record): it is bound by the
-                    # shared-memory pipe (ncu: 75 % busy), not by HBM, which is the point of the hybrid path
-                    "dram": {"bytes_moved_per_launch": 2 * n_sorted * es,
-                             "achieved": 2 * n_sorted * es / (ms_k3 * 1e-3) / 1e9,
-                             "frac": 2 * n_sorted * es / (ms_k3 * 1e-3) / 1e9 / peak}}
-            tr = traffic_db.get(args.workload + ":k3")
+            kname = ("K3-U local_count_kernel (key-only records: one wide counting-sort level + per-run comparison fix-up)"
+                     if unstable & 1 else "K3 local_sort_kernel (stable shared-memory segment sort)")
+            ach = moved_per_launch / (ms_k3 * 1e-3) / 1e9
+            roof = {"bound": "hbm", "kernel": kname, "achieved": ach, "peak": peak, "unit": "GB/s", "frac": ach / peak,
+                    "traffic": None, "peak_source": peak_src, "algorithmic_bytes_per_launch": moved_per_launch,
+                    "launches_per_step": 1, "avg_launch_ms": ms_k3, "limiter": "instruction issue and the shared-memory pipe "
+                    "(ncu: DRAM ~23 % busy); the kernel moves each record through HBM once and does the work of "
+                    f"{nl} LSD levels on chip",
+                    "how": "bytes = 2*n*S (one read + one write of every record) / the library's CUDA-event time of the "
+                           "segment sort in the last step",
+                    "lsd_equivalent_gbps": 2 * n_sorted * es * nl / (ms_k3 * 1e-3) / 1e9,
+                    "k2_msd_pass": {"kernel": ("K2-U msd_pass_atomic_kernel" if unstable & 6 else
+                                               "lsd_pass_or16_kernel, variant " + str(st_local.get("variant"))),
+                                    "algorithmic_bytes_per_launch": moved_per_launch, "launches_per_step": 2,
+                                    "avg_launch_ms": ms_k2, "achieved": moved_per_launch / (ms_k2 * 1e-3) / 1e9,
+                                    "frac": moved_per_launch / (ms_k2 * 1e-3) / 1e9 / peak},
+                    "ms_joint_histogram": float(st_local["ms_joint"]), "slow_segments": int(st_local.get("slow_segments", 0))}
+            tr = traffic_db.get(workload + (":k3u" if unstable & 1 else ":k3"))
         else:
-            per_launch_bytes = 2 * n_sorted * es
-            ach = per_launch_bytes * passes / (ms_passes * 1e-3) / 1e9
+            ach = moved_per_launch * passes / (ms_passes * 1e-3) / 1e9
             roof = {"bound": "hbm", "kernel": "K2 LSD pass (lsd_pass_or16_kernel, variant " + str(st_local.get("variant")) + ")",
                     "achieved": ach, "peak": peak, "unit": "GB/s", "frac": ach / peak, "traffic": None, "peak_source": peak_src,
-                    "algorithmic_bytes_per_launch": per_launch_bytes, "launches_per_step": passes,
-                    "avg_launch_ms": ms_passes / passes,
+                    "algorithmic_bytes_per_launch": moved_per_launch, "launches_per_step": passes,
+                    "avg_launch_ms": ms_passes / passes, "limiter": "the shared-memory pipe (ranking is paid per record)",
                     "how": "CUDA events recorded by the library on the launch stream around the K2 passes of the last step"}
-            tr = traffic_db.get(args.workload)
+            tr = traffic_db.get(workload)
         if tr and tr.get("records") == n_sorted:
             roof["traffic"] = tr["traffic_bytes_per_launch"]
-            roof["traffic_source"] = "profiles/k2_traffic.json (ncu dram__bytes_read.sum + dram__bytes_write.sum, one launch)"
+            roof["traffic_source"] = tr.get("source", "profiles/k2_traffic.json") + " (ncu dram__bytes_read.sum + dram__bytes_write.sum, one launch)"
+            roof["achieved_by_traffic"] = roof["traffic"] / (roof["avg_launch_ms"] * 1e-3) / 1e9
+            roof["frac_by_traffic"] = roof["achieved_by_traffic"] / peak
+        # the contract's whole-sort figure (bytes of an LSD engine, N*S*(1 + 2*levels)) next to what moved
         roof["whole_sort"] = {"algorithmic_bytes": whole_bytes, "achieved": whole, "frac": whole / peak,
                               "frac_of_8TBs_nominal": whole / 8000.0, "ms_hist": st_local["ms_hist"], "ms_passes": ms_passes,
-                              "path": "hybrid (K1, K2 x2, joint histogram, K3)" if hybrid else "LSD (K1, K2 per level)"}
-        if hybrid:  # the formula above is BASELINE's (an LSD engine's traffic); the hybrid path moves 8 N*S
-            moved = 8 * n_sorted * es
-            roof["whole_sort"]["hbm_bytes_moved"] = moved
-            roof["whole_sort"]["hbm_moved_frac"] = moved / ((st_local["ms_hist"] + ms_passes) * 1e-3) / 1e9 / peak
+                              "path": ("hybrid (K1, MSD pass x2, joint histogram, segment sort)" if hybrid else "LSD (K1, K2 per level)")}
+        moved = (8 if hybrid else 1 + 2 * passes + (2 if st_local.get("copy_back") else 0)) * n_sorted * es
+        roof["whole_sort"]["hbm_bytes_moved"] = moved
+        roof["whole_sort"]["hbm_moved_frac"] = moved / (ms_whole * 1e-3) / 1e9 / peak
     cb = None
     if world == 1 and not args.no_cpu:
         cb = cpu_baseline(dtype, gen, args.cpu_steps, 1, min(args.cpu_sample, n))
     value = n * world * args.steps / (ms_total_max * 1e-3) / 1e9
+    dname = "u32 key + 8-byte payload" if struct else np.dtype(dtype).name.replace("uint", "u").replace("float", "f").replace("int", "i")
     line = {
         "metric": "Gkeys/s sorted", "value": value, "unit": "Gkeys/s", "n_gpus": world, "steps": args.steps,
         "warmup": args.warmup, "ms_per_step": ms_total_max / args.steps, "higher_is_better": True, "scaling": "weak",
-        "vs_baseline": None, "dtype": np.dtype(dtype).name.replace("uint", "u").replace("float", "f").replace("int", "i"),
-        "data": "synthetic",
-        "config": {"workload": f"{args.workload}: {desc}", "records_per_gpu": n, "record_bytes": es,
+        "vs_baseline": None, "dtype": dname, "data": "synthetic",
+        "config": {"workload": f"{workload}: {desc}", "records_per_gpu": n, "record_bytes": es,
                    "levels_run": passes, "parallelism": f"range-partition x{world}" if world > 1 else "single GPU",
                    "l2": "inputs (>= 0.4 GB) larger than L2; unsorted input restored by a D2D copy between steps, untimed",
                    "timing": "CUDA events per step on the launch stream, summed; max over ranks",
                    "wall_s_timed_loop_incl_restore": t_wall},
         "ms_steps": ms_steps, "clocks": clocks, "e2e": e2e, "gpu_launches": launches,
-        "roofline": roof, "cpu_baseline": cb,
+        "roofline": roof, "cpu_baseline": cb, "verified": verified,
+        "route": {k: st_local.get(k) for k in ("hybrid", "unstable", "levels_run", "levels_skipped", "local_levels", "variant",
+                                               "copy_back", "slow_segments", "kernel_launches")},
     }
+    if e2e_pageable:
+        line["e2e_pageable"] = e2e_pageable
     if world > 1:
         line["exchange"] = {"mode": args.exchange}
         line["exchange"].update({k: last.get(k) for k in ("level", "n_recv", "sent_bytes", "phase_ms", "splitter_mode", "splitter_plan_ms", "exchange_path")})
@@ -474,7 +630,36 @@ def run_b200(args):
             line["exchange"]["exchange_ms"] = t_x
             line["exchange"]["all_to_all_GBps_per_direction"] = last["sent_bytes"] / (t_x * 1e-3) / 1e9
             line["exchange"]["nvlink_peak_GBps"] = 900.0
-    print(json.dumps(line))
+            line["exchange"]["nvlink_measured_peer_copy_GBps"] = 770.0
+    return line
+
+
+def run_b200(args):
+    import torch
+    import torch.distributed as dist
+
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    assert torch.cuda.is_available(), "bench.py needs a GPU (no CPU fallback)"
+    torch.cuda.set_device(local_rank)
+    cpu_group = None
+    if world > 1:
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+        cpu_group = dist.new_group(backend="gloo")
+    names = [args.workload]
+    if args.all_configs:
+        names = ALL_CONFIGS_N1 if world == 1 else ALL_CONFIGS_NX
+    for i, name in enumerate(names):
+        if args.all_configs and world > 1 and i > 0:
+            args.no_e2e = True  # the host-memory run (N x 8 GB pinned twice over) once per invocation is enough
+        line = run_one(args, name, torch, dist, world, rank, local_rank, cpu_group)
+        if line is not None:
+            print(json.dumps(line), flush=True)
+        from rdst_b200 import _abi
+
+        _abi.lib().b200_release_scratch(-1)
+        torch.cuda.empty_cache()
     if world > 1:
         dist.destroy_process_group()
     return 0
@@ -496,6 +681,8 @@ def main():
                     help="N>1: fused partition + peer stores over NVLink (CUDA IPC); ce: chunked partition pipelined with "
                          "copy-engine pushes into the same IPC buffers; nccl: partition + NCCL all-to-all")
     ap.add_argument("--ce-chunks", type=int, default=8)
+    ap.add_argument("--all-configs", action="store_true",
+                    help="one JSON line per BASELINE.json config that fits this GPU count (N=1: configs 0-3; N>1: config 4 uniform and skewed)")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-cpu", action="store_true")
     args = ap.parse_args()

@@ -81,11 +81,66 @@ def main():
             good = got == exp
             print(f"[dist_check] {mode} {name} ({tm.get('exchange_path')}): {'ok' if good else 'MISMATCH'} splitters={tm.get('splitter_mode')} sizes={[s // es for s in sizes]}", flush=True)
             ok = ok and good
+    if os.environ.get("DIST_CHECK_BIG"):
+        ok = big_case(rank, world, mode) and ok
     dist.barrier()
     if peers:
         peers.close()
     dist.destroy_process_group()
     sys.exit(0 if ok else 1)
+
+
+def big_case(rank, world, mode):
+    """DIST_CHECK_BIG=<records per rank> (>= 32 Mi so that the local sort takes the hybrid route with bit-window
+    digits below the rank's fixed top bits): too large for the CPU oracle, so the GLOBAL result is checked on the
+    devices — every rank's range sorted, max(rank r) <= min(rank r + 1), record count and two multiset checksums
+    equal to the input's — plus oracle equality on rank 0's first 2 M output records against the oracle's sort of
+    the same key range gathered from all inputs."""
+    from rdst_b200.dist import PeerBuffers
+
+    n = int(os.environ["DIST_CHECK_BIG"])
+    key = RadixKey.for_dtype("u8")
+    g = torch.Generator(device="cuda").manual_seed(77 + rank)
+    src = torch.randint(-2**63, 2**63 - 1, (n,), dtype=torch.int64, device="cuda", generator=g)
+    work = src.clone()
+    scratch = None
+    peers = None
+    if mode in ("peer", "ce"):
+        peers = PeerBuffers(int(n * 8 * 1.3))
+        scratch = {"peers": peers}
+        if mode == "ce":
+            scratch.update({"part": torch.empty(n * 8, dtype=torch.uint8, device="cuda"), "ce_chunks": 3})
+    tm = {}
+    out, n_out = sharded_sort(work.view(torch.uint8).view(-1), n, key, scratch=scratch, timings=tm)
+    torch.cuda.synchronize()
+    res = out[: n_out * 8].view(torch.int64)
+    u = res ^ (-2**63)
+    ok = bool((u[1:] >= u[:-1]).all())
+    fl = torch.tensor([int(u[0]), int(u[-1]), n_out], dtype=torch.int64, device="cuda")
+    allfl = [torch.empty_like(fl) for _ in range(world)]
+    dist.all_gather(allfl, fl)
+    allfl = [[int(v) for v in t.tolist()] for t in allfl]
+    ok = ok and all(a[1] <= b[0] for a, b in zip(allfl, allfl[1:]))
+    chk = lambda t: [int(t.sum()), int(((t * 0x9E3779B1) ^ (t >> 7)).sum())]
+    tot = torch.tensor([n_out] + chk(res) + chk(src), dtype=torch.int64, device="cuda")
+    dist.all_reduce(tot)
+    tot = [int(v) for v in tot.tolist()]
+    ok = ok and tot[0] == n * world and tot[1:3] == tot[3:5]
+    # rank 0's first 2 M outputs = the 2 M smallest keys overall: gather every rank's candidates (its 2 M smallest)
+    m = min(2_000_000, n)
+    cand = torch.sort(src ^ (-2**63)).values[:m] ^ (-2**63)
+    allc = [torch.empty_like(cand) for _ in range(world)]
+    dist.all_gather(allc, cand)
+    if rank == 0:
+        pool = torch.cat(allc).cpu().numpy().view("u8")
+        exp = o.sorted_copy(pool, key)[:m]
+        ok = ok and res[:m].cpu().numpy().view("u8").tobytes() == exp.tobytes()
+        print(f"[dist_check] {mode} big u64 x {n} per rank, world {world} (local sort hybrid={tm['local'].get('hybrid')} "
+              f"unstable={tm['local'].get('unstable')}): {'ok' if ok else 'MISMATCH'} per-rank {[x[2] for x in allfl]}", flush=True)
+    if peers:
+        del scratch
+        peers.close()
+    return ok
 
 
 if __name__ == "__main__":

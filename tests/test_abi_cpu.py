@@ -160,3 +160,32 @@ def test_multi_gpu_entry_points_validate_arguments_without_a_device():
     odd = RadixKey.byte_array(5).to_desc()
     assert l.b200_sort_multi_host(None, 0, 2, None, C.byref(odd), None, None) == 2   # records of 4..16 bytes, multiple of 4
     assert l.b200_multi_release() == 0
+
+
+def test_rust_sys_crate_declares_every_header_symbol():
+    """rust/rdst-b200-sys is shipped as source (no Rust toolchain in this image): at least its extern block must
+    name exactly the functions of include/b200sort.h, and its struct fields the header's, in order."""
+    src = open(os.path.join(ROOT, "rust", "rdst-b200-sys", "src", "lib.rs")).read()
+    declared = sorted(set(re.findall(r"pub fn (b200_[a-z0-9_]+)\s*\(", src)))
+    assert declared == header_functions(), set(declared) ^ set(header_functions())
+    hdr = open(os.path.join(ROOT, "include", "b200sort.h")).read()
+    hdr = re.sub(r"/\*.*?\*/", "", hdr, flags=re.S)
+
+    def c_fields(name):
+        end = hdr.index("} " + name + ";")
+        body = hdr[hdr.rindex("{", 0, end) + 1:end]
+        out = []
+        for decl in body.split(";"):
+            decl = decl.strip()
+            if not decl:
+                continue
+            for part in decl.split(","):
+                out.append(re.sub(r"\[.*?\]", "", part.strip().split()[-1].lstrip("*")))
+        return out
+
+    def rust_fields(name):
+        body = re.search(r"pub struct " + name + r" \{(.*?)\n\}", src, flags=re.S).group(1)
+        return re.findall(r"pub (\w+):", body)
+
+    for t in ("b200_level", "b200_key_desc", "b200_sort_opts", "b200_stats", "b200_multi_stats", "b200_window_plan", "b200_route"):
+        assert rust_fields(t) == c_fields(t), t
