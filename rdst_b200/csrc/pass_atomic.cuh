@@ -20,6 +20,8 @@
 // Same-address atomics serialise, so the planner keeps skewed digits on the stable K2 (its ballot
 // path for hot buckets) — see pick_unstable() in b200sort.cu.
 #pragma once
+#include <type_traits>
+
 #include "pass_or.cuh"
 
 namespace b200 {
@@ -43,11 +45,14 @@ __device__ __forceinline__ uint32_t atom_add_shared(uint32_t saddr, uint32_t v) 
     return old;
 }
 
-template <int WORDS, int THREADS, int ITEMS, bool FLOATK, int MINB>
+template <int WORDS, int THREADS, int ITEMS, bool FLOATK, int MINB, bool VEC = false>
 __global__ void __launch_bounds__(THREADS, MINB) msd_pass_atomic_kernel(const PassParams p) {
+    static_assert(!VEC || (ITEMS % 2 == 0 && ITEMS <= 32), "vector loads take records in pairs");
     static_assert(THREADS >= RADIX && THREADS % 32 == 0, "one thread per digit is needed for the look-back");
     using SM = AtomSmem<WORDS, THREADS, ITEMS>;
     constexpr int TILE = SM::TILE;
+    // predecessors read per look-back round trip (8 / 16 / 32 measured slower: 4.62 / 5.20 / 9.1 ms per pass against
+    // 4.58 ms at 1 B u64 keys, profiles/r6_k2u_experiments.txt)
     constexpr int LB_BATCH = 4;
 
     extern __shared__ __align__(128) uint8_t smem_raw[];
@@ -78,14 +83,40 @@ __global__ void __launch_bounds__(THREADS, MINB) msd_pass_atomic_kernel(const Pa
         const uint64_t rem = nrec - uint64_t(t - t0) * TILE;
         return rem < uint64_t(TILE) ? uint32_t(rem) : uint32_t(TILE);
     };
-    // the order of records inside a bucket is free: plain coalesced element order e = j * THREADS + tid
+    // the order of records inside a bucket is free: plain coalesced element order e = j * THREADS + tid, or
+    // (VEC) records in aligned pairs — one 16-byte load per two u64 keys, half the load instructions
     Rec<WORDS> r[ITEMS];
+    uint32_t vmask = 0;  // VEC: bit j = r[j] holds a record of the tile
     auto load_tile = [&](uint32_t t, uint32_t b, uint32_t t0) {
+        vmask = 0;
         if (t >= p.num_tiles) return;
         const uint32_t v = tile_valid_at(t, b, t0);
         const uint64_t first = __ldg(p.seg_rec_start + b) + uint64_t(t - t0) * TILE;
         const uint32_t* g = p.src + first * WORDS;
-        if (v == uint32_t(TILE)) {
+        if constexpr (VEC) {
+            // a tile starts at any record: `head` records (0 or 1) up to pair alignment, npairs aligned pairs, maybe
+            // one tail record; head and tail go to the last slots of the last thread (free whenever they exist)
+            using Vec2 = typename std::conditional<WORDS == 1, uint2, uint4>::type;
+            const uint32_t head = uint32_t(first) & 1u, npairs = (v - head) >> 1;
+            const Vec2* gp = reinterpret_cast<const Vec2*>(g + head * WORDS);
+#pragma unroll
+            for (int k = 0; k < ITEMS / 2; ++k) {
+                const uint32_t q = uint32_t(k * THREADS + tid);
+                if (q < npairs) {
+                    const Vec2 x = gp[q];
+                    if constexpr (WORDS == 1) {
+                        r[2 * k].w[0] = x.x, r[2 * k + 1].w[0] = x.y;
+                    } else {
+                        r[2 * k].w[0] = x.x, r[2 * k].w[1] = x.y, r[2 * k + 1].w[0] = x.z, r[2 * k + 1].w[1] = x.w;
+                    }
+                    vmask |= 3u << (2 * k);
+                }
+            }
+            if (tid == THREADS - 1) {
+                if (head) r[ITEMS - 2] = load_rec<WORDS>(g, 0), vmask |= 1u << (ITEMS - 2);
+                if ((v - head) & 1u) r[ITEMS - 1] = load_rec<WORDS>(g, v - 1), vmask |= 1u << (ITEMS - 1);
+            }
+        } else if (v == uint32_t(TILE)) {
 #pragma unroll
             for (int j = 0; j < ITEMS; ++j) r[j] = load_rec<WORDS>(g, uint32_t(j * THREADS + tid));
         } else {
@@ -115,6 +146,8 @@ __global__ void __launch_bounds__(THREADS, MINB) msd_pass_atomic_kernel(const Pa
     uint32_t par = 0;  // which counter table this tile uses
 
     while (tile < p.num_tiles) {
+        // (claiming the next tile later in the trip — after the scan, or after the scatter — so that it publishes its
+        // counts sooner after the claim changed nothing: 4.75 / 4.65 against 4.55 ms, profiles/r6_k2u_experiments.txt)
         if (tid == 0) {  // read by everyone after barrier (B)
             const uint32_t t = atomicAdd(p.ticket, 1u);
             s_tile[1] = t;
@@ -125,11 +158,19 @@ __global__ void __launch_bounds__(THREADS, MINB) msd_pass_atomic_kernel(const Pa
         const bool full = valid == uint32_t(TILE);
         const uint32_t my_cnt = cnt_base + par * RADIX * 4;
 
-        // ---- count ----
+        // ---- count (the digits are kept, four per register, for the scatter) ----
+        const uint32_t mine = vmask;
+        auto have = [&](int j) { return VEC ? bool(mine >> j & 1u) : (full || uint32_t(j * THREADS + tid) < valid); };
+        uint32_t dcache[(ITEMS + 3) / 4];
+#pragma unroll
+        for (int q = 0; q < (ITEMS + 3) / 4; ++q) dcache[q] = 0;
 #pragma unroll
         for (int j = 0; j < ITEMS; ++j) {
-            if (full || uint32_t(j * THREADS + tid) < valid)
-                red_add_shared(my_cnt + rec_digit_w<WORDS, FLOATK, true>(dp, r[j]) * 4, 1u);
+            if (have(j)) {
+                const uint32_t d = rec_digit_w<WORDS, FLOATK, true>(dp, r[j]);
+                dcache[j / 4] |= d << ((j % 4) * 8);
+                red_add_shared(my_cnt + d * 4, 1u);
+            }
         }
         __syncthreads();  // (B)
 
@@ -174,13 +215,12 @@ __global__ void __launch_bounds__(THREADS, MINB) msd_pass_atomic_kernel(const Pa
             for (int u = 0; u < SB; ++u) {
                 const int j = j0 + u;
                 pos[u] = 0;
-                if (full || uint32_t(j * THREADS + tid) < valid)
-                    pos[u] = atom_add_shared(my_cnt + rec_digit_w<WORDS, FLOATK, true>(dp, r[j]) * 4, 1u);
+                if (have(j)) pos[u] = atom_add_shared(my_cnt + ((dcache[j / 4] >> ((j % 4) * 8)) & 0xffu) * 4, 1u);
             }
 #pragma unroll
             for (int u = 0; u < SB; ++u) {
                 const int j = j0 + u;
-                if (full || uint32_t(j * THREADS + tid) < valid) store_rec<WORDS>(s_out, pos[u], r[j]);
+                if (have(j)) store_rec<WORDS>(s_out, pos[u], r[j]);
             }
         }
         const uint32_t next_tile = s_tile[1];

@@ -9,7 +9,7 @@ namespace b200 {
 struct PassParams;
 struct LocalCountParams;
 
-constexpr int NUM_MSDU_VARIANTS = 4;
+constexpr int NUM_MSDU_VARIANTS = 8;
 struct MsdULaunch {
     void (*kernel)(const PassParams);
     size_t smem;

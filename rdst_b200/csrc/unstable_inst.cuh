@@ -6,11 +6,11 @@
 
 namespace b200 {
 
-template <int WORDS, bool FLOATK, int THREADS, int ITEMS, int MINB>
+template <int WORDS, bool FLOATK, int THREADS, int ITEMS, int MINB, bool VEC = false>
 static MsdULaunch make_msdu(const char* name) {
     using SM = AtomSmem<WORDS, THREADS, ITEMS>;
     MsdULaunch l{};
-    l.kernel = &msd_pass_atomic_kernel<WORDS, THREADS, ITEMS, FLOATK, MINB>;
+    l.kernel = &msd_pass_atomic_kernel<WORDS, THREADS, ITEMS, FLOATK, MINB, VEC>;
     l.smem = SM::TOTAL;
     l.tile = SM::TILE;
     l.threads = THREADS;
@@ -23,9 +23,13 @@ static MsdULaunch pick_msdu(int variant) {
     if constexpr (WORDS == 1) {
         switch (variant) {
             case 0: return make_msdu<WORDS, FLOATK, 256, 32, 4>("u256_i32_occ4");
-            case 1: return make_msdu<WORDS, FLOATK, 256, 48, 2>("u256_i48_occ2");
+            case 1: return make_msdu<WORDS, FLOATK, 256, 32, 3>("u256_i32_occ3");
             case 2: return make_msdu<WORDS, FLOATK, 512, 24, 2>("u512_i24_occ2");
             case 3: return make_msdu<WORDS, FLOATK, 256, 16, 5>("u256_i16_occ5");
+            case 4: return make_msdu<WORDS, FLOATK, 256, 32, 4, true>("v256_i32_occ4");
+            case 5: return make_msdu<WORDS, FLOATK, 512, 24, 2, true>("v512_i24_occ2");
+            case 6: return make_msdu<WORDS, FLOATK, 512, 16, 3, true>("v512_i16_occ3");
+            case 7: return make_msdu<WORDS, FLOATK, 256, 16, 5, true>("v256_i16_occ5");
         }
     } else {
         switch (variant) {
@@ -33,6 +37,10 @@ static MsdULaunch pick_msdu(int variant) {
             case 1: return make_msdu<WORDS, FLOATK, 256, 24, 3>("u256_i24_occ3");
             case 2: return make_msdu<WORDS, FLOATK, 512, 16, 2>("u512_i16_occ2");
             case 3: return make_msdu<WORDS, FLOATK, 256, 16, 4>("u256_i16_occ4");
+            case 4: return make_msdu<WORDS, FLOATK, 256, 32, 2, true>("v256_i32_occ2");
+            case 5: return make_msdu<WORDS, FLOATK, 256, 24, 3, true>("v256_i24_occ3");
+            case 6: return make_msdu<WORDS, FLOATK, 512, 16, 2, true>("v512_i16_occ2");
+            case 7: return make_msdu<WORDS, FLOATK, 256, 16, 4, true>("v256_i16_occ4");
         }
     }
     return MsdULaunch{};
