@@ -134,6 +134,9 @@ typedef struct {
                                   result is bit-identical to the stable engine's — rdst's default entry point is
                                   radix_sort_unstable, src/radix_sort.rs:21-45), bit 1 / bit 2 = MSD pass 1 / 2 ran
                                   the atomic-ranking kernel K2-U (flat digits only) */
+    uint32_t heavy_segments;   /* key-only hybrid route: segments too large for one SM (a heavily duplicated key makes its
+                                  whole segment long) that were split three ways around a pivot key instead of sorted */
+    uint32_t heavy_rounds;     /* pivot-split rounds that took (0 = no oversized segment) */
 } b200_stats;
 
 /*

@@ -79,6 +79,8 @@ class Stats(C.Structure):
         ("ms_joint", C.c_float),
         ("ms_local", C.c_float),
         ("unstable", C.c_uint32),
+        ("heavy_segments", C.c_uint32),
+        ("heavy_rounds", C.c_uint32),
     ]
 
     def as_dict(self):

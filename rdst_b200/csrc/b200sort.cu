@@ -34,6 +34,7 @@
 #include "variants.h"
 #include "unstable.h"
 #include "local_count.cuh"
+#include "heavy.cuh"
 
 using namespace b200;
 
@@ -157,6 +158,8 @@ struct DeviceCtx {
     cudaEvent_t bounce_ev[4] = {};
     uint32_t* d_slow = nullptr;  // hybrid key-only route: segments K3-U left to the stable K3 ([0] = count)
     size_t slow_bytes = 0;
+    uint8_t* d_heavy = nullptr;  // oversized segments (heavy.cuh): range tables, pivots, tile counts and bases, lists
+    size_t heavy_bytes = 0;
 };
 
 constexpr size_t SMALL_HIST_OFF = 0;
@@ -612,6 +615,10 @@ bool digit_is_flat(const uint64_t* hist, uint64_t n) {
     for (int b = 0; b < RADIX; ++b) m = std::max(m, hist[b]);
     return m <= n / 8;
 }
+bool heavy_split_enabled() {
+    const char* env = getenv("B200SORT_HEAVY");  // read per call: tests flip it
+    return !(env && atoi(env) == 0);
+}
 uint64_t hybrid_min_records(bool key_only, uint32_t words) {
     const char* env = getenv("B200SORT_HYBRID_MIN");
     if (env) return strtoull(env, nullptr, 10);
@@ -629,6 +636,192 @@ MsdULaunch get_msdu_launch(uint32_t words, bool floatk) {
     return words == 1 ? get_msdu_launch_w1(floatk, vv) : get_msdu_launch_w2(floatk, vv);
 }
 
+// ---------------------------------------------------------------------------
+// Oversized segments of the key-only hybrid route (heavy.cuh): split three ways around a pivot key, round
+// by round; equal parts are final, small parts go to K3-U, parts that are still oversized take the next round.
+// `ranges` = {first record, records} of the oversized segments, all living in `data`.  On return *ok says
+// whether everything was finished (else the caller falls back to LSD passes over `data`, which is a
+// permutation of the input at any time).
+// ---------------------------------------------------------------------------
+constexpr uint32_t HEAVY_MAX_ROUNDS = 6;
+constexpr size_t HEAVY_MAX_RANGES = 1 << 16;
+
+template <int WORDS>
+int launch_heavy_w(int which, bool floatk, int grid, int threads, cudaStream_t st, const HeavyRanges& hr) {
+    if (which == 0) {
+        if (floatk) pivot_kernel<WORDS, true><<<grid, threads, 0, st>>>(hr);
+        else pivot_kernel<WORDS, false><<<grid, threads, 0, st>>>(hr);
+    } else {
+        if (floatk) split_ends_kernel<WORDS, true><<<grid, HV_THREADS, 0, st>>>(hr);
+        else split_ends_kernel<WORDS, false><<<grid, HV_THREADS, 0, st>>>(hr);
+    }
+    CUDA_TRY(cudaGetLastError());
+    return B200_OK;
+}
+
+int sort_heavy(DeviceCtx& c, cudaStream_t st, void* data, void* tmp, const Lowered& lo, uint32_t words, std::vector<uint2> ranges,
+               LocalCountParams cp, LocalSortParams lp, uint32_t* launches, uint32_t* rounds_out, uint32_t* slow_out, bool* ok) {
+    *ok = false;
+    *rounds_out = 0;
+    const uint32_t cap = uint32_t(LS_CAP);
+    void* src = data;
+    void* dst = tmp;
+    uint32_t slow_total = 0;
+    const char* renv = getenv("B200SORT_HEAVY_ROUNDS");  // read per call: tests flip it
+    const uint32_t max_rounds = renv ? uint32_t(atoi(renv)) : HEAVY_MAX_ROUNDS;
+    for (uint32_t round = 0; round < max_rounds && !ranges.empty(); ++round) {
+        const size_t nr = ranges.size();
+        if (nr > HEAVY_MAX_RANGES) break;
+        // ---- tiles of the ranges ----
+        std::vector<uint32_t> h_off(nr), h_cnt(nr), h_ts(nr + 1);
+        uint64_t T = 0;
+        for (size_t i = 0; i < nr; ++i) {
+            h_off[i] = ranges[i].x, h_cnt[i] = ranges[i].y, h_ts[i] = uint32_t(T);
+            T += (uint64_t(ranges[i].y) + HV_TILE - 1) / HV_TILE;
+        }
+        h_ts[nr] = uint32_t(T);
+        // device scratch: off | cnt | tile_start | pivot | ends | pairs | chunks | chunk owners | slow list
+        uint64_t recs = 0;
+        for (size_t i = 0; i < nr; ++i) recs += ranges[i].y;
+        const size_t max_chunks = size_t(recs / 65536) + nr + 1;  // equal parts cut into pieces of <= 65 536 records
+        const size_t o_off = 0, o_cnt = o_off + nr * 4, o_ts = o_cnt + nr * 4, o_piv = (o_ts + (nr + 1) * 4 + 7) / 8 * 8,
+                     o_ends = o_piv + nr * 8, o_pairs = o_ends + nr * 8, o_chunks = o_pairs + 2 * nr * 8,
+                     o_owner = o_chunks + max_chunks * 8, o_slow = o_owner + max_chunks * 4, total = o_slow + (2 * nr + 1) * 4;
+        int rc = ensure_bytes(reinterpret_cast<void**>(&c.d_heavy), &c.heavy_bytes, total);
+        if (rc) return rc;
+        uint8_t* d = c.d_heavy;
+        CUDA_TRY(cudaMemcpyAsync(d + o_off, h_off.data(), nr * 4, cudaMemcpyHostToDevice, st));
+        CUDA_TRY(cudaMemcpyAsync(d + o_cnt, h_cnt.data(), nr * 4, cudaMemcpyHostToDevice, st));
+        CUDA_TRY(cudaMemcpyAsync(d + o_ts, h_ts.data(), (nr + 1) * 4, cudaMemcpyHostToDevice, st));
+        CUDA_TRY(cudaMemsetAsync(d + o_ends, 0, nr * 8, st));
+        HeavyRanges hr;
+        memset(&hr, 0, sizeof(hr));
+        hr.src = static_cast<const uint32_t*>(src);
+        hr.dst = static_cast<uint32_t*>(dst);
+        hr.range_off = reinterpret_cast<const uint32_t*>(d + o_off);
+        hr.range_cnt = reinterpret_cast<const uint32_t*>(d + o_cnt);
+        hr.range_tile_start = reinterpret_cast<const uint32_t*>(d + o_ts);
+        hr.nranges = uint32_t(nr);
+        hr.ntiles = uint32_t(T);
+        hr.pivot = reinterpret_cast<unsigned long long*>(d + o_piv);
+        hr.ends = reinterpret_cast<uint32_t*>(d + o_ends);
+        hr.xorv = cp.key.xorv;
+        const int tgrid = int(std::min<uint64_t>(T, uint64_t(c.sm_count) * 8));
+        // ---- a pivot per range; one read of the ranges moves the smaller / larger records to the other buffer ----
+        rc = words == 1 ? launch_heavy_w<1>(0, lo.is_float, int((nr + 127) / 128), 128, st, hr)
+                        : launch_heavy_w<2>(0, lo.is_float, int((nr + 127) / 128), 128, st, hr);
+        if (rc) return rc;
+        rc = words == 1 ? launch_heavy_w<1>(1, lo.is_float, tgrid, HV_THREADS, st, hr) : launch_heavy_w<2>(1, lo.is_float, tgrid, HV_THREADS, st, hr);
+        if (rc) return rc;
+        *launches += 2;
+        std::vector<uint32_t> h_ends(2 * nr);
+        CUDA_TRY(cudaMemcpyAsync(h_ends.data(), d + o_ends, nr * 8, cudaMemcpyDeviceToHost, st));
+        CUDA_TRY(cudaStreamSynchronize(st));
+        // ---- what happens to every part: equal part = the pivot record written into `data`, small parts to K3-U
+        // (read from `dst`, written sorted into `data`), oversized parts to the next round (they live in `dst`) ----
+        std::vector<uint2> next, pairs, chunks;
+        std::vector<uint32_t> owner;
+        uint32_t max_small = 0;
+        for (size_t i = 0; i < nr; ++i) {
+            const uint32_t off = h_off[i], cnt = h_cnt[i], LT = h_ends[2 * i], GT = h_ends[2 * i + 1], EQ = cnt - LT - GT;
+            // the equal records were never moved: where the range lives in `data` and nothing smaller or larger was found
+            // they are in place already; otherwise the middle of the range is written
+            if (EQ && !(src == data && LT == 0 && GT == 0))
+                for (uint32_t at = 0; at < EQ; at += 65536)
+                    chunks.push_back(make_uint2(off + LT + at, std::min<uint32_t>(65536, EQ - at))), owner.push_back(uint32_t(i));
+            const uint2 parts[2] = {make_uint2(off, LT), make_uint2(off + cnt - GT, GT)};
+            for (const uint2& pt : parts) {
+                if (pt.y == 0) continue;
+                if (pt.y > cap) next.push_back(pt);
+                else pairs.push_back(pt), max_small = std::max(max_small, pt.y);
+            }
+        }
+        if (chunks.size() > max_chunks || pairs.size() > 2 * nr) {
+            g_last_cuda_error = "heavy segments: list sizes exceed their bounds";
+            return B200_ERR_CUDA;
+        }
+        if (!chunks.empty()) {
+            CUDA_TRY(cudaMemcpyAsync(d + o_chunks, chunks.data(), chunks.size() * 8, cudaMemcpyHostToDevice, st));
+            CUDA_TRY(cudaMemcpyAsync(d + o_owner, owner.data(), owner.size() * 4, cudaMemcpyHostToDevice, st));
+            const int cgrid = int(std::min<uint64_t>(chunks.size(), uint64_t(c.sm_count) * 8));
+            if (words == 1)
+                fill_kernel<1><<<cgrid, 256, 0, st>>>(static_cast<uint32_t*>(data), reinterpret_cast<const uint2*>(d + o_chunks),
+                                                      reinterpret_cast<const uint32_t*>(d + o_owner), uint32_t(chunks.size()), hr.pivot);
+            else
+                fill_kernel<2><<<cgrid, 256, 0, st>>>(static_cast<uint32_t*>(data), reinterpret_cast<const uint2*>(d + o_chunks),
+                                                      reinterpret_cast<const uint32_t*>(d + o_owner), uint32_t(chunks.size()), hr.pivot);
+            CUDA_TRY(cudaGetLastError());
+            *launches += 1;
+        }
+        // ---- small parts: K3-U reads them where the split put them and writes them, sorted, into `data` ----
+        if (!pairs.empty()) {
+            CUDA_TRY(cudaMemcpyAsync(d + o_pairs, pairs.data(), pairs.size() * 8, cudaMemcpyHostToDevice, st));
+            uint32_t* d_slow2 = reinterpret_cast<uint32_t*>(d + o_slow);
+            CUDA_TRY(cudaMemsetAsync(d_slow2, 0, 4, st));
+            CUDA_TRY(cudaMemsetAsync(cp.ticket, 0, 4, st));
+            const int size = max_small <= 4096 ? 0 : (max_small <= 8192 ? 1 : 2);
+            const LocalCountLaunch ll = words == 1 ? get_local_count_launch_w1(lo.is_float, size, true) : get_local_count_launch_w2(lo.is_float, size, false);
+            cp.data = static_cast<uint32_t*>(data);
+            cp.src = dst != data ? static_cast<const uint32_t*>(dst) : nullptr;
+            cp.seg_off = nullptr;
+            cp.seg_pairs = reinterpret_cast<const uint2*>(d + o_pairs);
+            cp.seg_first = 0;
+            cp.nseg = uint32_t(pairs.size());
+            cp.bmax = std::min<uint32_t>(cp.bmax, uint32_t(ll.cbits));
+            cp.slow_list = d_slow2;
+            cp.prof = nullptr;
+            CUDA_TRY(cudaFuncSetAttribute(ll.kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, int(ll.smem)));
+            int occ = 1;
+            CUDA_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, ll.kernel, ll.threads, ll.smem));
+            const int ugrid = int(std::min<uint64_t>(uint64_t(c.sm_count) * std::max(occ, 1), pairs.size()));
+            ll.kernel<<<ugrid, ll.threads, ll.smem, st>>>(cp);
+            CUDA_TRY(cudaGetLastError());
+            // what K3-U could not finish (now in `data`, as a permutation): the stable segment sort, from the list
+            CUDA_TRY(cudaMemsetAsync(lp.ticket, 0, 4, st));
+            lp.data = static_cast<uint32_t*>(data);
+            lp.seg_off = nullptr;
+            lp.seg_pairs = cp.seg_pairs;
+            lp.nseg = cp.nseg;
+            lp.list = d_slow2;
+            const int lgrid = int(std::min<uint64_t>(uint64_t(c.sm_count), pairs.size()));
+            rc = words == 1 ? launch_local_sort_w<1>(lo.is_float, lgrid, st, lp) : launch_local_sort_w<2>(lo.is_float, lgrid, st, lp);
+            if (rc) return rc;
+            *launches += 2;
+            uint32_t slow = 0;
+            CUDA_TRY(cudaMemcpyAsync(&slow, d_slow2, 4, cudaMemcpyDeviceToHost, st));
+            CUDA_TRY(cudaStreamSynchronize(st));
+            slow_total += slow;
+        }
+        ranges.swap(next);
+        std::swap(src, dst);  // the parts of this round live in the buffer the split wrote into
+        *rounds_out = round + 1;
+    }
+    if (slow_out) *slow_out = slow_total;
+    if (!ranges.empty()) {
+        // still oversized after the last round: bring those ranges home and let the caller run the LSD passes
+        if (src != data) {
+            std::vector<uint2> chunks;
+            for (const uint2& r : ranges)
+                for (uint32_t at = 0; at < r.y; at += 65536) chunks.push_back(make_uint2(r.x + at, std::min<uint32_t>(65536, r.y - at)));
+            int rc = ensure_bytes(reinterpret_cast<void**>(&c.d_heavy), &c.heavy_bytes, chunks.size() * 8);
+            if (rc) return rc;
+            CUDA_TRY(cudaMemcpyAsync(c.d_heavy, chunks.data(), chunks.size() * 8, cudaMemcpyHostToDevice, st));
+            const int cgrid = int(std::min<uint64_t>(chunks.size(), uint64_t(c.sm_count) * 8));
+            if (words == 1)
+                copy_ranges_kernel<1><<<cgrid, 256, 0, st>>>(static_cast<const uint32_t*>(tmp), static_cast<uint32_t*>(data),
+                                                             reinterpret_cast<const uint2*>(c.d_heavy), uint32_t(chunks.size()));
+            else
+                copy_ranges_kernel<2><<<cgrid, 256, 0, st>>>(static_cast<const uint32_t*>(tmp), static_cast<uint32_t*>(data),
+                                                             reinterpret_cast<const uint2*>(c.d_heavy), uint32_t(chunks.size()));
+            CUDA_TRY(cudaGetLastError());
+            CUDA_TRY(cudaStreamSynchronize(st));
+        }
+        return B200_OK;
+    }
+    *ok = true;
+    return B200_OK;
+}
+
 // How one sort call is driven (what b200_sort_opts carries, plus what the host entry point adds).
 struct SortCtl {
     int variant = -1;             // >= 0: that tile variant, LSD passes only
@@ -643,6 +836,7 @@ struct SortCtl {
     cudaStream_t drain_stream = nullptr;
     cudaEvent_t drain_event = nullptr;
     bool drained = false;         // out: the result is already on its way to drain_host (all of it)
+    uint32_t heavy_segments = 0, heavy_rounds = 0;  // out: oversized segments split around pivots (heavy.cuh)
 };
 
 // Returns B200_OK with *done = true when the array was sorted here (result in `data`);
@@ -731,7 +925,11 @@ int sort_hybrid(DeviceCtx& c, cudaStream_t st, void* data, void* tmp, uint64_t n
         // check follows the joint histogram)
         uint64_t m1 = 0, m2 = 0;
         for (int b = 0; b < RADIX; ++b) m1 = std::max(m1, hw[b]), m2 = std::max(m2, hw[RADIX + b]);
-        if (double(m1) * double(m2) / double(n) > 0.97 * LS_CAP) return B200_OK;
+        // key-only records may still take the route when oversized segments are to be expected: those of heavily
+        // duplicated keys are split around a pivot instead of sorted (heavy.cuh).  Marginals with a bucket above a
+        // quarter of the records are clustered keys, not duplicates: passes.
+        const bool may_split = key_only && heavy_split_enabled() && m1 <= n / 4 && m2 <= n / 4;
+        if (double(m1) * double(m2) / double(n) > 0.97 * LS_CAP && !may_split) return B200_OK;
     }
 
     // ---- the pass kernels: stable K2 (SEG instantiation) or, for key-only records, K2-U ----
@@ -839,7 +1037,17 @@ int sort_hybrid(DeviceCtx& c, cudaStream_t st, void* data, void* tmp, uint64_t n
         g_last_cuda_error = "hybrid: joint histogram does not sum to n";
         return B200_ERR_CUDA;
     }
-    if (max_seg > uint64_t(LS_CAP)) return B200_OK;  // *done stays false, records are in tmp
+    std::vector<uint2> big;  // oversized segments {first record, records}
+    if (max_seg > uint64_t(LS_CAP)) {
+        // records with a payload, or too much of the array in oversized segments: *done stays false, records are in tmp
+        if (!key_only || !heavy_split_enabled()) return B200_OK;
+        uint64_t big_total = 0;
+        for (uint32_t i = 0; i < uint32_t(RADIX * RADIX); ++i) {
+            const uint64_t cnt = c.h_joint[i + 1] - c.h_joint[i];
+            if (cnt > uint64_t(LS_CAP)) big.push_back(make_uint2(uint32_t(c.h_joint[i]), uint32_t(cnt))), big_total += cnt;
+        }
+        if (big.size() > 16384 || big_total > n / 10 * 9) return B200_OK;
+    }
     CUDA_TRY(cudaMemcpyAsync(d_seg, c.h_joint, size_t(RADIX * RADIX + 1) * 8, cudaMemcpyHostToDevice, st));
     // ---- MSD pass 2: tmp -> data on the second digit, every bucket of the first partitioned on its own ----
     uint32_t h_tile_start[RADIX + 1];
@@ -892,7 +1100,7 @@ int sort_hybrid(DeviceCtx& c, cudaStream_t st, void* data, void* tmp, uint64_t n
         if (rc) return rc;
         CUDA_TRY(cudaMemsetAsync(c.d_slow, 0, 4, st));
         const int force_size = getenv("B200SORT_K3U_SIZE") ? atoi(getenv("B200SORT_K3U_SIZE")) : -1;  // read per call: tests flip it
-        int size = max_seg <= 4096 ? 0 : (max_seg <= 8192 ? 1 : 2);
+        int size = max_seg <= 4096 ? 0 : (max_seg <= 8192 ? 1 : 2);  // (oversized segments are skipped by K3-U: size 2 then)
         if (force_size >= 0 && force_size <= 2) size = std::max(size, force_size);
         // twice the threads with half the records each: pays for 4-byte keys (0.69 against 0.81 ms at 100 M u32,
         // 3.59 against 3.88 ms at 500 M f32), loses for 8-byte keys whose 64-register budget spills
@@ -918,7 +1126,7 @@ int sort_hybrid(DeviceCtx& c, cudaStream_t st, void* data, void* tmp, uint64_t n
         const int ugrid = int(std::min<uint64_t>(uint64_t(c.sm_count) * occ, nonempty ? nonempty : 1));
         // Segments are claimed in memory order, so the sort can run in slices of consecutive segments; the host
         // entry point uses that to start the D2H copy of a finished slice while the next one is sorted.
-        const bool drain = ctl && ctl->drain_host && n * lo.elem_size >= (size_t(256) << 20);
+        const bool drain = ctl && ctl->drain_host && n * lo.elem_size >= (size_t(256) << 20) && big.empty();
         const uint32_t slices = drain ? 8u : 1u;
         for (uint32_t sl = 0; sl < slices; ++sl) {
             cp.seg_first = uint32_t(uint64_t(RADIX * RADIX) * sl / slices);
@@ -958,6 +1166,20 @@ int sort_hybrid(DeviceCtx& c, cudaStream_t st, void* data, void* tmp, uint64_t n
         if (rc) return rc;
         *launches += 1;
         if (unstable_out) *unstable_out = 1u | (u1 ? 2u : 0u) | (u2 ? 4u : 0u);
+        if (!big.empty()) {
+            bool finished = false;
+            uint32_t rounds = 0, slow2 = 0;
+            cp.ticket = d_tk + 12;
+            rc = sort_heavy(c, st, data, tmp, lo, words, big, cp, lp, launches, &rounds, &slow2, &finished);
+            if (rc) return rc;
+            if (ctl) ctl->heavy_segments = uint32_t(big.size()), ctl->heavy_rounds = rounds;
+            if (dbg) fprintf(stderr, "[b200sort] hybrid: %zu oversized segments, %u pivot-split rounds, %s\n", big.size(), rounds,
+                             finished ? "finished" : "NOT finished: LSD passes over the array");
+            if (!finished) {
+                *src_out = data;  // a permutation of the input; the caller runs the LSD passes on it
+                return B200_OK;
+            }
+        }
     } else {
         // fast levels: as many of the top local levels as make runs of equal prefixes rare
         const double avg = double(n) / double(std::max<uint64_t>(1, nonempty));
@@ -1379,6 +1601,8 @@ int sort_device_impl(DeviceCtx& c, cudaStream_t st, void* data, void* tmp, uint6
         stats->levels_skipped = lo.levels - pass;
         stats->hybrid = hybrid_done ? 1u : (msd1_done ? 2u : 0u);
         stats->unstable = hybrid_done ? unstable : 0u;
+        stats->heavy_segments = ctl.heavy_segments;
+        stats->heavy_rounds = ctl.heavy_rounds;
         stats->slow_segments = slow_segments;
         stats->local_levels = hybrid_done ? local_levels : (msd1_done ? msd1_local : 0);
         stats->ms_joint = stats->ms_local = 0.0f;
@@ -2176,7 +2400,8 @@ int b200_route_plan(const b200_key_desc* desc, const uint64_t* hist, size_t n, b
                     m1 = std::max(m1, hist[size_t(wp.w1_lo / 8) * RADIX + b]);
                     m2 = std::max(m2, hist[size_t(wp.w2_lo / 8) * RADIX + b]);
                 }
-                ok = double(m1) * double(m2) / double(n) <= 0.97 * LS_CAP;
+                ok = double(m1) * double(m2) / double(n) <= 0.97 * LS_CAP ||
+                     (key_only_record(lo) && heavy_split_enabled() && m1 <= n / 4 && m2 <= n / 4);  // pivot splits (heavy.cuh)
             }
             if (ok) {
                 out->route = B200_ROUTE_HYBRID;

@@ -32,8 +32,10 @@ namespace b200 {
 constexpr int LC_MAXRUN = 16;
 
 struct LocalCountParams {
-    uint32_t* data;           // sorted in place, segment by segment
+    uint32_t* data;           // where the sorted segments go (sorted in place when src is null)
+    const uint32_t* src;      // where the segments are read from; nullptr = data
     const uint64_t* seg_off;  // [nseg + 1] record offsets of the segments
+    const uint2* seg_pairs;   // alternative to seg_off: [nseg] {first record, records} of arbitrary, non-adjacent segments
     uint32_t seg_first;       // this launch sorts segments [seg_first, nseg)
     uint32_t nseg;
     uint32_t* ticket;         // zeroed before the launch
@@ -108,18 +110,31 @@ __global__ void __launch_bounds__(THREADS, MINB) local_count_kernel(const LocalC
     // record.  The order of records inside a segment is free, so thread t simply takes pairs t, t + THREADS, ...;
     // head and tail go to the last slots of the last thread (free whenever they exist, as cnt <= CAP).
     uint32_t cnt = 0, head = 0, vmask = 0;  // vmask: bit j = r[j] holds a record
-    uint32_t* g = nullptr;
+    const uint32_t* g = nullptr;
+    uint64_t gbase = 0;
     Rec<WORDS> r[ITEMS];
     using Vec2 = typename std::conditional<WORDS == 1, uint2, uint4>::type;
     auto fetch = [&](uint32_t sg) {
         cnt = 0;
         vmask = 0;
         if (sg >= p.nseg) return;
-        const uint64_t base = p.seg_off[sg];
-        cnt = uint32_t(p.seg_off[sg + 1] - base);
-        g = p.data + base * WORDS;
+        uint64_t base;
+        if (p.seg_pairs) {
+            const uint2 pr = p.seg_pairs[sg];
+            base = pr.x, cnt = pr.y;
+        } else {
+            base = p.seg_off[sg];
+            cnt = uint32_t(p.seg_off[sg + 1] - base);
+        }
+        if (cnt > uint32_t(SM::CAP)) cnt = 0;  // oversized segments are somebody else's (heavy.cuh): skip
+        gbase = base;
+        g = (p.src ? p.src : p.data) + base * WORDS;
         head = uint32_t(base) & 1u;
-        if (cnt <= 1) return;
+        if (cnt <= 1) {
+            // a single record still has to travel when the segments are read from another buffer
+            if (cnt == 1 && p.src && tid == 0) store_rec<WORDS>(p.data, base, load_rec<WORDS>(g, 0));
+            return;
+        }
         const uint32_t npairs = (cnt - head) >> 1;
         const Vec2* gp = reinterpret_cast<const Vec2*>(g + head * WORDS);
 #pragma unroll
@@ -176,7 +191,7 @@ __global__ void __launch_bounds__(THREADS, MINB) local_count_kernel(const LocalC
             continue;
         }
         const uint32_t cur_cnt = cnt, cur_seg = seg, cur_head = head, mine = vmask;
-        uint32_t* const cur_g = g;
+        uint32_t* const cur_g = p.data + gbase * WORDS;
         // staging positions are shifted by `head`, so that the aligned pairs of the write-out are aligned here too
         uint32_t* const st = s_out + cur_head * WORDS;
         auto key_at = [&](uint32_t i) { return key_image<WORDS, FLOATK>(load_rec<WORDS>(st, i), xorv); };
@@ -388,30 +403,72 @@ __global__ void __launch_bounds__(THREADS, MINB) local_count_kernel(const LocalC
         __syncthreads();  // (5)
         tick(5);
         if (flag[2]) {
-            // runs longer than LC_MAXRUN: fine if all their keys are equal (heavy duplicates: nothing to order),
-            // else the stable segment sort takes this segment
+            // Runs longer than LC_MAXRUN are heavy duplicates: one key many times over, plus at most a few other keys
+            // that share its digit.  A warp reads the run once, keeps the records that differ from the dominant key
+            // (the one in the middle of the run) in its lanes — up to 32 of them —, ranks those among themselves and
+            // rewrites the run as [smaller keys, sorted][the dominant key, copied][larger keys, sorted]: equal keys
+            // are identical records, so copies are as good as the originals.  More than 32 other keys in one run:
+            // the stable segment sort takes the segment.
             for (uint32_t q0 = 0; q0 < nruns; q0 += 32) {
                 const uint32_t e = q0 + lane < nruns ? s_runs[runs_at + q0 + lane] : 0u;
-                uint32_t m = __ballot_sync(0xffffffffu, (e >> 16) > uint32_t(LC_MAXRUN));
-                while (m) {
-                    const int src = __ffs(m) - 1;
-                    m &= m - 1;
-                    const uint32_t ee = __shfl_sync(0xffffffffu, e, src), at = ee & 0xffffu, c = ee >> 16;
-                    const KT k0 = key_at(at);
-                    bool same = true;
-                    for (uint32_t i = at + 1 + lane; i < at + c; i += 32) same = same && key_at(i) == k0;
-                    if (!__all_sync(0xffffffffu, same) && lane == 0) flag[3] = 1;
+                uint32_t lm = __ballot_sync(0xffffffffu, (e >> 16) > uint32_t(LC_MAXRUN));
+                while (lm) {
+                    const int srcl = __ffs(lm) - 1;
+                    lm &= lm - 1;
+                    const uint32_t ee = __shfl_sync(0xffffffffu, e, srcl), at = ee & 0xffffu, c = ee >> 16;
+                    const Rec<WORDS> pv = load_rec<WORDS>(st, at + c / 2);
+                    const KT kpv = key_image<WORDS, FLOATK>(pv, xorv);
+                    uint32_t m = 0;  // other keys found so far (warp-uniform); lane l < m holds the l-th of them
+                    Rec<WORDS> other;
+#pragma unroll
+                    for (int k = 0; k < WORDS; ++k) other.w[k] = 0;
+                    bool overflow = false;
+                    for (uint32_t i0 = at; i0 < at + c && !overflow; i0 += 32) {
+                        const uint32_t i = i0 + lane;
+                        const bool have = i < at + c;
+                        Rec<WORDS> x = pv;
+                        if (have) x = load_rec<WORDS>(st, i);
+                        const uint32_t nm = __ballot_sync(0xffffffffu, have && key_image<WORDS, FLOATK>(x, xorv) != kpv);
+                        const uint32_t found = __popc(nm);
+                        if (m + found > 32) {
+                            overflow = true;
+                        } else if (found) {
+                            // lane l in [m, m + found) takes the (l - m + 1)-th record flagged in nm
+                            const uint32_t from = __fns(nm, 0, int(uint32_t(lane) - m) + 1);
+                            Rec<WORDS> y;
+#pragma unroll
+                            for (int k = 0; k < WORDS; ++k) y.w[k] = __shfl_sync(0xffffffffu, x.w[k], from & 31u);
+                            if (uint32_t(lane) >= m && uint32_t(lane) < m + found) other = y;
+                            m += found;
+                        }
+                    }
+                    if (overflow) {
+                        if (lane == 0) flag[3] = 1;
+                    } else if (m) {
+                        const KT ko = key_image<WORDS, FLOATK>(other, xorv);
+                        const bool mine_ok = uint32_t(lane) < m;
+                        uint32_t rank = 0;  // among the other keys
+                        for (uint32_t i = 0; i < m; ++i) {
+                            const KT ky = KT(__shfl_sync(0xffffffffu, ko, int(i)));
+                            rank += (ky < ko || (ky == ko && i < uint32_t(lane))) ? 1u : 0u;
+                        }
+                        const uint32_t nlt = __popc(__ballot_sync(0xffffffffu, mine_ok && ko < kpv)), neq = c - m;
+                        __syncwarp();
+                        for (uint32_t i = at + nlt + lane; i < at + nlt + neq; i += 32) store_rec<WORDS>(st, i, pv);
+                        if (mine_ok) store_rec<WORDS>(st, at + rank + (ko > kpv ? neq : 0u), other);
+                    }
                 }
             }
             __syncthreads();
         }
         // ---- write-out ----
-        if (flag[3]) {
-            if (tid == 0) {
-                const uint32_t at = atomicAdd(p.slow_list, 1u);
-                p.slow_list[1 + at] = cur_seg;
-            }
-        } else {
+        // a segment for the slow list is written out all the same (as it stands: a permutation of its records), so
+        // that the stable segment sort finds it in `data` whatever buffer it was read from
+        if (flag[3] && tid == 0) {
+            const uint32_t at = atomicAdd(p.slow_list, 1u);
+            p.slow_list[1 + at] = cur_seg;
+        }
+        {
             // aligned pairs: one vector load from the staging buffer, one vector store
             const uint32_t npairs = (cur_cnt - cur_head) >> 1;
             Vec2* gp = reinterpret_cast<Vec2*>(cur_g + cur_head * WORDS);

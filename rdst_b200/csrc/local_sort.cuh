@@ -35,6 +35,7 @@ struct LocalSortParams {
     SplitParams key;           // 64-bit order-preserving image of the whole key (LEVELS <= 8)
     uint32_t* slow_segments;   // telemetry: segments that fell back to the full LSD
     unsigned long long* prof;  // optional [8] cycle counters per phase (thread 0 of every CTA), nullptr = off
+    const uint2* seg_pairs;    // alternative to seg_off: [nseg] {first record, records} (segments need not be adjacent)
     const uint32_t* list;      // list mode (nullptr = off): sort segments list[1 .. list[0]] only — the ones K3-U
                                // (local_count.cuh) left behind; the count is read on the device, no host round trip
 };
@@ -83,8 +84,14 @@ __global__ void __launch_bounds__(LS_THREADS, 1) local_sort_kernel(const LocalSo
         cnt = 0;
         if (sg >= nseg) return;
         if (p.list) sg = __ldg(p.list + 1 + sg);
-        const uint64_t base = p.seg_off[sg];
-        cnt = uint32_t(p.seg_off[sg + 1] - base);
+        uint64_t base;
+        if (p.seg_pairs) {
+            const uint2 pr = p.seg_pairs[sg];
+            base = pr.x, cnt = pr.y;
+        } else {
+            base = p.seg_off[sg];
+            cnt = uint32_t(p.seg_off[sg + 1] - base);
+        }
         g = p.data + base * WORDS;
         // records per thread actually used: element (group, j, lane16) = group*16*IT + j*16 + lane16,
         // so that every half-warp owns a contiguous run and (group, j, lane) order is memory order

@@ -96,6 +96,8 @@ pub struct b200_stats {
     pub ms_joint: f32,
     pub ms_local: f32,
     pub unstable: u32,
+    pub heavy_segments: u32,
+    pub heavy_rounds: u32,
 }
 
 #[repr(C)]
@@ -205,6 +207,6 @@ extern "C" {
 const _: () = assert!(std::mem::size_of::<b200_level>() == 4);
 const _: () = assert!(std::mem::size_of::<b200_key_desc>() == 24 + 4 * B200_MAX_LEVELS);
 const _: () = assert!(std::mem::size_of::<b200_sort_opts>() == 32);
-const _: () = assert!(std::mem::size_of::<b200_stats>() == 88);
-const _: () = assert!(std::mem::size_of::<b200_multi_stats>() == 272);
+const _: () = assert!(std::mem::size_of::<b200_stats>() == 96);
+const _: () = assert!(std::mem::size_of::<b200_multi_stats>() == 280);
 const _: () = assert!(std::mem::size_of::<b200_route>() == 24);

@@ -47,8 +47,8 @@ def test_struct_layouts_match_header():
     assert C.sizeof(_abi.KeyDesc) == 24 + 4 * 64
     assert C.sizeof(_abi.SortOpts) == 32 and _abi.SortOpts.route.offset == 24
     assert _abi.Stats.algorithmic_bytes.offset == 16
-    assert C.sizeof(_abi.Stats) == 88 and _abi.Stats.unstable.offset == 84
-    assert C.sizeof(_abi.MultiStats) == 272 and _abi.MultiStats.local0.offset == 184
+    assert C.sizeof(_abi.Stats) == 96 and _abi.Stats.unstable.offset == 84 and _abi.Stats.heavy_rounds.offset == 92
+    assert C.sizeof(_abi.MultiStats) == 280 and _abi.MultiStats.local0.offset == 184
 
 
 KEYS = [RadixKey.for_dtype(d) for d in ("u1", "u2", "u4", "u8", "i1", "i2", "i4", "i8", "f4", "f8")] + [

@@ -735,6 +735,25 @@ def _hybrid_cases():
     yield "u64_slow_list", "u8", top | (rng.integers(0, 2, n, dtype="u8") << np.uint64(40)) | rng.integers(0, 256, n, dtype="u8"), True
     # heavy duplicates inside big segments: long runs of EQUAL keys need no fix-up (warp check)
     yield "u64_big_segments_few_values", "u8", top | (rng.integers(0, 3, n, dtype="u8") * np.uint64(0x0000051234567891)), True
+    # oversized segments (key-only route: split around pivot keys, heavy.cuh; stable route: falls back to LSD passes)
+    heavy = rng.integers(0, 2**64, n, dtype="u8")
+    heavy[rng.random(n) < 0.3] = np.uint64(0x123456789ABCDEF0)          # one key holds 30 % of the records
+    yield "u64_one_heavy_key", "u8", heavy, None
+    heavy2 = heavy.copy()
+    heavy2[rng.random(n) < 0.1] = np.uint64(0x123456789ABCDEF0 + 5)      # a second heavy key in the same segment: two rounds
+    heavy2[rng.random(n) < 0.05] = np.uint64(0xFEDC000000000001)
+    yield "u64_heavy_keys_share_a_segment", "u8", heavy2, None
+    cluster = rng.integers(0, 2**64, n, dtype="u8")
+    m = rng.random(n) < 0.08                                             # 120 k DISTINCT keys in one segment: quicksort-like rounds
+    cluster[m] = np.uint64(0xABCD000000000000) | (cluster[m] & np.uint64(0xFFFFFFFFFFFF))
+    yield "u64_oversized_cluster", "u8", cluster, None
+    yield "i64_one_heavy_key", "i8", heavy.view("i8"), None
+    hf = rand_bits(rng, "f8", n)
+    hf[rng.random(n) < 0.25] = -1.5
+    yield "f64_one_heavy_key", "f8", hf, None
+    h4 = rng.integers(0, 2**32, n, dtype="u4")
+    h4[rng.random(n) < 0.4] = np.uint32(0xDEADBEEF)
+    yield "u32_one_heavy_key", "u4", h4, None
     yield "u32_big_segments", "u4", ((rng.integers(0, 16, n, dtype="u4") << np.uint32(28)) | (rng.integers(0, 16, n, dtype="u4") << np.uint32(20))
                                      | rng.integers(0, 2**16, n, dtype="u4")), True
 
@@ -765,6 +784,26 @@ def test_hybrid_path_matches_oracle(monkeypatch, name, dt, a, expect_hybrid, uns
         assert bool(b.stats["unstable"] & 1) == bool(unstable), b.stats
     if name == ("u64_slow_list" if unstable else "u64_dups"):
         assert b.stats["slow_segments"] > 0, b.stats
+    if unstable and name in ("u64_one_heavy_key", "u64_heavy_keys_share_a_segment", "u64_oversized_cluster", "i64_one_heavy_key",
+                             "f64_one_heavy_key", "u32_one_heavy_key", "u64_zipf_hashed"):
+        assert b.stats["hybrid"] == 1 and b.stats["heavy_segments"] >= 1 and b.stats["heavy_rounds"] >= 1, b.stats
+        if name == "u64_heavy_keys_share_a_segment":
+            assert b.stats["heavy_rounds"] >= 2, b.stats
+        # cut the rounds short: the route gives up cleanly and the LSD passes finish the job
+        monkeypatch.setenv("B200SORT_HEAVY_ROUNDS", "1" if name != "u64_one_heavy_key" else "0")
+        t3 = torch.from_numpy(np.ascontiguousarray(a).view(np.uint8).reshape(-1).copy()).cuda()
+        b3 = radix_sort_builder(t3, key)
+        b3.sort()
+        torch.cuda.synchronize()
+        assert t3.cpu().numpy().tobytes() == exp.tobytes(), name + " rounds cut short"
+        monkeypatch.delenv("B200SORT_HEAVY_ROUNDS")
+        monkeypatch.setenv("B200SORT_HEAVY", "0")  # the switch: oversized segments send the array to the LSD passes at once
+        t4 = torch.from_numpy(np.ascontiguousarray(a).view(np.uint8).reshape(-1).copy()).cuda()
+        b4 = radix_sort_builder(t4, key)
+        b4.sort()
+        torch.cuda.synchronize()
+        assert t4.cpu().numpy().tobytes() == exp.tobytes() and b4.stats["heavy_segments"] == 0, name + " heavy off"
+        monkeypatch.delenv("B200SORT_HEAVY")
     if unstable and name in ("u64_dups", "u64_big_segments_few_values"):
         assert b.stats["slow_segments"] == 0, b.stats  # long runs of equal keys are not a reason to fall back
     # the host entry point takes the same route
