@@ -126,6 +126,23 @@ def test_hybrid_route_rule_on_synthetic_histograms():
     h[7, 0] = h[7, 1] = n // 2
     name, r = route(k8, n, h)
     assert name in ("hybrid", "lsd")  # bit windows re-centre the digits on the varying bits
+    # skewed keys (rdst_b200/csrc/heavy.cuh): a tenth of the records share one key -> on both MSD digits one bucket
+    # holds a tenth plus its uniform share, the expected segment is far past an SM, yet the route is kept for
+    # key-only records (the oversized segment is split around a pivot) ...
+    h = np.zeros((8, 256), dtype=np.uint64)
+    h[:, :] = (n - n // 10) // 256
+    h[:, 17] += n // 10
+    h[:, 0] += np.uint64(n) - h[0].sum()
+    assert int(h[0].sum()) == n
+    assert route(k8, n, h)[0] == "hybrid"
+    # ... but not for records with a payload (equal keys are then different records, nothing may be filled in) ...
+    assert route(rec16, n, h[:6])[0] == "lsd"
+    # ... and not for clustered keys: a bucket with half of the records on the second digit is not duplicates
+    h2 = uniform_hist(8, n, range(8))
+    h2[6, :] = (n // 2) // 256
+    h2[6, 5] += np.uint64(n) - h2[6].sum()
+    assert int(h2[6].sum()) == n and int(h2[6].max()) > n // 4
+    assert route(k8, n, h2)[0] == "lsd"
     all_one = uniform_hist(8, n, [])
     name, r = route(k8, n, all_one)
     assert name == "lsd" and r.levels_run == 0 and r.active_levels == 0  # every level trivial: nothing to run
