@@ -38,7 +38,9 @@ enum {
     B200_ERR_NO_DEVICE = 4,     /* no usable sm_100 device */
     B200_ERR_ALLOC = 5,         /* scratch / staging allocation failed */
     B200_ERR_BAD_ARG = 6,       /* null pointer, unknown variant id … */
-    B200_ERR_LEVEL_RANGE = 7    /* level >= LEVELS (src/radix_key.rs:18 debug_assert) */
+    B200_ERR_LEVEL_RANGE = 7,   /* level >= LEVELS (src/radix_key.rs:18 debug_assert) */
+    /* 8 is taken by the Python driver (B200_ERR_NCCL, rdst_b200/_abi.py) */
+    B200_ERR_TOO_LARGE = 9      /* b200_sort_device_static: more records than the static scratch holds */
 };
 
 /*
@@ -159,6 +161,30 @@ int b200_sort_host(void* host_ptr, size_t n, const b200_key_desc* desc,
  */
 int b200_sort_device(void* dev_ptr, void* dev_tmp, size_t n, const b200_key_desc* desc,
                      const b200_sort_opts* opts, b200_stats* stats);
+
+/*
+ * The device sort for callers that cannot allocate: ALLOCATES NOTHING — no cudaMalloc, cudaFree,
+ * cudaMallocHost or allocating library routine, not on the first call either.
+ * No counterpart in the reference; added (code under CUDA graph
+ * capture, tight serving loops, harnesses that forbid cudaMalloc).
+ * Its scratch (ping-pong buffer, histograms, tile look-back table, tickets) is a file-scope
+ * `static __device__` array of ~20.3 MiB that every GPU loading the library holds until exit, hence the limits:
+ *   n <= B200_STATIC_MAX_RECORDS and n * elem_size <= B200_STATIC_MAX_BYTES, else B200_ERR_TOO_LARGE
+ *   (b200_last_cuda_error() names the sizes).
+ * Sorts `n` records in DEVICE memory in place, result bit-identical to b200_sort_device's.  n <= 16 384
+ * records of 4 / 8 bytes: one launch of the shared-memory segment sort; otherwise K1 + one stable pass per
+ * declared level (no histogram read-back, so no level is skipped).
+ * opts may be NULL; opts->stream = the stream to enqueue on (NULL = the legacy default stream: this entry
+ * point creates no stream of its own), opts->device as elsewhere, opts->variant as elsewhere (>= 0 forces
+ * the passes), opts->route must be B200_HINT_AUTO.  The call only ENQUEUES and returns without
+ * synchronising: the result is there when the stream gets there.
+ * Every call on a GPU shares that GPU's array, which keeps the last call's contents; what must start at zero
+ * is cleared by each call on its stream.  Calls that overlap on the same GPU (different streams, different
+ * threads) RACE on the array: serialise them.
+ */
+#define B200_STATIC_MAX_RECORDS (2u << 20) /* 2 Mi records */
+#define B200_STATIC_MAX_BYTES (16u << 20)  /* 16 MiB of records */
+int b200_sort_device_static(void* dev_ptr, size_t n, const b200_key_desc* desc, const b200_sort_opts* opts);
 
 /*
  * K1 on its own: all LEVELS 256-bin histograms of device data in one read.

@@ -24,6 +24,7 @@ ERR_NAMES = {
     6: "B200_ERR_BAD_ARG",
     7: "B200_ERR_LEVEL_RANGE",
     8: "B200_ERR_NCCL",
+    9: "B200_ERR_TOO_LARGE",
 }
 
 
@@ -55,6 +56,7 @@ class SortOpts(C.Structure):
 
 
 HINT_AUTO, HINT_LSD, HINT_LOW_SCRATCH = 0, 1, 2  # b200_route_hint
+STATIC_MAX_RECORDS, STATIC_MAX_BYTES = 2 << 20, 16 << 20  # b200_sort_device_static (include/b200sort.h)
 B200_MAX_GPUS = 16
 
 
@@ -167,6 +169,7 @@ SYMBOLS = {
         C.c_int,
         [C.c_void_p, C.c_void_p, C.c_size_t, C.POINTER(KeyDesc), C.POINTER(SortOpts), C.POINTER(Stats)],
     ),
+    "b200_sort_device_static": (C.c_int, [C.c_void_p, C.c_size_t, C.POINTER(KeyDesc), C.POINTER(SortOpts)]),
     "b200_histogram_device": (
         C.c_int,
         [C.c_void_p, C.c_size_t, C.POINTER(KeyDesc), C.POINTER(SortOpts), C.POINTER(C.c_uint64)],
@@ -286,7 +289,7 @@ def check(code):
     if code == 0:
         return
     detail = ""
-    if code == 3:
+    if code in (3, 9):
         detail = (lib().b200_last_cuda_error() or b"").decode()
     if code == 1:
         raise LevelsZeroError(code, "RadixKey must have at least 1 level")

@@ -2438,6 +2438,7 @@ const char* b200_strerror(int code) {
         case B200_ERR_ALLOC: return "device scratch allocation failed";
         case B200_ERR_BAD_ARG: return "bad argument";
         case B200_ERR_LEVEL_RANGE: return "level >= LEVELS";
+        case B200_ERR_TOO_LARGE: return "more records than the static scratch holds";
     }
     return "unknown error";
 }
@@ -2445,3 +2446,179 @@ const char* b200_last_cuda_error(void) { return g_last_cuda_error.c_str(); }
 const char* b200_version(void) { return "b200sort 0.1.0 (sm_100a)"; }
 
 }  // extern "C"
+
+// ===========================================================================
+// b200_sort_device_static — the sort with its scratch in a file-scope device array: no cudaMalloc, no
+// cudaFree, no allocating library routine, not on the first call either.  No counterpart in the reference;
+// added for callers that cannot allocate (code under CUDA graph
+// capture, tight serving loops, harnesses that forbid cudaMalloc).  It shares nothing with the entry points
+// above except the kernels: no DeviceCtx pool, no library stream, no events, no pinned host buffers.
+//
+//   n <= 16 384 records of 4 / 8 bytes (the `small` route's shape): ONE launch of K3, the shared-memory segment
+//     sort; its segment table and ticket live in the static array and are written by a one-CTA set-up kernel
+//   otherwise: K1 (all level histograms) -> scan -> one stable K2 pass per level, ping-ponging between the
+//     caller's buffer and the static array, with a device copy back when LEVELS is odd.  No histogram comes
+//     back to the host, so nothing is skipped: every declared level is a pass.
+//
+// Everything is enqueued on the caller's stream (NULL = the legacy default stream) and the call returns
+// without synchronising.  Every call on a device shares that device's copy of the array, which keeps the last
+// call's contents: what has to start at zero (histograms, tile look-back table, tickets) is cleared on the
+// stream by every call, and two calls that overlap on the same GPU race.
+// ===========================================================================
+namespace {
+
+static_assert(B200_STATIC_MAX_RECORDS % 1024 == 0, "look-back table is sized in tiles of >= 1024 records");
+constexpr size_t ST_HIST_OFF = 0;                                                  // [64][256] u64
+constexpr size_t ST_BASE_OFF = ST_HIST_OFF + size_t(MAX_LEVELS) * RADIX * 8;       // [64][256] u64
+constexpr size_t ST_TICKET_OFF = ST_BASE_OFF + size_t(MAX_LEVELS) * RADIX * 8;     // one u32 per pass, 1024 bytes
+constexpr size_t ST_SEG_OFF = ST_TICKET_OFF + 1024;                                // K3: segment offsets [2] u64
+constexpr size_t ST_K3TICKET_OFF = ST_SEG_OFF + 256;                               // K3: ticket + telemetry, 4096 bytes
+constexpr size_t ST_LOOKBACK_OFF = ST_K3TICKET_OFF + 4096;                         // [tiles][256] u64, tiles of >= 1024 records
+constexpr size_t ST_LOOKBACK_BYTES = size_t(B200_STATIC_MAX_RECORDS / 1024) * RADIX * 8;
+constexpr size_t ST_TMP_OFF = ST_LOOKBACK_OFF + ST_LOOKBACK_BYTES;                 // the ping-pong buffer
+constexpr size_t ST_BYTES = ST_TMP_OFF + size_t(B200_STATIC_MAX_BYTES);
+static_assert(ST_TMP_OFF % 256 == 0 && ST_LOOKBACK_OFF % 256 == 0 && ST_SEG_OFF % 256 == 0, "sub-buffers stay 256-byte aligned");
+
+}  // namespace
+
+// ~20.3 MiB in every GPU that loads this module, until the process exits.  In HOST code this name is a
+// stand-in, not a device address: static_scratch_base() below asks the runtime for the address.
+static __device__ __align__(256) unsigned char g_static_scratch[ST_BYTES];
+
+namespace {
+
+// Device code may name the array directly: the set-up of the one-launch route.
+__global__ void static_small_setup_kernel(unsigned long long n) {
+    unsigned long long* seg = reinterpret_cast<unsigned long long*>(g_static_scratch + ST_SEG_OFF);
+    uint32_t* tk = reinterpret_cast<uint32_t*>(g_static_scratch + ST_K3TICKET_OFF);
+    for (uint32_t i = threadIdx.x; i < 1024u; i += blockDim.x) tk[i] = 0u;
+    if (threadIdx.x == 0) {
+        seg[0] = 0ull;
+        seg[1] = n;
+    }
+}
+
+struct StaticDev {
+    bool ready = false;
+    unsigned char* base = nullptr;  // this device's copy of g_static_scratch
+    int sm_count = 0;
+};
+std::mutex g_static_mu;
+StaticDev g_static_dev[MAX_DEVICES];
+
+// Once per device, with that device current (the caller holds a DeviceGuard).
+int static_scratch_base(int dev, StaticDev** out) {
+    std::lock_guard<std::mutex> lk(g_static_mu);
+    StaticDev& s = g_static_dev[dev];
+    if (!s.ready) {
+        int major = 0;
+        CUDA_TRY(cudaDeviceGetAttribute(&major, cudaDevAttrComputeCapabilityMajor, dev));
+        if (major < 10) {
+            g_last_cuda_error = "device is not sm_100 class";
+            return B200_ERR_NO_DEVICE;
+        }
+        CUDA_TRY(cudaDeviceGetAttribute(&s.sm_count, cudaDevAttrMultiProcessorCount, dev));
+        void* p = nullptr;
+        CUDA_TRY(cudaGetSymbolAddress(&p, g_static_scratch));
+        if (!p || reinterpret_cast<uintptr_t>(p) % 256 != 0) {
+            g_last_cuda_error = "cudaGetSymbolAddress(g_static_scratch) returned an unusable address";
+            return B200_ERR_CUDA;
+        }
+        s.base = static_cast<unsigned char*>(p);
+        s.ready = true;
+    }
+    *out = &s;
+    return B200_OK;
+}
+
+}  // namespace
+
+extern "C" int b200_sort_device_static(void* dev_ptr, size_t n, const b200_key_desc* desc, const b200_sort_opts* opts) {
+    Lowered lo;
+    int rc = lower_desc(desc, &lo);
+    if (rc) return rc;
+    if (opts && opts->route != B200_HINT_AUTO) return B200_ERR_BAD_ARG;  // one route per size, nothing to hint
+    if (opts && opts->variant >= NUM_VARIANTS) return B200_ERR_BAD_ARG;
+    if (n <= 1) return B200_OK;  // reference src/radix_sort_builder.rs:151
+    if (!dev_ptr) return B200_ERR_BAD_ARG;
+    if (n > size_t(B200_STATIC_MAX_RECORDS) || n * size_t(lo.elem_size) > size_t(B200_STATIC_MAX_BYTES)) {
+        char msg[256];
+        snprintf(msg, sizeof(msg),
+                 "b200_sort_device_static: %zu records of %u bytes exceed the static scratch (at most %u records and %u bytes); "
+                 "use b200_sort_device",
+                 n, lo.elem_size, unsigned(B200_STATIC_MAX_RECORDS), unsigned(B200_STATIC_MAX_BYTES));
+        g_last_cuda_error = msg;
+        return B200_ERR_TOO_LARGE;
+    }
+    int dev = opts ? opts->device : -1;
+    if (dev < 0) CUDA_TRY(cudaGetDevice(&dev));
+    int count = 0;
+    cudaError_t e = cudaGetDeviceCount(&count);
+    if (e != cudaSuccess || count == 0) {
+        g_last_cuda_error = std::string("cudaGetDeviceCount: ") + cudaGetErrorString(e);
+        cudaGetLastError();
+        return B200_ERR_NO_DEVICE;
+    }
+    if (dev >= count || dev >= MAX_DEVICES) return B200_ERR_BAD_ARG;
+    DeviceGuard guard(dev);
+    StaticDev* sd = nullptr;
+    rc = static_scratch_base(dev, &sd);
+    if (rc) return rc;
+    unsigned char* base = sd->base;
+    cudaStream_t st = opts ? static_cast<cudaStream_t>(opts->stream) : nullptr;
+
+    // ---- n fits one SM: ONE launch of K3 over the whole array ----
+    SplitParams key;
+    if ((!opts || opts->variant < 0) && small_sort_ok(lo, dev_ptr, n, &key)) {
+        static_small_setup_kernel<<<1, 256, 0, st>>>(n);
+        CUDA_TRY(cudaGetLastError());
+        uint32_t* d_tk = reinterpret_cast<uint32_t*>(base + ST_K3TICKET_OFF);
+        LocalSortParams lp;
+        memset(&lp, 0, sizeof(lp));
+        lp.data = static_cast<uint32_t*>(dev_ptr);
+        lp.seg_off = reinterpret_cast<const uint64_t*>(base + ST_SEG_OFF);
+        lp.nseg = 1;
+        lp.ticket = d_tk;
+        lp.nlev = lo.levels;
+        for (uint32_t l = 0; l < lo.levels; ++l) lp.lv[l] = window_params(lo, key, 8 * l, 8);
+        lp.nfast = 0;  // a plain stable LSD over every level, all in shared memory
+        lp.key = key;
+        lp.slow_segments = d_tk + 300;
+        return lo.elem_size == 4 ? launch_local_sort_w<1>(lo.is_float, 1, st, lp) : launch_local_sort_w<2>(lo.is_float, 1, st, lp);
+    }
+
+    // ---- K1 -> scan -> one stable pass per level ----
+    DeviceCtx c;  // a view for the launch helpers, on the stack: SM count and the look-back table; owns nothing
+    c.dev = dev;
+    c.sm_count = sd->sm_count;
+    c.d_lookback = reinterpret_cast<uint64_t*>(base + ST_LOOKBACK_OFF);
+    c.lookback_bytes = ST_LOOKBACK_BYTES;
+    unsigned long long* d_hist = reinterpret_cast<unsigned long long*>(base + ST_HIST_OFF);
+    unsigned long long* d_base = reinterpret_cast<unsigned long long*>(base + ST_BASE_OFF);
+    uint32_t* d_ticket = reinterpret_cast<uint32_t*>(base + ST_TICKET_OFF);
+    void* tmp = base + ST_TMP_OFF;
+    PassPlan pp{};
+    rc = plan_pass(c, lo, n, dev_ptr, tmp, false, opts ? opts->variant : -1, &pp);
+    if (rc) return rc;
+    const size_t lb_bytes = size_t(pp.num_tiles) * RADIX * 8;
+    if (lb_bytes > ST_LOOKBACK_BYTES) {
+        g_last_cuda_error = "b200_sort_device_static: tile look-back table does not fit the static scratch";
+        return B200_ERR_TOO_LARGE;
+    }
+    rc = launch_histogram(c, st, lo, dev_ptr, n, d_hist);  // clears the histograms first
+    if (rc) return rc;
+    scan_hist_kernel<<<lo.levels, RADIX, 0, st>>>(d_hist, d_base);
+    CUDA_TRY(cudaGetLastError());
+    CUDA_TRY(cudaMemsetAsync(c.d_lookback, 0, lb_bytes, st));
+    CUDA_TRY(cudaMemsetAsync(d_ticket, 0, 1024, st));
+    void* src = dev_ptr;
+    void* dst = tmp;
+    for (uint32_t l = 0; l < lo.levels; ++l) {
+        rc = launch_pass(c, st, pp, lo, src, dst, n, l, reinterpret_cast<const uint64_t*>(d_base + size_t(l) * RADIX),
+                         d_ticket + l, l + 1, nullptr);
+        if (rc) return rc;
+        std::swap(src, dst);
+    }
+    if (src != dev_ptr) CUDA_TRY(cudaMemcpyAsync(dev_ptr, src, n * lo.elem_size, cudaMemcpyDeviceToDevice, st));
+    return B200_OK;
+}

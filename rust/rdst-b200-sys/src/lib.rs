@@ -18,6 +18,9 @@ pub const B200_ERR_NO_DEVICE: c_int = 4;
 pub const B200_ERR_ALLOC: c_int = 5;
 pub const B200_ERR_BAD_ARG: c_int = 6;
 pub const B200_ERR_LEVEL_RANGE: c_int = 7;
+pub const B200_ERR_TOO_LARGE: c_int = 9;
+pub const B200_STATIC_MAX_RECORDS: usize = 2 << 20;
+pub const B200_STATIC_MAX_BYTES: usize = 16 << 20;
 
 // b200_key_kind
 pub const B200_KEY_UINT: u32 = 0;
@@ -148,6 +151,10 @@ extern "C" {
                           stats: *mut b200_stats) -> c_int;
     pub fn b200_sort_device(dev_ptr: *mut c_void, dev_tmp: *mut c_void, n: usize, desc: *const b200_key_desc,
                             opts: *const b200_sort_opts, stats: *mut b200_stats) -> c_int;
+    /// Allocates nothing (scratch is a static device array); no counterpart in the reference.
+    /// Limits: B200_STATIC_MAX_RECORDS / B200_STATIC_MAX_BYTES, else B200_ERR_TOO_LARGE.  Enqueues only.
+    pub fn b200_sort_device_static(dev_ptr: *mut c_void, n: usize, desc: *const b200_key_desc,
+                                   opts: *const b200_sort_opts) -> c_int;
     // ---- building blocks ----
     pub fn b200_histogram_device(dev_ptr: *const c_void, n: usize, desc: *const b200_key_desc, opts: *const b200_sort_opts,
                                  hist_out: *mut u64) -> c_int;
