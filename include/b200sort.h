@@ -163,6 +163,23 @@ int b200_sort_device(void* dev_ptr, void* dev_tmp, size_t n, const b200_key_desc
                      const b200_sort_opts* opts, b200_stats* stats);
 
 /*
+ * Many independent sorts in one call: every segment [seg_off[i], seg_off[i + 1]) of the device array `dev_ptr`
+ * (n records) is sorted on its own, in place.  `seg_off` is HOST memory, nseg + 1 ascending record offsets, the last
+ * one <= n; n < 2^32.  Segments of <= 1 record are left alone (src/radix_sort_builder.rs:151).
+ * Replaces: the tail of the MSB-first recursion — Sorter::director handing every bucket of a split to
+ *           handle_chunk as its own task (src/sorter.rs:121-157), where small buckets end in lsb_sort_adapter
+ *           (src/sorts/lsb_sort.rs:38-128) or, below 128 records, comparative_sort
+ *           (src/sorts/comparative_sort.rs:29-119).
+ * Segments of up to 16 384 records of 4 / 8 bytes (LEVELS <= 8, contiguous key) are sorted in shared memory by the
+ * CTAs of one launch (stable; records that are nothing but their key take the unstable kernel, same result);
+ * larger segments and other record shapes take the whole-array sort one after the other.
+ * stats: tiles_per_pass = segments sorted on chip, heavy_segments = segments that took the whole-array sort,
+ * slow_segments = on-chip segments finished by the stable kernel, ms_local = the on-chip launch(es).
+ */
+int b200_sort_segments_device(void* dev_ptr, size_t n, const uint64_t* seg_off, size_t nseg,
+                              const b200_key_desc* desc, const b200_sort_opts* opts, b200_stats* stats);
+
+/*
  * The device sort for callers that cannot allocate: ALLOCATES NOTHING — no cudaMalloc, cudaFree,
  * cudaMallocHost or allocating library routine, not on the first call either.
  * No counterpart in the reference; added (code under CUDA graph

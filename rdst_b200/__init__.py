@@ -8,9 +8,9 @@ every sort call goes to the CUDA library and raises if it is missing or fails.
 from . import tuner
 from ._abi import B200SortError, LevelsZeroError
 from .radix_key import RadixKey
-from .radix_sort import RadixSortBuilder, radix_sort_builder, radix_sort_stable, radix_sort_unstable, sort_multi_host
+from .radix_sort import RadixSortBuilder, radix_sort_builder, radix_sort_stable, radix_sort_unstable, sort_multi_host, sort_segments
 
 __all__ = [
-    "RadixKey", "RadixSortBuilder", "radix_sort_builder", "radix_sort_unstable", "radix_sort_stable", "sort_multi_host",
+    "RadixKey", "RadixSortBuilder", "radix_sort_builder", "radix_sort_unstable", "radix_sort_stable", "sort_multi_host", "sort_segments",
     "tuner", "B200SortError", "LevelsZeroError",
 ]

@@ -169,6 +169,10 @@ SYMBOLS = {
         C.c_int,
         [C.c_void_p, C.c_void_p, C.c_size_t, C.POINTER(KeyDesc), C.POINTER(SortOpts), C.POINTER(Stats)],
     ),
+    "b200_sort_segments_device": (
+        C.c_int,
+        [C.c_void_p, C.c_size_t, C.POINTER(C.c_uint64), C.c_size_t, C.POINTER(KeyDesc), C.POINTER(SortOpts), C.POINTER(Stats)],
+    ),
     "b200_sort_device_static": (C.c_int, [C.c_void_p, C.c_size_t, C.POINTER(KeyDesc), C.POINTER(SortOpts)]),
     "b200_histogram_device": (
         C.c_int,

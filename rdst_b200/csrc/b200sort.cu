@@ -35,6 +35,7 @@
 #include "unstable.h"
 #include "local_count.cuh"
 #include "heavy.cuh"
+#include "tiny_sort.cuh"
 
 using namespace b200;
 
@@ -160,6 +161,8 @@ struct DeviceCtx {
     size_t slow_bytes = 0;
     uint8_t* d_heavy = nullptr;  // oversized segments (heavy.cuh): range tables, pivots, tile counts and bases, lists
     size_t heavy_bytes = 0;
+    uint8_t* d_batch = nullptr;  // b200_sort_segments_device: {first record, records} of the segments | slow list
+    size_t batch_bytes = 0;
 };
 
 constexpr size_t SMALL_HIST_OFF = 0;
@@ -2331,9 +2334,10 @@ int b200_release_scratch(int device) {
     std::lock_guard<std::mutex> lk(c->mu);
     DeviceGuard guard(c->dev);
     void** ptrs[] = {&c->d_tmp, reinterpret_cast<void**>(&c->d_lookback), &c->d_stage,
-                     reinterpret_cast<void**>(&c->d_sample), reinterpret_cast<void**>(&c->d_slow)};
-    size_t* sizes[] = {&c->tmp_bytes, &c->lookback_bytes, &c->stage_bytes, &c->sample_bytes, &c->slow_bytes};
-    for (int i = 0; i < 5; ++i) {
+                     reinterpret_cast<void**>(&c->d_sample), reinterpret_cast<void**>(&c->d_slow),
+                     reinterpret_cast<void**>(&c->d_batch)};
+    size_t* sizes[] = {&c->tmp_bytes, &c->lookback_bytes, &c->stage_bytes, &c->sample_bytes, &c->slow_bytes, &c->batch_bytes};
+    for (int i = 0; i < 6; ++i) {
         if (*ptrs[i]) cudaFree(*ptrs[i]);
         *ptrs[i] = nullptr;
         *sizes[i] = 0;
@@ -2446,6 +2450,195 @@ const char* b200_last_cuda_error(void) { return g_last_cuda_error.c_str(); }
 const char* b200_version(void) { return "b200sort 0.1.0 (sm_100a)"; }
 
 }  // extern "C"
+
+// ===========================================================================
+// b200_sort_segments_device — many independent sorts in one call: every segment [seg_off[i], seg_off[i + 1]) of one
+// device array is sorted on its own.  rdst's MSB-first recursion ends in exactly this: thousands of small buckets,
+// each finished by an in-cache LSB sort or, below 128 records, a comparison sort (reference src/sorter.rs:121-157,
+// src/sorts/lsb_sort.rs:38-128, src/sorts/comparative_sort.rs:29-119), one rayon task per bucket.  Here the segments
+// that fit one SM (<= 16 384 records of 4 / 8 bytes) are claimed by the CTAs of ONE launch of the segment sort —
+// K3-U for records that are nothing but their key (one wide counting-sort level + comparison fix-up; every segment
+// cuts its digit from the highest bit in which ITS keys differ, the AUTOTOP instantiations, because the buckets of an
+// MSD split share their leading bytes), the stable K3 over every declared level otherwise — and segments that do not
+// fit take the whole-array sort, one after the other.
+// ===========================================================================
+extern "C" int b200_sort_segments_device(void* dev_ptr, size_t n, const uint64_t* seg_off, size_t nseg, const b200_key_desc* desc,
+                                         const b200_sort_opts* opts, b200_stats* stats) {
+    Lowered lo;
+    int rc = lower_desc(desc, &lo);
+    if (rc) return rc;
+    if (stats) memset(stats, 0, sizeof(*stats));
+    if (opts && opts->route > B200_HINT_LOW_SCRATCH) return B200_ERR_BAD_ARG;
+    if (nseg == 0 || n == 0) return B200_OK;
+    if (!seg_off || nseg > 0xfffffffeull || n > 0xffffffffull) return B200_ERR_BAD_ARG;
+    // the segments, checked: offsets ascend and stay inside the array
+    const char* tenv = getenv("B200SORT_TINY");  // read per call: tests flip it
+    // a warp per segment (K3-T) up to 128 records for key-only records, 256 for records with a payload (whose
+    // CTA-wide stable sort runs every declared level): measured, profiles/r9_segments_bench.jsonl
+    const uint32_t tiny_cap = (tenv && atoi(tenv) == 0) ? 0u : (key_only_record(lo) ? 128u : uint32_t(TS_CAP));
+    std::vector<uint2> tiny;   // 2 .. tiny_cap records: one warp each
+    std::vector<uint2> pairs;  // .. 16 384 records: one CTA each
+    std::vector<uint2> big;    // more: the whole-array sort, one by one
+    uint32_t max_small = 0;
+    for (size_t i = 0; i < nseg; ++i) {
+        if (seg_off[i + 1] < seg_off[i] || seg_off[i + 1] > n) return B200_ERR_BAD_ARG;
+        const uint64_t cnt = seg_off[i + 1] - seg_off[i];
+        if (cnt <= 1) continue;  // reference src/radix_sort_builder.rs:151
+        if (cnt <= tiny_cap) {
+            tiny.push_back(make_uint2(uint32_t(seg_off[i]), uint32_t(cnt)));
+        } else if (cnt <= uint64_t(LS_CAP)) {
+            pairs.push_back(make_uint2(uint32_t(seg_off[i]), uint32_t(cnt)));
+            max_small = std::max(max_small, uint32_t(cnt));
+        } else {
+            big.push_back(make_uint2(uint32_t(seg_off[i]), uint32_t(cnt)));
+        }
+    }
+    if (tiny.empty() && pairs.empty() && big.empty()) return B200_OK;
+    if (!dev_ptr) return B200_ERR_BAD_ARG;
+    DeviceCtx* cp_ = nullptr;
+    rc = get_ctx(opts ? opts->device : -1, &cp_);
+    if (rc) return rc;
+    DeviceCtx& c = *cp_;
+    std::lock_guard<std::mutex> lk(c.mu);
+    DeviceGuard guard(c.dev);
+    cudaStream_t st = (opts && opts->stream) ? static_cast<cudaStream_t>(opts->stream) : c.stream;
+    SplitParams key;
+    const bool on_chip = (lo.elem_size == 4 || lo.elem_size == 8) && lo.levels <= uint32_t(LS_MAXLEV) && hybrid_mode() != 0 &&
+                         (!opts || opts->variant < 0) && lower_prefix(lo, &key) == B200_OK && word_path_ok(lo, dev_ptr, dev_ptr);
+    if (!on_chip) {  // shapes the segment sort does not take (2-byte keys, 12-byte records ...): every segment on its own
+        big.insert(big.end(), pairs.begin(), pairs.end());
+        big.insert(big.end(), tiny.begin(), tiny.end());
+        pairs.clear();
+        tiny.clear();
+    }
+    CUDA_TRY(cudaEventRecord(c.ev[10], st));
+    uint32_t launches = 0, slow = 0, unstable = 0;
+    const uint32_t words = lo.elem_size / 4;
+    const size_t np = pairs.size(), nt = tiny.size();
+    const size_t o_pairs = 0, o_tiny = np * 8, o_slow = o_tiny + nt * 8, o_tk = o_slow + (np + 1) * 4, total = (o_tk + 4096 + 15) / 16 * 16;
+    if (np + nt) {
+        rc = ensure_bytes(reinterpret_cast<void**>(&c.d_batch), &c.batch_bytes, total);
+        if (rc) return rc;
+    }
+    if (nt) {  // K3-T: a warp per segment
+        CUDA_TRY(cudaMemcpyAsync(c.d_batch + o_tiny, tiny.data(), nt * 8, cudaMemcpyHostToDevice, st));
+        TinySortParams tp;
+        memset(&tp, 0, sizeof(tp));
+        tp.data = static_cast<uint32_t*>(dev_ptr);
+        tp.seg_pairs = reinterpret_cast<const uint2*>(c.d_batch + o_tiny);
+        tp.nseg = uint32_t(nt);
+        tp.key = key;
+        const int tgrid = int(std::min<uint64_t>((nt + TS_WARPS - 1) / TS_WARPS, uint64_t(c.sm_count) * 8));
+        if (words == 1) {
+            if (lo.is_float) tiny_sort_kernel<1, true><<<tgrid, TS_THREADS, 0, st>>>(tp);
+            else tiny_sort_kernel<1, false><<<tgrid, TS_THREADS, 0, st>>>(tp);
+        } else {
+            if (lo.is_float) tiny_sort_kernel<2, true><<<tgrid, TS_THREADS, 0, st>>>(tp);
+            else tiny_sort_kernel<2, false><<<tgrid, TS_THREADS, 0, st>>>(tp);
+        }
+        CUDA_TRY(cudaGetLastError());
+        ++launches;
+    }
+    if (np) {
+        uint8_t* d = c.d_batch;
+        const size_t tk_at = (o_tk + 15) / 16 * 16;
+        uint32_t* d_slow = reinterpret_cast<uint32_t*>(d + o_slow);
+        uint32_t* d_tk = reinterpret_cast<uint32_t*>(d + tk_at);
+        CUDA_TRY(cudaMemcpyAsync(d + o_pairs, pairs.data(), np * 8, cudaMemcpyHostToDevice, st));
+        CUDA_TRY(cudaMemsetAsync(d_slow, 0, 4, st));
+        CUDA_TRY(cudaMemsetAsync(d_tk, 0, 2048, st));
+        LocalSortParams lp;
+        memset(&lp, 0, sizeof(lp));
+        lp.data = static_cast<uint32_t*>(dev_ptr);
+        lp.seg_pairs = reinterpret_cast<const uint2*>(d + o_pairs);
+        lp.nseg = uint32_t(np);
+        lp.ticket = d_tk;
+        lp.nlev = lo.levels;
+        for (uint32_t l = 0; l < lo.levels; ++l) lp.lv[l] = window_params(lo, key, 8 * l, 8);
+        lp.nfast = 0;  // a plain stable LSD over every declared level, all in shared memory
+        lp.key = key;
+        lp.slow_segments = d_tk + 300;
+        if (key_only_record(lo)) {
+            const int size = max_small <= 4096 ? 0 : (max_small <= 8192 ? 1 : 2);
+            const LocalCountLaunch ll = words == 1 ? get_local_count_launch_w1(lo.is_float, size, true, true)
+                                                   : get_local_count_launch_w2(lo.is_float, size, false, true);
+            LocalCountParams cp;
+            memset(&cp, 0, sizeof(cp));
+            cp.data = static_cast<uint32_t*>(dev_ptr);
+            cp.seg_pairs = lp.seg_pairs;
+            cp.nseg = uint32_t(np);
+            cp.ticket = d_tk + 16;
+            cp.key = key;
+            cp.top_bit = 8 * lo.levels;
+            cp.bmax = uint32_t(ll.cbits);
+            cp.slow_list = d_slow;
+            CUDA_TRY(cudaFuncSetAttribute(ll.kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, int(ll.smem)));
+            int occ = 1;
+            CUDA_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, ll.kernel, ll.threads, ll.smem));
+            const int ugrid = int(std::min<uint64_t>(uint64_t(c.sm_count) * std::max(occ, 1), np));
+            ll.kernel<<<ugrid, ll.threads, ll.smem, st>>>(cp);
+            CUDA_TRY(cudaGetLastError());
+            lp.list = d_slow;  // what K3-U left behind (a long run of unequal keys in one counter): the stable K3, from the list
+            unstable = 1;
+            ++launches;
+        }
+        const int lgrid = int(std::min<uint64_t>(uint64_t(c.sm_count), np));
+        rc = words == 1 ? launch_local_sort_w<1>(lo.is_float, lgrid, st, lp) : launch_local_sort_w<2>(lo.is_float, lgrid, st, lp);
+        if (rc) return rc;
+        ++launches;
+        if (unstable) CUDA_TRY(cudaMemcpyAsync(&slow, d_slow, 4, cudaMemcpyDeviceToHost, st));
+    }
+    CUDA_TRY(cudaEventRecord(c.ev[11], st));
+    // ---- segments that do not fit an SM: the whole-array sort on each (through an aligned staging copy when the
+    // segment does not start on a 16-byte boundary, which the vector loads of the pass kernels need) ----
+    if (!big.empty()) {
+        uint32_t mx = 0;
+        for (const uint2& b : big) mx = std::max(mx, b.y);
+        rc = ensure_bytes(&c.d_tmp, &c.tmp_bytes, size_t(mx) * lo.elem_size);
+        if (rc) return rc;
+        for (const uint2& b : big) {
+            uint8_t* at = static_cast<uint8_t*>(dev_ptr) + size_t(b.x) * lo.elem_size;
+            const size_t bytes = size_t(b.y) * lo.elem_size;
+            const bool staged = reinterpret_cast<uintptr_t>(at) % 16 != 0;
+            void* where = at;
+            if (staged) {
+                rc = ensure_bytes(&c.d_stage, &c.stage_bytes, bytes);
+                if (rc) return rc;
+                CUDA_TRY(cudaMemcpyAsync(c.d_stage, at, bytes, cudaMemcpyDeviceToDevice, st));
+                where = c.d_stage;
+            }
+            SortCtl ctl;
+            ctl.variant = opts ? opts->variant : -1;
+            ctl.route = opts ? opts->route : uint32_t(B200_HINT_AUTO);
+            b200_stats sub;
+            memset(&sub, 0, sizeof(sub));
+            rc = sort_device_impl(c, st, where, c.d_tmp, b.y, lo, ctl, nullptr, &sub);
+            if (rc) return rc;
+            if (staged) CUDA_TRY(cudaMemcpyAsync(at, c.d_stage, bytes, cudaMemcpyDeviceToDevice, st));
+            launches += sub.kernel_launches;
+        }
+    }
+    CUDA_TRY(cudaEventRecord(c.ev[2], st));
+    CUDA_TRY(cudaStreamSynchronize(st));
+    if (stats) {
+        stats->levels_run = lo.levels;
+        stats->local_levels = (pairs.empty() && tiny.empty()) ? 0 : lo.levels;
+        stats->kernel_launches = launches;
+        stats->slow_segments = slow;
+        stats->unstable = unstable;
+        stats->tiles_per_pass = pairs.size() + tiny.size();   // segments sorted on chip
+        stats->heavy_segments = uint32_t(big.size());  // segments that took the whole-array sort
+        uint64_t recs = 0;
+        for (const uint2& p : pairs) recs += p.y;
+        for (const uint2& p : tiny) recs += p.y;
+        for (const uint2& b : big) recs += b.y;
+        stats->algorithmic_bytes = 2ull * recs * lo.elem_size;
+        CUDA_TRY(cudaEventElapsedTime(&stats->ms_local, c.ev[10], c.ev[11]));
+        CUDA_TRY(cudaEventElapsedTime(&stats->ms_total, c.ev[10], c.ev[2]));
+        stats->ms_passes = stats->ms_total;
+    }
+    return B200_OK;
+}
 
 // ===========================================================================
 // b200_sort_device_static — the sort with its scratch in a file-scope device array: no cudaMalloc, no

@@ -45,6 +45,9 @@ struct LocalCountParams {
     uint32_t* slow_list;      // [0] = count, [1 ..] = ids of the segments left to the stable segment sort
     unsigned long long* prof; // optional [8] cycle counters per phase (thread 0 of every CTA), nullptr = off
 };
+// AUTOTOP instantiations (b200_sort_segments_device: segments of unknown origin): every segment finds its own top bit,
+// the highest image bit in which ITS keys differ — the buckets of an MSD split share their leading bytes, and a digit
+// cut from constant bits would put a whole segment into one counter.
 
 template <int WORDS, int THREADS, int ITEMS, int CBITS>
 struct LocalCountSmem {
@@ -52,7 +55,7 @@ struct LocalCountSmem {
     static constexpr size_t OUT_BYTES = (size_t(CAP + 2) * WORDS * 4 + 127) / 128 * 128;  // + the shift that aligns record pairs
     static constexpr size_t CNT_BYTES = (size_t(1) << CBITS) * 2;
     static constexpr size_t RUN_BYTES = size_t(CAP / 2) * 4;  // a segment of c records has at most c / 2 runs of >= 2
-    static constexpr size_t MISC_BYTES = 256;
+    static constexpr size_t MISC_BYTES = 512;  // flags | warp totals (<= 32 warps) | auto_top: per-warp vary masks
     static constexpr size_t TOTAL = OUT_BYTES + CNT_BYTES + RUN_BYTES + MISC_BYTES;
 };
 
@@ -82,7 +85,7 @@ __device__ __forceinline__ typename KeyImage<WORDS>::T key_image(const Rec<WORDS
     }
 }
 
-template <int WORDS, bool FLOATK, int THREADS, int ITEMS, int CBITS, int MINB>
+template <int WORDS, bool FLOATK, int THREADS, int ITEMS, int CBITS, int MINB, bool AUTOTOP = false>
 __global__ void __launch_bounds__(THREADS, MINB) local_count_kernel(const LocalCountParams p) {
     using SM = LocalCountSmem<WORDS, THREADS, ITEMS, CBITS>;
     using KT = typename KeyImage<WORDS>::T;
@@ -98,6 +101,8 @@ __global__ void __launch_bounds__(THREADS, MINB) local_count_kernel(const LocalC
     volatile uint32_t* s_seg = reinterpret_cast<volatile uint32_t*>(misc);
     uint32_t par = 0;
     uint32_t* s_wtot = reinterpret_cast<uint32_t*>(misc + 64);  // WARPS warp totals
+    unsigned long long* s_vary = reinterpret_cast<unsigned long long*>(misc + 256);  // auto_top: per-warp OR of (key ^ first key)
+    static_assert(WARPS <= 32, "s_wtot / s_vary hold 32 warps");
 
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const uint32_t cnt_base = smem_u32(s_cnt);
@@ -176,6 +181,18 @@ __global__ void __launch_bounds__(THREADS, MINB) local_count_kernel(const LocalC
     while (seg < p.nseg) {
         par ^= 1u;
         volatile uint32_t* flag = s_seg + 4 * par;  // [2] long run seen, [3] slow
+        if (AUTOTOP && cnt > 1) {
+            // bits in which this segment's keys differ: OR of (key ^ the segment's first key), per warp; combined after
+            // barrier (0) (the slots are rewritten one trip later, behind barriers (1)..(5))
+            const KT kref = key_image<WORDS, FLOATK>(load_rec<WORDS>(g, 0), xorv);
+            KT v = 0;
+#pragma unroll
+            for (int j = 0; j < ITEMS; ++j)
+                if (vmask >> j & 1u) v |= key_image<WORDS, FLOATK>(r[j], xorv) ^ kref;
+            uint32_t lo = __reduce_or_sync(0xffffffffu, uint32_t(v)), hi = 0;
+            if constexpr (WORDS == 2) hi = __reduce_or_sync(0xffffffffu, uint32_t(uint64_t(v) >> 32));
+            if (lane == 0) s_vary[warp] = (unsigned long long)lo | ((unsigned long long)hi << 32);
+        }
         if (tid == 0) {
             s_seg[1] = p.seg_first + atomicAdd(p.ticket, 1u);
             flag[2] = 0;
@@ -198,8 +215,16 @@ __global__ void __launch_bounds__(THREADS, MINB) local_count_kernel(const LocalC
         // digit width of this segment: 2..4 counters per record, within [1, min(bmax, top_bit)]
         uint32_t b = 33u - uint32_t(__clz(int(cur_cnt - 1)));  // ceil(log2 cnt) + 1 for cnt >= 2
         b = b < p.bmax ? b : p.bmax;
-        b = b < p.top_bit ? b : p.top_bit;
-        const uint32_t shift = p.top_bit - b;
+        uint32_t top_bit = p.top_bit;
+        if constexpr (AUTOTOP) {
+            unsigned long long vary = 0;
+#pragma unroll
+            for (int w = 0; w < WARPS; ++w) vary |= s_vary[w];
+            const uint32_t bits = 64u - uint32_t(__clzll((long long)vary));  // 0 when every key is the same
+            top_bit = min(top_bit, max(bits, 1u));
+        }
+        b = b < top_bit ? b : top_bit;
+        const uint32_t shift = top_bit - b;
         const bool exact = shift == 0;  // the digit is everything that is left of the key: no fix-up
         const uint32_t dmask = (1u << b) - 1u;
         const uint32_t NW = b ? (1u << (b - 1)) : 1u;  // packed counter words

@@ -29,6 +29,7 @@ struct LocalCountLaunch {
     int cap;    // records per segment
     int cbits;  // widest digit
 };
-LocalCountLaunch get_local_count_launch_w1(bool floatk, int size, bool wide);
-LocalCountLaunch get_local_count_launch_w2(bool floatk, int size, bool wide);
+// autotop = the instantiation in which every segment finds its own top bit (local_count.cuh); `wide` is ignored then
+LocalCountLaunch get_local_count_launch_w1(bool floatk, int size, bool wide, bool autotop = false);
+LocalCountLaunch get_local_count_launch_w2(bool floatk, int size, bool wide, bool autotop = false);
 }  // namespace b200

@@ -46,11 +46,11 @@ static MsdULaunch pick_msdu(int variant) {
     return MsdULaunch{};
 }
 
-template <int WORDS, bool FLOATK, int THREADS, int ITEMS, int CBITS, int MINB>
+template <int WORDS, bool FLOATK, int THREADS, int ITEMS, int CBITS, int MINB, bool AUTOTOP = false>
 static LocalCountLaunch make_local_count() {
     using SM = LocalCountSmem<WORDS, THREADS, ITEMS, CBITS>;
     LocalCountLaunch l{};
-    l.kernel = &local_count_kernel<WORDS, FLOATK, THREADS, ITEMS, CBITS, MINB>;
+    l.kernel = &local_count_kernel<WORDS, FLOATK, THREADS, ITEMS, CBITS, MINB, AUTOTOP>;
     l.smem = SM::TOTAL;
     l.threads = THREADS;
     l.cap = SM::CAP;
@@ -59,8 +59,24 @@ static LocalCountLaunch make_local_count() {
 }
 
 // size 0 / 1 / 2 = segments of <= 4096 / 8192 / 16384 records; wide = twice the threads with half the records each
+// autotop (per-segment top bit) exists in the shape each width runs by default: wide for 1-word, narrow for 2-word records
 template <int WORDS, bool FLOATK>
-static LocalCountLaunch pick_local_count(int size, bool wide) {
+static LocalCountLaunch pick_local_count(int size, bool wide, bool autotop) {
+    if (autotop) {
+        if constexpr (WORDS == 1) {
+            switch (size) {
+                case 0: return make_local_count<WORDS, FLOATK, 256, 16, 13, 4, true>();
+                case 1: return make_local_count<WORDS, FLOATK, 512, 16, 14, 2, true>();
+                default: return make_local_count<WORDS, FLOATK, 1024, 16, 15, 1, true>();
+            }
+        } else {
+            switch (size) {
+                case 0: return make_local_count<WORDS, FLOATK, 128, 32, 13, 4, true>();
+                case 1: return make_local_count<WORDS, FLOATK, 256, 32, 14, 2, true>();
+                default: return make_local_count<WORDS, FLOATK, 512, 32, 15, 1, true>();
+            }
+        }
+    }
     if (wide) {
         switch (size) {
             case 0: return make_local_count<WORDS, FLOATK, 256, 16, 13, 4>();

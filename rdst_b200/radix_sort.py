@@ -192,6 +192,34 @@ def sort_multi_host(data, key: RadixKey | None = None, gpus=None):
     return st.as_dict()
 
 
+def sort_segments(data, seg_off, key: RadixKey | None = None):
+    """Many independent sorts in one call (b200_sort_segments_device): every segment [seg_off[i], seg_off[i + 1]) of a
+    torch CUDA tensor is sorted on its own, in place — what rdst's recursion does with the buckets of an MSB split
+    (reference src/sorter.rs:121-157).  `seg_off`: ascending record offsets (host), len = segments + 1.
+    Returns the b200_stats dict."""
+    key = key_for_array(data, key)
+    if key.levels == 0:
+        raise _abi.LevelsZeroError(1, "RadixKey must have at least 1 level")
+    ptr, n, on_device, dev, _keep = _buffer_info(data, key)
+    if not on_device:
+        raise ValueError("sort_segments takes a device tensor")
+    off = np.ascontiguousarray(seg_off, dtype=np.uint64)
+    if off.ndim != 1 or len(off) < 1:
+        raise ValueError("seg_off: a 1-d array of segments + 1 offsets")
+    import torch
+
+    lib = _abi.lib()
+    desc = key.to_desc()
+    opts = _abi.SortOpts()
+    opts.variant, opts.device, opts.route = -1, dev, 0
+    stats = _abi.Stats()
+    with torch.cuda.device(dev):
+        opts.stream = _stream_handle(torch)
+        _abi.check(lib.b200_sort_segments_device(ptr, n, off.ctypes.data_as(C.POINTER(C.c_uint64)), len(off) - 1,
+                                                 C.byref(desc), C.byref(opts), C.byref(stats)))
+    return stats.as_dict()
+
+
 def radix_sort_builder(data, key: RadixKey | None = None) -> RadixSortBuilder:
     """RadixSort::radix_sort_builder (reference src/radix_sort.rs:17-18)."""
     return RadixSortBuilder(data, key)

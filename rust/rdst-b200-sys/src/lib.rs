@@ -151,6 +151,9 @@ extern "C" {
                           stats: *mut b200_stats) -> c_int;
     pub fn b200_sort_device(dev_ptr: *mut c_void, dev_tmp: *mut c_void, n: usize, desc: *const b200_key_desc,
                             opts: *const b200_sort_opts, stats: *mut b200_stats) -> c_int;
+    /// Every segment [seg_off[i], seg_off[i + 1]) sorted on its own (seg_off: host memory, nseg + 1 offsets).
+    pub fn b200_sort_segments_device(dev_ptr: *mut c_void, n: usize, seg_off: *const u64, nseg: usize,
+                                     desc: *const b200_key_desc, opts: *const b200_sort_opts, stats: *mut b200_stats) -> c_int;
     /// Allocates nothing (scratch is a static device array); no counterpart in the reference.
     /// Limits: B200_STATIC_MAX_RECORDS / B200_STATIC_MAX_BYTES, else B200_ERR_TOO_LARGE.  Enqueues only.
     pub fn b200_sort_device_static(dev_ptr: *mut c_void, n: usize, desc: *const b200_key_desc,
