@@ -621,7 +621,7 @@ def run_one(args, workload, torch, dist, world, rank, local_rank, cpu_group):
         line["e2e_pageable"] = e2e_pageable
     if world > 1:
         line["exchange"] = {"mode": args.exchange}
-        line["exchange"].update({k: last.get(k) for k in ("level", "n_recv", "sent_bytes", "phase_ms", "splitter_mode", "splitter_plan_ms", "exchange_path")})
+        line["exchange"].update({k: last.get(k) for k in ("level", "n_recv", "sent_bytes", "phase_ms", "splitter_mode", "splitter_plan_ms", "exchange_path", "presplit")})
         line["exchange"]["max_n_recv_over_ranks"] = max_n_recv
         line["exchange"]["imbalance"] = max_n_recv / float(n)
         pm = last.get("phase_ms") or {}
@@ -672,7 +672,7 @@ def main():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--workload", default="u64_1b_uniform", choices=sorted(WORKLOADS))
-    ap.add_argument("--n", type=int, default=0, help="override records per GPU (debug)")
+    ap.add_argument("--n", "--records", dest="n", type=int, default=0, help="override records per GPU (debug; use --records under torchrun, whose own parser claims --n)")
     ap.add_argument("--cpu-sample", type=int, default=CPU_SAMPLE)
     ap.add_argument("--cpu-steps", type=int, default=3)
     ap.add_argument("--e2e-steps", type=int, default=3)

@@ -163,6 +163,18 @@ int b200_sort_device(void* dev_ptr, void* dev_tmp, size_t n, const b200_key_desc
                      const b200_sort_opts* opts, b200_stats* stats);
 
 /*
+ * The local sort of the sharded sort when the exchange has already split the records on one level: `dev_ptr` holds n
+ * records partitioned on `level` — bucket sizes `counts[256]` (host), buckets in digit order, every level above
+ * `level` constant — as b200_partition_peers_device with 256 parts delivers them.  K0, K1 and the first MSD pass are
+ * skipped (joint histogram, MSD pass 2 dev_ptr -> dev_tmp, segment sort in dev_tmp); the sorted records are at
+ * *result_out, which is dev_ptr or dev_tmp (both n * elem_size bytes, both clobbered).  Records with a payload,
+ * level < 2, or segments that do not fit one SM take the general sort from wherever the records are: same result.
+ * No counterpart in the reference (it has no distributed path); SURVEY §8(e).
+ */
+int b200_sort_device_presplit(void* dev_ptr, void* dev_tmp, size_t n, const b200_key_desc* desc, uint32_t level,
+                              const uint64_t* counts, const b200_sort_opts* opts, b200_stats* stats, void** result_out);
+
+/*
  * Many independent sorts in one call: every segment [seg_off[i], seg_off[i + 1]) of the device array `dev_ptr`
  * (n records) is sorted on its own, in place.  `seg_off` is HOST memory, nseg + 1 ascending record offsets, the last
  * one <= n; n < 2^32.  Segments of <= 1 record are left alone (src/radix_sort_builder.rs:151).

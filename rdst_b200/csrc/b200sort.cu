@@ -844,6 +844,11 @@ struct SortCtl {
     cudaEvent_t drain_event = nullptr;
     bool drained = false;         // out: the result is already on its way to drain_host (all of it)
     uint32_t heavy_segments = 0, heavy_rounds = 0;  // out: oversized segments split around pivots (heavy.cuh)
+    // the array arrives already partitioned on one level (the sharded sort's exchange did MSD pass 1 on the way,
+    // b200_sort_device_presplit): sort_hybrid skips its first pass, runs the second one data -> tmp and leaves the
+    // result in `tmp`
+    const uint64_t* presplit_counts = nullptr;  // [256] bucket sizes on presplit_level, in order
+    uint32_t presplit_level = 0;
 };
 
 // Returns B200_OK with *done = true when the array was sorted here (result in `data`);
@@ -855,8 +860,9 @@ int sort_hybrid(DeviceCtx& c, cudaStream_t st, void* data, void* tmp, uint64_t n
                 uint32_t* unstable_out, SortCtl* ctl) {
     *done = false;
     *src_out = data;
-    const int mode = hybrid_mode();
-    if (mode == 0 || active.size() < 3) return B200_OK;
+    const bool pre = ctl && ctl->presplit_counts;
+    const int mode = pre ? 1 : hybrid_mode();
+    if (mode == 0 || (!pre && active.size() < 3)) return B200_OK;
     const uint32_t words = lo.elem_size / 4;
     if (lo.elem_size % 4 != 0 || (words != 1 && words != 2) || lo.levels > 8) return B200_OK;
     if (!word_path_ok(lo, data, tmp) || n >= (1ull << 32)) return B200_OK;
@@ -872,7 +878,21 @@ int sort_hybrid(DeviceCtx& c, cudaStream_t st, void* data, void* tmp, uint64_t n
     // ---- the digits: bit windows over the varying bits of the key image (plan_windows) ----
     // keys that do not fill their type — or one rank's range of a sharded sort — still split 65 536 ways
     WindowPlan wp;
-    if (!plan_windows(lo, c.h_hist, n, &wp)) return B200_OK;
+    if (pre) {
+        // D1 = the level the array is partitioned on, D2 = the level below, local windows = every level below that.
+        // Which of the lower bits vary is not known (no K1 ran on this array); windows over constant bits sort
+        // nothing and cost little, and K3-U finds every segment's top bit by itself (AUTOTOP instantiations).
+        const uint32_t L = ctl->presplit_level;
+        if (!key_only || L < 2 || L >= lo.levels) return B200_OK;
+        memset(&wp, 0, sizeof(wp));
+        wp.w1_lo = 8 * L, wp.w2_lo = 8 * (L - 1), wp.w2_width = 8;
+        wp.nlocal = L - 1;
+        for (uint32_t i = 0; i + 1 < L; ++i) wp.local_lo[i] = 8 * i, wp.local_width[i] = 8;
+        wp.vary = (L + 1 >= 8) ? ~0ull : ((1ull << (8 * (L + 1))) - 1);
+        wp.aligned = true;
+    } else if (!plan_windows(lo, c.h_hist, n, &wp)) {
+        return B200_OK;
+    }
     const uint32_t w1_lo = wp.w1_lo, w2_lo = wp.w2_lo, w2_width = wp.w2_width, nlocal = wp.nlocal;
     const DigitParams W1 = window_params(lo, key, w1_lo, 8), W2 = window_params(lo, key, w2_lo, w2_width);
     DigitParams local[LS_MAXLEV];
@@ -901,7 +921,13 @@ int sort_hybrid(DeviceCtx& c, cudaStream_t st, void* data, void* tmp, uint64_t n
     static const bool dbg = getenv("B200SORT_DEBUG_TIMING") != nullptr;
     if (dbg) cudaEventRecord(c.ev[3], st);
     uint64_t hw[2 * RADIX];  // histograms of the two MSD digits
-    if (aligned) {
+    void* const A = pre ? data : tmp;  // where MSD pass 2 reads (the array partitioned on D1)
+    void* const B = pre ? tmp : data;  // where it writes: the segments' home
+    if (pre) {
+        uint64_t s1 = 0;
+        for (int b = 0; b < RADIX; ++b) hw[b] = ctl->presplit_counts[b], hw[RADIX + b] = 0, s1 += hw[b];
+        if (s1 != n) return B200_ERR_BAD_ARG;
+    } else if (aligned) {
         memcpy(hw, c.h_hist + size_t(A1) * RADIX, RADIX * 8);
         memcpy(hw + RADIX, c.h_hist + size_t(A2) * RADIX, RADIX * 8);
     } else {
@@ -961,7 +987,9 @@ int sort_hybrid(DeviceCtx& c, cudaStream_t st, void* data, void* tmp, uint64_t n
         *occ = std::max(*occ, 1);
         return B200_OK;
     };
-    const bool u1 = key_only && digit_is_flat(hw, n), u2 = key_only && digit_is_flat(hw + RADIX, n);
+    // (presplit: D2's histogram is not known yet; uniform-looking keys are what takes this route, and a skewed
+    // digit costs K2-U time, not correctness)
+    const bool u1 = key_only && digit_is_flat(hw, n), u2 = key_only && (pre || digit_is_flat(hw + RADIX, n));
     const PassPlan& k1 = u1 ? pu : ps;
     const PassPlan& k2 = u2 ? pu : ps;
     int occ1 = 1, occ2 = 1;
@@ -981,7 +1009,9 @@ int sort_hybrid(DeviceCtx& c, cudaStream_t st, void* data, void* tmp, uint64_t n
     CUDA_TRY(cudaMemsetAsync(d_tk, 0, 4096, st));
 
     // ---- MSD pass 1: data -> tmp on the first digit ----
-    if (aligned && !u1) {
+    if (pre) {
+        rc = B200_OK;  // done by whoever partitioned the array
+    } else if (aligned && !u1) {
         rc = launch_pass(c, st, pp, lo, data, tmp, n, A1, reinterpret_cast<const uint64_t*>(d_base + size_t(A1) * RADIX),
                          d_ticket, 1, nullptr);
     } else {
@@ -1005,12 +1035,12 @@ int sort_hybrid(DeviceCtx& c, cudaStream_t st, void* data, void* tmp, uint64_t n
                          d_ts, d_rs, d_b1, &W1);
     }
     if (rc) return rc;
-    *launches += 1;
-    *src_out = tmp;
+    if (!pre) *launches += 1;
+    *src_out = A;
     cudaEventRecord(c.ev[4], st);
     // ---- joint histogram of the two digits on the partitioned array = the 65 536 segment sizes ----
     Hist2Params hp;
-    hp.src = static_cast<const uint32_t*>(tmp);
+    hp.src = static_cast<const uint32_t*>(A);
     hp.n = n;
     hp.l1 = W1;
     hp.l2 = W2;
@@ -1082,7 +1112,7 @@ int sort_hybrid(DeviceCtx& c, cudaStream_t st, void* data, void* tmp, uint64_t n
     PassPlan p2 = k2;
     p2.num_tiles = h_tile_start[RADIX];
     p2.grid = int(std::min<uint64_t>(p2.num_tiles, uint64_t(c.sm_count) * occ2));
-    rc = launch_pass(c, st, p2, lo, tmp, data, n, 0, d_seg, d_tk + 1, 1, nullptr, nullptr, nullptr, nullptr, 0, nullptr,
+    rc = launch_pass(c, st, p2, lo, A, B, n, 0, d_seg, d_tk + 1, 1, nullptr, nullptr, nullptr, nullptr, 0, nullptr,
                      d_tile_start, d_rec_start, d_seg, &W2);
     if (rc) return rc;
     *launches += 1;
@@ -1090,7 +1120,7 @@ int sort_hybrid(DeviceCtx& c, cudaStream_t st, void* data, void* tmp, uint64_t n
     // ---- K3: every segment sorted in shared memory, in place in `data` ----
     LocalSortParams lp;
     memset(&lp, 0, sizeof(lp));
-    lp.data = static_cast<uint32_t*>(data);
+    lp.data = static_cast<uint32_t*>(B);
     lp.seg_off = d_seg;
     lp.nseg = RADIX * RADIX;
     lp.ticket = d_tk;
@@ -1113,10 +1143,11 @@ int sort_hybrid(DeviceCtx& c, cudaStream_t st, void* data, void* tmp, uint64_t n
         // 3.59 against 3.88 ms at 500 M f32), loses for 8-byte keys whose 64-register budget spills
         // (profiles/r4_k3u_variants.txt)
         const bool wide = getenv("B200SORT_K3U_WIDE") ? atoi(getenv("B200SORT_K3U_WIDE")) != 0 : words == 1;
-        const LocalCountLaunch ll = words == 1 ? get_local_count_launch_w1(lo.is_float, size, wide) : get_local_count_launch_w2(lo.is_float, size, wide);
+        const LocalCountLaunch ll = words == 1 ? get_local_count_launch_w1(lo.is_float, size, wide, pre)
+                                               : get_local_count_launch_w2(lo.is_float, size, wide, pre);
         LocalCountParams cp;
         memset(&cp, 0, sizeof(cp));
-        cp.data = static_cast<uint32_t*>(data);
+        cp.data = static_cast<uint32_t*>(B);
         cp.seg_off = d_seg;
         cp.key = key;
         // the digit starts at the highest bit below D2 that varies at all (plan_windows guarantees there is one)
@@ -1147,7 +1178,7 @@ int sort_hybrid(DeviceCtx& c, cudaStream_t st, void* data, void* tmp, uint64_t n
                 CUDA_TRY(cudaEventRecord(ctl->drain_event, st));
                 CUDA_TRY(cudaStreamWaitEvent(ctl->drain_stream, ctl->drain_event, 0));
                 if (hi_b > lo_b)
-                    CUDA_TRY(cudaMemcpyAsync(static_cast<uint8_t*>(ctl->drain_host) + lo_b, static_cast<const uint8_t*>(data) + lo_b,
+                    CUDA_TRY(cudaMemcpyAsync(static_cast<uint8_t*>(ctl->drain_host) + lo_b, static_cast<const uint8_t*>(B) + lo_b,
                                              hi_b - lo_b, cudaMemcpyDeviceToHost, ctl->drain_stream));
             }
         }
@@ -1177,13 +1208,13 @@ int sort_hybrid(DeviceCtx& c, cudaStream_t st, void* data, void* tmp, uint64_t n
             bool finished = false;
             uint32_t rounds = 0, slow2 = 0;
             cp.ticket = d_tk + 12;
-            rc = sort_heavy(c, st, data, tmp, lo, words, big, cp, lp, launches, &rounds, &slow2, &finished);
+            rc = sort_heavy(c, st, B, A, lo, words, big, cp, lp, launches, &rounds, &slow2, &finished);
             if (rc) return rc;
             if (ctl) ctl->heavy_segments = uint32_t(big.size()), ctl->heavy_rounds = rounds;
             if (dbg) fprintf(stderr, "[b200sort] hybrid: %zu oversized segments, %u pivot-split rounds, %s\n", big.size(), rounds,
                              finished ? "finished" : "NOT finished: LSD passes over the array");
             if (!finished) {
-                *src_out = data;  // a permutation of the input; the caller runs the LSD passes on it
+                *src_out = B;  // a permutation of the input; the caller runs the LSD passes on it
                 return B200_OK;
             }
         }
@@ -1236,7 +1267,7 @@ int sort_hybrid(DeviceCtx& c, cudaStream_t st, void* data, void* tmp, uint64_t n
                 aligned ? "" : ", window histogram pass");
     }
     *done = true;
-    *src_out = data;
+    *src_out = B;
     if (local_levels) *local_levels = nlocal;
     return B200_OK;
 }
@@ -2450,6 +2481,73 @@ const char* b200_last_cuda_error(void) { return g_last_cuda_error.c_str(); }
 const char* b200_version(void) { return "b200sort 0.1.0 (sm_100a)"; }
 
 }  // extern "C"
+
+// ===========================================================================
+// b200_sort_device_presplit — the local sort of the sharded sort when the exchange has already done MSD pass 1:
+// the array arrives partitioned on `level` (bucket sizes `counts`, buckets in digit order; every level above is
+// constant), so K0, K1 and the first MSD pass are skipped: joint histogram -> MSD pass 2 (dev_ptr -> dev_tmp) ->
+// K3-U in dev_tmp.  The result is wherever it ends up (*result_out = dev_ptr or dev_tmp): a copy home would cost
+// a quarter of what was saved.  Records that are not key-only, or segments that do not fit: the general sort runs
+// from where the records are — same result, none of the saving.
+// ===========================================================================
+extern "C" int b200_sort_device_presplit(void* dev_ptr, void* dev_tmp, size_t n, const b200_key_desc* desc, uint32_t level,
+                                         const uint64_t* counts, const b200_sort_opts* opts, b200_stats* stats, void** result_out) {
+    Lowered lo;
+    int rc = lower_desc(desc, &lo);
+    if (rc) return rc;
+    if (stats) memset(stats, 0, sizeof(*stats));
+    if (level >= lo.levels) return B200_ERR_LEVEL_RANGE;
+    if (!counts || !result_out) return B200_ERR_BAD_ARG;
+    *result_out = dev_ptr;
+    if (n <= 1) return B200_OK;
+    if (!dev_ptr || !dev_tmp) return B200_ERR_BAD_ARG;
+    DeviceCtx* cp_ = nullptr;
+    rc = get_ctx(opts ? opts->device : -1, &cp_);
+    if (rc) return rc;
+    DeviceCtx& c = *cp_;
+    std::lock_guard<std::mutex> lk(c.mu);
+    DeviceGuard guard(c.dev);
+    cudaStream_t st = (opts && opts->stream) ? static_cast<cudaStream_t>(opts->stream) : c.stream;
+    SortCtl ctl;
+    ctl.presplit_counts = counts;
+    ctl.presplit_level = level;
+    ctl.result_anywhere = true;
+    bool done = false;
+    void* where = dev_ptr;
+    uint32_t launches = 0, slow = 0, local_levels = 0, unstable = 0;
+    const std::vector<uint32_t> no_levels;
+    CUDA_TRY(cudaEventRecord(c.ev[0], st));
+    rc = sort_hybrid(c, st, dev_ptr, dev_tmp, n, lo, no_levels, reinterpret_cast<unsigned long long*>(c.d_small + SMALL_BASE_OFF),
+                     reinterpret_cast<uint32_t*>(c.d_small + SMALL_TICKET_OFF), &done, &where, &launches, &slow, &local_levels,
+                     &unstable, &ctl);
+    if (rc) return rc;
+    if (!done) {  // not this route's shape, or it gave up: `where` holds a permutation of the input
+        SortCtl plain;
+        plain.variant = opts ? opts->variant : -1;
+        plain.result_anywhere = true;
+        return sort_device_impl(c, st, where, where == dev_ptr ? dev_tmp : dev_ptr, n, lo, plain, result_out, stats);
+    }
+    CUDA_TRY(cudaEventRecord(c.ev[2], st));
+    CUDA_TRY(cudaStreamSynchronize(st));
+    *result_out = where;
+    if (stats) {
+        stats->levels_run = level + 1;
+        stats->levels_skipped = lo.levels - (level + 1);
+        stats->hybrid = 1;
+        stats->unstable = unstable;
+        stats->slow_segments = slow;
+        stats->local_levels = local_levels;
+        stats->heavy_segments = ctl.heavy_segments;
+        stats->heavy_rounds = ctl.heavy_rounds;
+        stats->kernel_launches = launches;
+        stats->algorithmic_bytes = n * lo.elem_size * (1ull + 2ull * (level + 1));
+        CUDA_TRY(cudaEventElapsedTime(&stats->ms_joint, c.ev[4], c.ev[5]));
+        CUDA_TRY(cudaEventElapsedTime(&stats->ms_local, c.ev[6], c.ev[7]));
+        CUDA_TRY(cudaEventElapsedTime(&stats->ms_total, c.ev[0], c.ev[2]));
+        stats->ms_passes = stats->ms_total;
+    }
+    return B200_OK;
+}
 
 // ===========================================================================
 // b200_sort_segments_device — many independent sorts in one call: every segment [seg_off[i], seg_off[i + 1]) of one

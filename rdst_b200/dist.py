@@ -16,6 +16,7 @@ nothing here falls back to a CPU path.)
 from __future__ import annotations
 
 import ctypes as C
+import os
 
 import numpy as np
 
@@ -297,6 +298,26 @@ class CudaEngine:
         self.launches += st.kernel_launches
         return st.as_dict()
 
+    def presplit_ok(self):
+        """Records that are nothing but their key, 4 or 8 bytes: the shape the exchange may deliver split on all 256
+        digits of the partition level, so that the local sort starts at its second MSD pass."""
+        k = self.key
+        return (k.kind in ("uint", "int", "float") and k.elem_size in (4, 8) and k.key_offset == 0
+                and k.key_width == k.elem_size and k.levels == k.elem_size)
+
+    def sort_presplit(self, buf, tmp, n, level, counts):
+        """Local sort of an array that arrives partitioned on `level` (b200_sort_device_presplit).  Returns
+        (the buffer holding the result: buf or tmp, stats)."""
+        o = self._opts()
+        st = _abi.Stats()
+        cnt = np.ascontiguousarray(counts, dtype=np.uint64)
+        res = C.c_void_p()
+        _abi.check(self.lib.b200_sort_device_presplit(buf.data_ptr(), tmp.data_ptr(), n, C.byref(self.desc), int(level),
+                                                      cnt.ctypes.data_as(C.POINTER(C.c_uint64)), C.byref(o), C.byref(st),
+                                                      C.byref(res)))
+        self.launches += st.kernel_launches
+        return (tmp if res.value == tmp.data_ptr() else buf), st.as_dict()
+
     def to_comm(self, arr_np):
         return self.torch.from_numpy(arr_np).cuda()
 
@@ -515,6 +536,7 @@ def sharded_sort(local, n_local: int, key: RadixKey, engine=None, group=None, re
         plan_t["gather_plan_ms"] = (_time.perf_counter() - _t0) * 1e3
     send_counts, recv_counts = m[rank], m[:, rank]
     n_recv = int(recv_counts.sum())
+    presplit = presplit_counts = None
     # 4. stable local partition into P contiguous send regions, then the all-to-all
     fused = bool(scratch and scratch.get("peers") is not None)
     part = recv = None
@@ -524,6 +546,14 @@ def sharded_sort(local, n_local: int, key: RadixKey, engine=None, group=None, re
         if recv.numel() < n_recv * key.elem_size:
             raise _abi.B200SortError(5, f"receive buffer too small for {n_recv} records (skewed splitters)")
     peers = scratch.get("peers") if scratch else None
+    # (a rank owns 256 / P digits of the partition level, so its local sort is left with (256 / P) * 256 segments: they
+    # fit an SM — 16 384 records, 8192 expected — only up to 512 Mi records in the whole job; a decision every rank
+    # takes from the same gathered numbers)
+    n_total = int(all_hist[:, 0, :].sum())
+    penv = os.environ.get("B200SORT_DIST_PRESPLIT", "")
+    presplit = bool(peers is not None and splitters is None and not pipelined and level >= 2 and scratch.get("tmp") is not None
+                    and getattr(eng, "presplit_ok", None) and eng.presplit_ok() and penv != "0"
+                    and (n_total <= 512 << 20 or penv == "1"))
     if ev:
         ev[1].record()
     if peers is not None:
@@ -538,6 +568,23 @@ def sharded_sort(local, n_local: int, key: RadixKey, engine=None, group=None, re
                                 send_counts)
         elif splitters is not None:
             eng.partition_splitters(local, None, dst, n_local, splitters, incl_mask_for_rank(t_thr, rank), send_counts)
+        elif presplit:
+            # the exchange IS the first MSD pass: every digit of the partition level gets its own run in the owner's
+            # buffer — buckets in digit order, inside a bucket the senders in rank order — so the receiver's array
+            # arrives partitioned on that level and its local sort starts at the second pass
+            tot = all_hist[:, level, :].astype(np.int64)              # [P, 256]
+            gtot = tot.sum(axis=0)
+            pod = part_of_digit(split, world)
+            bucket_start = np.zeros(256, dtype=np.int64)
+            for g in range(world):
+                idx = np.nonzero(pod == g)[0]
+                if len(idx):
+                    bucket_start[idx] = np.concatenate([[0], np.cumsum(gtot[idx])[:-1]])
+            before_me = tot[:rank].sum(axis=0)
+            dst256 = [peers.ptrs[int(pod[d])] + int(bucket_start[d] + before_me[d]) * key.elem_size for d in range(256)]
+            pc = eng.partition_peers(local, dst256, n_local, level, hist[level], np.arange(1, 256, dtype=np.uint32), 256)
+            assert np.array_equal(pc, hist[level].astype(np.int64)), "partition counts disagree with the histogram"
+            presplit_counts = np.where(pod == rank, gtot, 0).astype(np.uint64)
         else:
             pc = eng.partition_peers(local, dst, n_local, level, hist[level], split, world)
             assert np.array_equal(pc, send_counts), "partition counts disagree with the gathered histograms"
@@ -560,9 +607,12 @@ def sharded_sort(local, n_local: int, key: RadixKey, engine=None, group=None, re
             ev[3].record()
     # 5. independent local LSD sort of the received range (levels above `level` are
     #    single-bucket per rank only by luck; K1 decides what to skip)
-    st = eng.sort(recv, n_recv, scratch.get("tmp") if scratch else None)
+    if presplit and scratch["tmp"].numel() >= n_recv * key.elem_size:
+        recv, st = eng.sort_presplit(recv, scratch["tmp"], n_recv, level, presplit_counts)
+    else:
+        st = eng.sort(recv, n_recv, scratch.get("tmp") if scratch else None)
     if timings is not None:
-        timings.update({"level": level, "split": split.tolist(), "n_recv": n_recv, "local": st,
+        timings.update({"level": level, "presplit": bool(presplit), "split": split.tolist(), "n_recv": n_recv, "local": st,
                         "splitter_mode": "prefix" if splitters is not None else "digit", "splitter_plan_ms": plan_t,
                         "exchange_path": "pipelined" if (pipelined and splitters is None and peers is not None) else
                         ("fused" if peers is not None else "all_to_all"),

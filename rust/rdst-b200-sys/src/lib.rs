@@ -151,6 +151,10 @@ extern "C" {
                           stats: *mut b200_stats) -> c_int;
     pub fn b200_sort_device(dev_ptr: *mut c_void, dev_tmp: *mut c_void, n: usize, desc: *const b200_key_desc,
                             opts: *const b200_sort_opts, stats: *mut b200_stats) -> c_int;
+    /// Local sort of an array that arrives partitioned on `level` (bucket sizes `counts[256]`); result at *result_out.
+    pub fn b200_sort_device_presplit(dev_ptr: *mut c_void, dev_tmp: *mut c_void, n: usize, desc: *const b200_key_desc, level: u32,
+                                     counts: *const u64, opts: *const b200_sort_opts, stats: *mut b200_stats,
+                                     result_out: *mut *mut c_void) -> c_int;
     /// Every segment [seg_off[i], seg_off[i + 1]) sorted on its own (seg_off: host memory, nseg + 1 offsets).
     pub fn b200_sort_segments_device(dev_ptr: *mut c_void, n: usize, seg_off: *const u64, nseg: usize,
                                      desc: *const b200_key_desc, opts: *const b200_sort_opts, stats: *mut b200_stats) -> c_int;

@@ -53,6 +53,7 @@ def main():
     mode = os.environ.get("DIST_CHECK_MODE", "nccl")
     peers = PeerBuffers(64 << 20) if mode in ("peer", "ce") else None
     part = torch.empty(64 << 20, dtype=torch.uint8, device="cuda") if mode == "ce" else None
+    tmp_buf = torch.empty(64 << 20, dtype=torch.uint8, device="cuda") if peers else None
     for name, key, full in cases():
         es = key.elem_size
         n = len(full) // es
@@ -61,7 +62,9 @@ def main():
         tm = {}
         scratch = None
         if peers:
-            scratch = {"peers": peers}
+            # (with a scratch buffer for the local sort the peer mode delivers key-only records split on all 256 digits
+            # of the partition level and the local sort starts at its second MSD pass: rdst_b200/dist.py `presplit`)
+            scratch = {"peers": peers, "tmp": tmp_buf}
             if part is not None:  # chunked partition pipelined with copy-engine pushes (3 uneven chunks)
                 scratch.update({"part": part, "ce_chunks": 3})
         out, n_out = sharded_sort(shard, hi - lo, key, scratch=scratch, timings=tm)
@@ -79,7 +82,7 @@ def main():
             got = torch.cat(bufs).cpu().numpy().tobytes()
             exp = o.stable_sorted(full, key).tobytes()
             good = got == exp
-            print(f"[dist_check] {mode} {name} ({tm.get('exchange_path')}): {'ok' if good else 'MISMATCH'} splitters={tm.get('splitter_mode')} sizes={[s // es for s in sizes]}", flush=True)
+            print(f"[dist_check] {mode} {name} ({tm.get('exchange_path')}{', presplit' if tm.get('presplit') else ''}): {'ok' if good else 'MISMATCH'} splitters={tm.get('splitter_mode')} sizes={[s // es for s in sizes]}", flush=True)
             ok = ok and good
     if os.environ.get("DIST_CHECK_BIG"):
         ok = big_case(rank, world, mode) and ok
@@ -107,7 +110,7 @@ def big_case(rank, world, mode):
     peers = None
     if mode in ("peer", "ce"):
         peers = PeerBuffers(int(n * 8 * 1.3))
-        scratch = {"peers": peers}
+        scratch = {"peers": peers, "tmp": torch.empty(int(n * 8 * 1.3), dtype=torch.uint8, device="cuda")}
         if mode == "ce":
             scratch.update({"part": torch.empty(n * 8, dtype=torch.uint8, device="cuda"), "ce_chunks": 3})
     tm = {}
@@ -135,7 +138,7 @@ def big_case(rank, world, mode):
         pool = torch.cat(allc).cpu().numpy().view("u8")
         exp = o.sorted_copy(pool, key)[:m]
         ok = ok and res[:m].cpu().numpy().view("u8").tobytes() == exp.tobytes()
-        print(f"[dist_check] {mode} big u64 x {n} per rank, world {world} (local sort hybrid={tm['local'].get('hybrid')} "
+        print(f"[dist_check] {mode} big u64 x {n} per rank, world {world} (presplit={tm.get('presplit')} local sort hybrid={tm['local'].get('hybrid')} "
               f"unstable={tm['local'].get('unstable')}): {'ok' if ok else 'MISMATCH'} per-rank {[x[2] for x in allfl]}", flush=True)
     if peers:
         del scratch
