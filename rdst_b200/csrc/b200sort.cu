@@ -333,7 +333,7 @@ int launch_pass(DeviceCtx& c, cudaStream_t st, const PassPlan& pp, const Lowered
                 const uint8_t* d_remap, const uint64_t* d_dst_tab = nullptr, const SplitParams* sp = nullptr,
                 const uint32_t* hot = nullptr, uint32_t match_bits = 0, uint64_t* lookback = nullptr,
                 const uint32_t* seg_tile_start = nullptr, const uint64_t* seg_rec_start = nullptr,
-                const uint64_t* seg_bases = nullptr, const DigitParams* window = nullptr) {
+                const uint64_t* seg_bases = nullptr, const DigitParams* window = nullptr, uint32_t nparts = 0) {
     if (pp.word_path) {
         PassParams p;
         memset(&p.sp, 0, sizeof(p.sp));
@@ -352,6 +352,7 @@ int launch_pass(DeviceCtx& c, cudaStream_t st, const PassPlan& pp, const Lowered
         p.hot[0] = hot ? hot[0] : 0xffffffffu;
         p.hot[1] = hot ? hot[1] : 0xffffffffu;
         p.match_bits = match_bits;
+        p.nparts = nparts;
         p.seg_tile_start = seg_tile_start;
         p.seg_rec_start = seg_rec_start;
         p.seg_bases = seg_bases;
@@ -2125,7 +2126,7 @@ static int pass_common(const void* dev_src, void* dev_dst, size_t n, const b200_
     if (dst_ptrs) CUDA_TRY(cudaMemcpyAsync(d_dtab, h_dtab, sizeof(h_dtab), cudaMemcpyHostToDevice, st));
     rc = launch_pass(*c, st, pp, lo, dev_src, dev_dst, n, level, d_pbase, d_ticket, 1, remap ? d_remap : nullptr,
                      dst_ptrs ? d_dtab : nullptr, nullptr, (pp.word_path && pp.pl.hot) ? hot : nullptr,
-                     remap ? match_bits_for(parts) : 0);
+                     remap ? match_bits_for(parts) : 0, nullptr, nullptr, nullptr, nullptr, nullptr, remap ? parts : 0);
     if (rc) return rc;
     CUDA_TRY(cudaStreamSynchronize(st));
     return B200_OK;
@@ -2308,7 +2309,7 @@ int b200_partition_splitters_device(const void* dev_src, void* dev_dst, void* co
     CUDA_TRY(cudaMemcpyAsync(d_pbase, h_base, sizeof(h_base), cudaMemcpyHostToDevice, st));
     if (dst_ptrs) CUDA_TRY(cudaMemcpyAsync(d_dtab, h_dtab, sizeof(h_dtab), cudaMemcpyHostToDevice, st));
     rc = launch_pass(*c, st, pp, lo, dev_src, dev_dst, n, 0, d_pbase, d_ticket, 1, d_remap, dst_ptrs ? d_dtab : nullptr, &sp,
-                     nullptr, match_bits_for(parts));
+                     nullptr, match_bits_for(parts), nullptr, nullptr, nullptr, nullptr, nullptr, parts);
     if (rc) return rc;
     CUDA_TRY(cudaStreamSynchronize(st));
     return B200_OK;

@@ -54,6 +54,8 @@ struct PassParams {
     SplitParams sp;               // remap kernels only: splitter mode when sp.nsplit != 0
     uint32_t hot[2];              // half-warp kernel: buckets matched by ballot (0xffffffff = none)
     uint32_t match_bits;          // half-warp remap kernel: match the part id by this many ballots (0 = OR-matching)
+    uint32_t nparts;              // half-warp remap kernel with dst_tab: parts in use (0 = unknown); <= 16 parts are
+                                  // written out part by part, the warps lined up on the destination's 128-byte lines
     // half-warp kernel, segmented mode (second MSD pass of the hybrid path): the array is 256 buckets, every
     // bucket is partitioned on its own (own tiles, own look-back chain, own bucket bases)
     const uint32_t* seg_tile_start;  // [257] first global tile id of every bucket; nullptr = one array

@@ -250,6 +250,7 @@ __global__ void __launch_bounds__(THREADS, MINB) lsd_pass_or16_kernel(const Pass
             for (int w = 0; w < RADIX / 32; ++w)
                 if (uint32_t(w) < dg / 32) wbase += s_wtot[w];
             local_off = wbase + incl - sum;
+            if (REMAP && h == 0) s_gofs32[dg] = local_off;  // REMAP: where every part's run starts in the staged tile
             // slot count := position of the (group, digit) run inside the locally sorted tile
             const uint32_t ca = slot_base + (h * GPH * RADIX + dg) * 4;
             uint32_t run = local_off + before;
@@ -330,7 +331,22 @@ __global__ void __launch_bounds__(THREADS, MINB) lsd_pass_or16_kernel(const Pass
 
         // ---- write-out: runs of equal digits are contiguous in s_out and in dst ----
         if constexpr (WORDS == 1 || WORDS == 2 || WORDS == 4) {
-            if (!REMAP && full && p.n <= 0xffffffffull) {
+            if (REMAP && p.dst_tab && p.nparts != 0 && p.nparts <= 16) {
+                // few parts, each with its own destination (peer GPUs over NVLink): part by part, with the warps lined
+                // up on the DESTINATION's 128-byte lines.  A run starts wherever the previous tile's run ended; stores
+                // issued in staging order straddle three lines per warp, two of them partially, which costs the link
+                // an eighth of its rate (profiles/r12_exchange_experiments.txt: 628 against 715 GB/s).
+                constexpr uint32_t LINE = 128 / (4 * WORDS);  // records per line
+                for (uint32_t q = 0; q < p.nparts; ++q) {
+                    const uint32_t a = s_gofs32[q], b = q + 1 < uint32_t(RADIX) ? s_gofs32[q + 1] : valid;
+                    if (a == b) continue;
+                    uint32_t* const dstq = reinterpret_cast<uint32_t*>(s_gptr[q]);
+                    const uint64_t go = s_gofs[q];
+                    const uint32_t mis = uint32_t((s_gptr[q] / (4 * WORDS) + go + a) % LINE);
+                    for (int64_t i = int64_t(a) - mis + tid; i < int64_t(b); i += THREADS)
+                        if (i >= int64_t(a)) store_rec<WORDS>(dstq, go + uint64_t(i), load_rec<WORDS>(s_out, uint32_t(i)));
+                }
+            } else if (!REMAP && full && p.n <= 0xffffffffull) {
                 // record indices fit 32 bits: 32-bit offset table (half the shared-memory wavefronts)
 #pragma unroll 4
                 for (int k = 0; k < ITEMS; ++k) {
