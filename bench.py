@@ -621,7 +621,7 @@ def run_one(args, workload, torch, dist, world, rank, local_rank, cpu_group):
         line["e2e_pageable"] = e2e_pageable
     if world > 1:
         line["exchange"] = {"mode": args.exchange}
-        line["exchange"].update({k: last.get(k) for k in ("level", "n_recv", "sent_bytes", "phase_ms", "splitter_mode", "splitter_plan_ms", "exchange_path", "presplit")})
+        line["exchange"].update({k: last.get(k) for k in ("level", "n_recv", "sent_bytes", "phase_ms", "splitter_mode", "splitter_plan_ms", "exchange_path", "presplit", "vary_hint")})
         line["exchange"]["max_n_recv_over_ranks"] = max_n_recv
         line["exchange"]["imbalance"] = max_n_recv / float(n)
         pm = last.get("phase_ms") or {}

@@ -163,6 +163,17 @@ int b200_sort_device(void* dev_ptr, void* dev_tmp, size_t n, const b200_key_desc
                      const b200_sort_opts* opts, b200_stats* stats);
 
 /*
+ * b200_sort_device for a caller that already knows which bits of the key image (level l = bits 8l .. 8l+7) can differ
+ * between two records; a superset of the truth is fine, a missing bit gives a wrong order.  The library then does not
+ * count the records first (no K0, no K1): the digits of the MSD route are planned from `vary_bits`.  Inputs the MSD route
+ * does not take (records with a payload below 256 Mi records, small arrays ...) are sorted as by b200_sort_device.
+ * Used by the sharded sort, whose gathered histograms describe every rank's range (rdst_b200/dist.py).
+ * No counterpart in the reference; SURVEY §8(e).
+ */
+int b200_sort_device_hinted(void* dev_ptr, void* dev_tmp, size_t n, const b200_key_desc* desc, uint64_t vary_bits,
+                            const b200_sort_opts* opts, b200_stats* stats);
+
+/*
  * The local sort of the sharded sort when the exchange has already split the records on one level: `dev_ptr` holds n
  * records partitioned on `level` — bucket sizes `counts[256]` (host), buckets in digit order, every level above
  * `level` constant — as b200_partition_peers_device with 256 parts delivers them.  K0, K1 and the first MSD pass are

@@ -169,6 +169,10 @@ SYMBOLS = {
         C.c_int,
         [C.c_void_p, C.c_void_p, C.c_size_t, C.POINTER(KeyDesc), C.POINTER(SortOpts), C.POINTER(Stats)],
     ),
+    "b200_sort_device_hinted": (
+        C.c_int,
+        [C.c_void_p, C.c_void_p, C.c_size_t, C.POINTER(KeyDesc), C.c_uint64, C.POINTER(SortOpts), C.POINTER(Stats)],
+    ),
     "b200_sort_device_presplit": (
         C.c_int,
         [C.c_void_p, C.c_void_p, C.c_size_t, C.POINTER(KeyDesc), C.c_uint32, C.POINTER(C.c_uint64), C.POINTER(SortOpts),

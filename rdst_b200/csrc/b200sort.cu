@@ -556,6 +556,7 @@ struct WindowPlan {
     uint32_t nlocal, local_lo[LS_MAXLEV], local_width[LS_MAXLEV];
     bool aligned;             // D1 and D2 are whole levels: K1 already has their histograms
 };
+bool plan_windows_from_vary(uint64_t vary, WindowPlan* wp);
 bool plan_windows(const Lowered& lo, const uint64_t* hist, uint64_t n, WindowPlan* wp) {
     memset(wp, 0, sizeof(*wp));
     if (lo.levels > 8) return false;
@@ -569,6 +570,11 @@ bool plan_windows(const Lowered& lo, const uint64_t* hist, uint64_t n, WindowPla
             if (ones != 0 && ones != n) vary |= 1ull << (8 * l + bit);
         }
     }
+    return plan_windows_from_vary(vary, wp);
+}
+// the windows from the set of varying bits alone (a superset is fine: windows over constant bits sort nothing)
+bool plan_windows_from_vary(uint64_t vary, WindowPlan* wp) {
+    memset(wp, 0, sizeof(*wp));
     wp->vary = vary;
     if (!vary) return false;
     const int T1 = 63 - __builtin_clzll(vary);
@@ -850,6 +856,10 @@ struct SortCtl {
     // result in `tmp`
     const uint64_t* presplit_counts = nullptr;  // [256] bucket sizes on presplit_level, in order
     uint32_t presplit_level = 0;
+    // the caller knows which bits of the key image can differ between two records (the sharded sort: the gathered
+    // histograms say so for every rank's range): K0 and K1 are skipped, the digits are planned from the hint and their
+    // histograms come from the window histogram pass.  A superset of the truth is fine.  0 = no hint.
+    uint64_t vary_hint = 0;
 };
 
 // Returns B200_OK with *done = true when the array was sorted here (result in `data`);
@@ -891,6 +901,9 @@ int sort_hybrid(DeviceCtx& c, cudaStream_t st, void* data, void* tmp, uint64_t n
         for (uint32_t i = 0; i + 1 < L; ++i) wp.local_lo[i] = 8 * i, wp.local_width[i] = 8;
         wp.vary = (L + 1 >= 8) ? ~0ull : ((1ull << (8 * (L + 1))) - 1);
         wp.aligned = true;
+    } else if (ctl && ctl->vary_hint) {
+        if (!plan_windows_from_vary(ctl->vary_hint, &wp)) return B200_OK;
+        wp.aligned = false;  // no K1 ran: the digits' histograms come from the window histogram pass
     } else if (!plan_windows(lo, c.h_hist, n, &wp)) {
         return B200_OK;
     }
@@ -1501,6 +1514,60 @@ int sort_device_impl(DeviceCtx& c, cudaStream_t st, void* data, void* tmp, uint6
             stats->ms_passes = stats->ms_total = stats->ms_local;
         }
         return B200_OK;
+    }
+    // The caller says which key bits can vary (SortCtl::vary_hint): no K0, no K1 — the hybrid route plans its digits
+    // from the hint and counts them itself.  If it declines or gives up, the general path below runs on wherever the
+    // records are, without the hint.
+    if (ctl.vary_hint && auto_route && !ctl.pre_counted) {
+        std::vector<uint32_t> hinted;
+        for (uint32_t l = 0; l < lo.levels && l < 8; ++l)
+            if ((ctl.vary_hint >> (8 * l)) & 0xffull) hinted.push_back(l);
+        bool hdone = false;
+        void* where = data;
+        uint32_t hl = 0, hslow = 0, hlocal = 0, hunst = 0;
+        CUDA_TRY(cudaEventRecord(c.ev[1], st));
+        rc = sort_hybrid(c, st, data, tmp, n, lo, hinted, d_base, d_ticket, &hdone, &where, &hl, &hslow, &hlocal, &hunst, &ctl);
+        if (rc) return rc;
+        if (hdone) {
+            CUDA_TRY(cudaEventRecord(c.ev[2], st));
+            CUDA_TRY(cudaStreamSynchronize(st));
+            if (result_ptr) *result_ptr = where;
+            if (stats) {
+                stats->levels_run = uint32_t(hinted.size());
+                stats->levels_skipped = lo.levels - uint32_t(hinted.size());
+                stats->hybrid = 1;
+                stats->unstable = hunst;
+                stats->heavy_segments = ctl.heavy_segments;
+                stats->heavy_rounds = ctl.heavy_rounds;
+                stats->slow_segments = hslow;
+                stats->local_levels = hlocal;
+                stats->kernel_launches = hl;
+                stats->algorithmic_bytes = n * lo.elem_size * (1ull + 2ull * hinted.size());
+                CUDA_TRY(cudaEventElapsedTime(&stats->ms_joint, c.ev[4], c.ev[5]));
+                CUDA_TRY(cudaEventElapsedTime(&stats->ms_local, c.ev[6], c.ev[7]));
+                CUDA_TRY(cudaEventElapsedTime(&stats->ms_passes, c.ev[1], c.ev[7]));
+                CUDA_TRY(cudaEventElapsedTime(&stats->ms_total, c.ev[0], c.ev[2]));
+            }
+            return B200_OK;
+        }
+        ctl.vary_hint = 0;
+        ctl.heavy_segments = ctl.heavy_rounds = 0;
+        if (where != data) {  // MSD pass 1 ran before the route gave up: the records live in `tmp` now
+            SortCtl plain;
+            plain.variant = ctl.variant;
+            plain.route = ctl.route;
+            plain.result_anywhere = true;
+            void* res = nullptr;
+            rc = sort_device_impl(c, st, tmp, data, n, lo, plain, &res, stats);
+            if (rc) return rc;
+            if (res != data && !result_anywhere) {
+                CUDA_TRY(cudaMemcpyAsync(data, res, n * lo.elem_size, cudaMemcpyDeviceToDevice, st));
+                CUDA_TRY(cudaStreamSynchronize(st));
+                res = data;
+            }
+            if (result_ptr) *result_ptr = res;
+            return B200_OK;
+        }
     }
     // K0, the already-sorted early-out, rides in front of K1 on the same stream.  K1 is gated on K0's
     // flag on the device (its CTAs leave at once when no pair was out of order), so a presorted input
@@ -2482,6 +2549,37 @@ const char* b200_last_cuda_error(void) { return g_last_cuda_error.c_str(); }
 const char* b200_version(void) { return "b200sort 0.1.0 (sm_100a)"; }
 
 }  // extern "C"
+
+// b200_sort_device_hinted — b200_sort_device for a caller that knows which bits of the key image can differ between
+// two records (a superset is fine).  The local sort of the sharded sort: the gathered histograms say which bits vary
+// in every rank's range, so the receiver need not count its records again (K0 and K1 are skipped).
+extern "C" int b200_sort_device_hinted(void* dev_ptr, void* dev_tmp, size_t n, const b200_key_desc* desc, uint64_t vary_bits,
+                                       const b200_sort_opts* opts, b200_stats* stats) {
+    Lowered lo;
+    int rc = lower_desc(desc, &lo);
+    if (rc) return rc;
+    if (stats) memset(stats, 0, sizeof(*stats));
+    if (opts && opts->route > B200_HINT_LOW_SCRATCH) return B200_ERR_BAD_ARG;
+    if (n <= 1) return B200_OK;
+    if (!dev_ptr) return B200_ERR_BAD_ARG;
+    DeviceCtx* c = nullptr;
+    rc = get_ctx(opts ? opts->device : -1, &c);
+    if (rc) return rc;
+    std::lock_guard<std::mutex> lk(c->mu);
+    DeviceGuard guard(c->dev);
+    cudaStream_t st = (opts && opts->stream) ? static_cast<cudaStream_t>(opts->stream) : c->stream;
+    void* tmp = dev_tmp;
+    if (!tmp) {
+        rc = ensure_bytes(&c->d_tmp, &c->tmp_bytes, n * lo.elem_size);
+        if (rc) return rc;
+        tmp = c->d_tmp;
+    }
+    SortCtl ctl;
+    ctl.variant = opts ? opts->variant : -1;
+    ctl.route = opts ? opts->route : uint32_t(B200_HINT_AUTO);
+    if (lo.levels <= 8) ctl.vary_hint = lo.levels == 8 ? vary_bits : (vary_bits & ((1ull << (8 * lo.levels)) - 1));
+    return sort_device_impl(*c, st, dev_ptr, tmp, n, lo, ctl, nullptr, stats);
+}
 
 // ===========================================================================
 // b200_sort_device_presplit — the local sort of the sharded sort when the exchange has already done MSD pass 1:

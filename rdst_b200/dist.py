@@ -75,6 +75,29 @@ def plan_splitters(less: np.ndarray, equal: np.ndarray, n_per_rank: np.ndarray, 
     return t, m, masks
 
 
+_BIT_OF_DIGIT = ((np.arange(256)[:, None] >> np.arange(8)[None, :]) & 1).astype(np.int64)  # [256, 8]
+
+
+def global_vary_bits(global_hist: np.ndarray) -> int:
+    """Bits of the key image (level l = bits 8l..8l+7, the first 8 levels) in which some two records of the whole job
+    differ, from the summed per-level histograms [L, 256]."""
+    g = np.asarray(global_hist, dtype=np.int64)[:8]
+    n = int(g[0].sum())
+    ones = g @ _BIT_OF_DIGIT  # [L, 8]: records whose digit on level l has bit b set
+    varies = (ones > 0) & (ones < n)
+    vary = 0
+    for l, b in zip(*np.nonzero(varies)):
+        vary |= 1 << (8 * int(l) + int(b))
+    return vary
+
+
+def range_vary_bits(global_vary: int, lo_key: int, hi_key: int) -> int:
+    """Bits that can vary among keys of [lo_key, hi_key]: everything above the highest bit in which the two bounds
+    differ is the same for the whole range.  A superset of the truth, which is all b200_sort_device_hinted needs."""
+    x = int(lo_key) ^ int(hi_key)
+    return global_vary & ((1 << x.bit_length()) - 1)
+
+
 def pick_partition_level(global_hist: np.ndarray) -> int:
     """Most significant level whose global histogram is not a single bucket (rdst's
     trivial-level skip, reference src/sorts/ska_sort.rs:52-54, applied to the splitters).
@@ -317,6 +340,15 @@ class CudaEngine:
                                                       C.byref(res)))
         self.launches += st.kernel_launches
         return (tmp if res.value == tmp.data_ptr() else buf), st.as_dict()
+
+    def sort_hinted(self, buf, n, tmp, vary_bits):
+        """b200_sort_device_hinted: the local sort without its counting pass (the caller knows which bits can vary)."""
+        o = self._opts()
+        st = _abi.Stats()
+        _abi.check(self.lib.b200_sort_device_hinted(buf.data_ptr(), tmp.data_ptr() if tmp is not None else None, n,
+                                                    C.byref(self.desc), C.c_uint64(int(vary_bits)), C.byref(o), C.byref(st)))
+        self.launches += st.kernel_launches
+        return st.as_dict()
 
     def to_comm(self, arr_np):
         return self.torch.from_numpy(arr_np).cuda()
@@ -607,12 +639,29 @@ def sharded_sort(local, n_local: int, key: RadixKey, engine=None, group=None, re
             ev[3].record()
     # 5. independent local LSD sort of the received range (levels above `level` are
     #    single-bucket per rank only by luck; K1 decides what to skip)
+    hint = 0
+    if (key.levels <= 8 and hasattr(eng, "sort_hinted") and os.environ.get("B200SORT_DIST_HINT", "1") != "0"):
+        # which key bits can vary inside this rank's range: the job's varying bits below the highest bit in which the
+        # range's bounds differ — the receiver then sorts without counting its records first
+        gv = global_vary_bits(all_hist.sum(axis=0))
+        full = (1 << (8 * key.levels)) - 1
+        if splitters is not None:
+            lo_key = int(splitters[rank - 1]) if rank > 0 else 0
+            hi_key = int(splitters[rank]) if rank < world - 1 else full
+        else:
+            # (every level above the partition level is one value for the whole job: it cancels in lo ^ hi)
+            owned = np.nonzero((part_of_digit(split, world) == rank) & (all_hist[:, level, :].sum(axis=0) > 0))[0]
+            lo_key = (int(owned.min()) if len(owned) else 0) << (8 * level)
+            hi_key = ((int(owned.max()) if len(owned) else 0) << (8 * level)) | ((1 << (8 * level)) - 1)
+        hint = range_vary_bits(gv, lo_key, hi_key)
     if presplit and scratch["tmp"].numel() >= n_recv * key.elem_size:
         recv, st = eng.sort_presplit(recv, scratch["tmp"], n_recv, level, presplit_counts)
+    elif hint:
+        st = eng.sort_hinted(recv, n_recv, scratch.get("tmp") if scratch else None, hint)
     else:
         st = eng.sort(recv, n_recv, scratch.get("tmp") if scratch else None)
     if timings is not None:
-        timings.update({"level": level, "presplit": bool(presplit), "split": split.tolist(), "n_recv": n_recv, "local": st,
+        timings.update({"level": level, "presplit": bool(presplit), "vary_hint": hex(hint), "split": split.tolist(), "n_recv": n_recv, "local": st,
                         "splitter_mode": "prefix" if splitters is not None else "digit", "splitter_plan_ms": plan_t,
                         "exchange_path": "pipelined" if (pipelined and splitters is None and peers is not None) else
                         ("fused" if peers is not None else "all_to_all"),

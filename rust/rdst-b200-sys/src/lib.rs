@@ -151,6 +151,9 @@ extern "C" {
                           stats: *mut b200_stats) -> c_int;
     pub fn b200_sort_device(dev_ptr: *mut c_void, dev_tmp: *mut c_void, n: usize, desc: *const b200_key_desc,
                             opts: *const b200_sort_opts, stats: *mut b200_stats) -> c_int;
+    /// b200_sort_device for a caller that knows which key-image bits can vary (superset allowed): no counting pass.
+    pub fn b200_sort_device_hinted(dev_ptr: *mut c_void, dev_tmp: *mut c_void, n: usize, desc: *const b200_key_desc,
+                                   vary_bits: u64, opts: *const b200_sort_opts, stats: *mut b200_stats) -> c_int;
     /// Local sort of an array that arrives partitioned on `level` (bucket sizes `counts[256]`); result at *result_out.
     pub fn b200_sort_device_presplit(dev_ptr: *mut c_void, dev_tmp: *mut c_void, n: usize, desc: *const b200_key_desc, level: u32,
                                      counts: *const u64, opts: *const b200_sort_opts, stats: *mut b200_stats,

@@ -77,3 +77,30 @@ def test_splitter_plan_matches_the_numpy_model(P, kind):
         for r, s in enumerate(sh):
             part = dist.part_of_prefix(s, sp, int(masks[r]))
             assert np.bincount(part, minlength=P).tolist() == m[r].tolist()
+
+
+def test_vary_hints_are_supersets_of_the_truth():
+    """rdst_b200/dist.py tells every rank's local sort which key bits can vary inside its range (b200_sort_device_hinted
+    skips the counting pass): the job's varying bits below the highest bit in which the range's bounds differ.  A missing
+    bit would give a wrong order, so the hint must cover the true varying bits of ANY keys inside the range."""
+    from rdst_b200.dist import global_vary_bits, range_vary_bits
+
+    rng = np.random.default_rng(11)
+    for bits in (64, 61, 40, 33, 9):
+        a = rng.integers(0, 2**bits, 50_000, dtype=np.uint64)
+        a |= np.uint64(0x5 << 20) if bits > 24 else np.uint64(0)          # a few constant-one bits
+        hist = np.stack([np.bincount(((a >> np.uint64(8 * l)) & np.uint64(255)).astype(np.int64), minlength=256) for l in range(8)])
+        gv = global_vary_bits(hist)
+        true_vary = int(np.bitwise_or.reduce(a) & ~np.bitwise_and.reduce(a))
+        assert gv == true_vary
+        s = np.sort(a)
+        for parts in (2, 3, 8):
+            cuts = [0] + [len(s) * g // parts for g in range(1, parts)] + [len(s)]
+            for g in range(parts):
+                part = s[cuts[g]:cuts[g + 1]]
+                lo, hi = int(part[0]), int(part[-1])
+                hint = range_vary_bits(gv, lo, hi)
+                part_vary = int(np.bitwise_or.reduce(part) & ~np.bitwise_and.reduce(part))
+                assert part_vary & ~hint == 0, (bits, parts, g, hex(part_vary), hex(hint))
+                assert hint & ~gv == 0
+    assert range_vary_bits(0xFFFF, 7, 7) == 0
