@@ -127,10 +127,14 @@ def gen_device(torch, dtype, n, gen, seed):
         t = torch.randint(-2**63, 2**63 - 1, (n,), dtype=torch.int64, device="cuda", generator=g)
         if gen == "low40":
             t &= (1 << 40) - 1
-        if gen == "low61":
+        if gen.startswith("low61"):  # (low61heavyNN: one rank's range of an 8-way split that owns the job's top key)
             t &= (1 << 61) - 1
+            gen = gen[5:] or "low61"
         if gen == "lowcard":
             t &= 0x0101010101010101
+        if gen.startswith("heavy"):  # heavyNN: NN % of the records are one key (what the rank owning a job's top key sees)
+            m = torch.rand(n, dtype=torch.float32, device="cuda", generator=g) < (int(gen[5:]) / 100.0)
+            t[m] = 0x1234567812345678
         return t
     t = torch.randint(-2**31, 2**31, (n,), dtype=torch.int32, device="cuda", generator=g)
     if dt.kind == "f":
