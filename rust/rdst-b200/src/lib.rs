@@ -23,6 +23,7 @@
 //!
 //! NOTE: this crate is shipped as source only; the engine's build image has no Rust toolchain.
 
+pub mod device;
 mod gpu_key;
 pub mod multi;
 mod radix_key;
