@@ -98,6 +98,25 @@ def range_vary_bits(global_vary: int, lo_key: int, hi_key: int) -> int:
     return global_vary & ((1 << x.bit_length()) - 1)
 
 
+def presplit_layout(rows: np.ndarray, split: np.ndarray, parts: int, rank: int):
+    """Where rank `rank` stores its records of every digit when the exchange delivers each digit of the partition level
+    as its own run (`presplit`): rows = every rank's 256-bin row on that level [P, 256].  Returns (owner[256] = the rank
+    that owns digit d, offset[256] = first record of THIS rank's run of digit d inside the owner's receive buffer,
+    counts[256] = the bucket sizes of the array this rank receives).  A receive buffer is laid out bucket by bucket in
+    digit order, inside a bucket sender by sender in rank order; the runs of all senders tile it without gaps."""
+    tot = np.asarray(rows, dtype=np.int64)
+    gtot = tot.sum(axis=0)
+    owner = part_of_digit(split, parts)
+    bucket_start = np.zeros(256, dtype=np.int64)
+    for g in range(parts):
+        idx = np.nonzero(owner == g)[0]
+        if len(idx):
+            bucket_start[idx] = np.concatenate([[0], np.cumsum(gtot[idx])[:-1]])
+    offset = bucket_start + tot[:rank].sum(axis=0)
+    counts = np.where(owner == rank, gtot, 0).astype(np.uint64)
+    return owner, offset, counts
+
+
 def pick_partition_level(global_hist: np.ndarray) -> int:
     """Most significant level whose global histogram is not a single bucket (rdst's
     trivial-level skip, reference src/sorts/ska_sort.rs:52-54, applied to the splitters).
@@ -604,19 +623,10 @@ def sharded_sort(local, n_local: int, key: RadixKey, engine=None, group=None, re
             # the exchange IS the first MSD pass: every digit of the partition level gets its own run in the owner's
             # buffer — buckets in digit order, inside a bucket the senders in rank order — so the receiver's array
             # arrives partitioned on that level and its local sort starts at the second pass
-            tot = all_hist[:, level, :].astype(np.int64)              # [P, 256]
-            gtot = tot.sum(axis=0)
-            pod = part_of_digit(split, world)
-            bucket_start = np.zeros(256, dtype=np.int64)
-            for g in range(world):
-                idx = np.nonzero(pod == g)[0]
-                if len(idx):
-                    bucket_start[idx] = np.concatenate([[0], np.cumsum(gtot[idx])[:-1]])
-            before_me = tot[:rank].sum(axis=0)
-            dst256 = [peers.ptrs[int(pod[d])] + int(bucket_start[d] + before_me[d]) * key.elem_size for d in range(256)]
+            owner, offset, presplit_counts = presplit_layout(all_hist[:, level, :], split, world, rank)
+            dst256 = [peers.ptrs[int(owner[d])] + int(offset[d]) * key.elem_size for d in range(256)]
             pc = eng.partition_peers(local, dst256, n_local, level, hist[level], np.arange(1, 256, dtype=np.uint32), 256)
             assert np.array_equal(pc, hist[level].astype(np.int64)), "partition counts disagree with the histogram"
-            presplit_counts = np.where(pod == rank, gtot, 0).astype(np.uint64)
         else:
             pc = eng.partition_peers(local, dst, n_local, level, hist[level], split, world)
             assert np.array_equal(pc, send_counts), "partition counts disagree with the gathered histograms"

@@ -104,3 +104,36 @@ def test_vary_hints_are_supersets_of_the_truth():
                 assert part_vary & ~hint == 0, (bits, parts, g, hex(part_vary), hex(hint))
                 assert hint & ~gv == 0
     assert range_vary_bits(0xFFFF, 7, 7) == 0
+
+
+def test_presplit_layout_tiles_every_receive_buffer():
+    """rdst_b200/dist.py `presplit`: the exchange stores every digit of the partition level as its own run in the owner's
+    buffer.  Whatever the histograms, the runs of all senders must tile every receive buffer exactly — bucket by bucket in
+    digit order, inside a bucket sender by sender — and the receiver's bucket sizes must be the global counts."""
+    from rdst_b200.dist import choose_splitters, presplit_layout, send_matrix
+
+    rng = np.random.default_rng(21)
+    for parts in (2, 3, 4, 8):
+        for trial in range(6):
+            rows = rng.integers(0, 5000, (parts, 256))
+            if trial % 2:
+                rows[:, rng.integers(0, 256, 180)] = 0                # empty digits
+            if trial == 4:
+                rows[:, 17] += 400_000                                # a heavy digit
+            split = choose_splitters(rows.sum(axis=0), parts)
+            m = send_matrix(rows, split, parts)                      # m[r][g] = records r sends to g
+            filled = [np.zeros(int(m[:, g].sum()), dtype=np.int64) for g in range(parts)]
+            digit_at = [np.full(len(f), -1, dtype=np.int64) for f in filled]
+            for r in range(parts):
+                owner, offset, counts = presplit_layout(rows, split, parts, r)
+                assert int(counts.sum()) == int(m[:, r].sum())
+                assert np.array_equal(counts[owner == r], rows.sum(axis=0)[owner == r]) and not counts[owner != r].any()
+                for d in range(256):
+                    c = int(rows[r, d])
+                    g, o_ = int(owner[d]), int(offset[d])
+                    assert o_ + c <= len(filled[g])
+                    filled[g][o_:o_ + c] += 1
+                    digit_at[g][o_:o_ + c] = d
+            for g in range(parts):
+                assert (filled[g] == 1).all(), (parts, trial, g)      # no gap, no overlap
+                assert (np.diff(digit_at[g]) >= 0).all()              # buckets in digit order
