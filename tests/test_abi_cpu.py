@@ -189,3 +189,28 @@ def test_rust_sys_crate_declares_every_header_symbol():
 
     for t in ("b200_level", "b200_key_desc", "b200_sort_opts", "b200_stats", "b200_multi_stats", "b200_window_plan", "b200_route"):
         assert rust_fields(t) == c_fields(t), t
+
+
+def test_hinted_and_presplit_entry_points_validate_arguments_without_a_device():
+    l = _abi.lib()
+    d = RadixKey.for_dtype("u8").to_desc()
+    z = RadixKey.for_dtype("u8", levels=0).to_desc()
+    fake = C.c_void_p(256)
+    counts = (C.c_uint64 * 256)()
+    res = C.c_void_p()
+    # b200_sort_device_hinted
+    assert l.b200_sort_device_hinted(None, None, 0, C.byref(d), C.c_uint64(0), None, None) == 0      # n <= 1
+    assert l.b200_sort_device_hinted(None, None, 1, C.byref(d), C.c_uint64(0), None, None) == 0
+    assert l.b200_sort_device_hinted(None, None, 10, C.byref(d), C.c_uint64(0), None, None) == 6     # null data
+    assert l.b200_sort_device_hinted(fake, None, 10, C.byref(z), C.c_uint64(0), None, None) == 1     # LEVELS == 0
+    o_ = _abi.SortOpts()
+    o_.variant, o_.device, o_.route = -1, -1, 9
+    assert l.b200_sort_device_hinted(fake, None, 10, C.byref(d), C.c_uint64(0), C.byref(o_), None) == 6
+    # b200_sort_device_presplit
+    assert l.b200_sort_device_presplit(fake, fake, 10, C.byref(d), 8, counts, None, None, C.byref(res)) == 7   # level >= LEVELS
+    assert l.b200_sort_device_presplit(fake, fake, 10, C.byref(d), 7, None, None, None, C.byref(res)) == 6     # no counts
+    assert l.b200_sort_device_presplit(fake, fake, 10, C.byref(d), 7, counts, None, None, None) == 6           # no result slot
+    assert l.b200_sort_device_presplit(fake, None, 10, C.byref(d), 7, counts, None, None, C.byref(res)) == 6   # no scratch
+    assert l.b200_sort_device_presplit(fake, fake, 1, C.byref(d), 7, counts, None, None, C.byref(res)) == 0    # n <= 1 ...
+    assert res.value == 256                                                                                   # ... result where it was
+    assert l.b200_sort_device_presplit(fake, fake, 10, C.byref(z), 0, counts, None, None, C.byref(res)) == 1   # LEVELS == 0
